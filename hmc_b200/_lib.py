@@ -1,0 +1,84 @@
+"""ctypes binding of libhmcb.so (include/hmcb.h).  Loading fails loudly: the
+product path has no CPU fallback."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libhmcb.so")
+
+OK, E_ARG, E_UNSUPPORTED, E_CUDA, E_WORKSPACE = 0, -1, -2, -3, -4
+F64, F32 = 0, 1
+MODEL_FUNNEL, MODEL_GAUSSIAN, MODEL_ROSENBROCK, MODEL_LOGISTIC = 0, 1, 2, 3
+RULE_PYHMC, RULE_ALG = 0, 1
+RNG_NORMAL_F64 = 1
+MAX_PROPS = 6
+
+
+class Model(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("d", C.c_int32), ("dtype", C.c_int32), ("n_data", C.c_int32),
+                ("par", C.c_double * 4), ("dev0", C.c_void_p), ("dev1", C.c_void_p), ("invmetric_diag", C.c_void_p)]
+
+
+class Chains(C.Structure):
+    _fields_ = [("n_chains", C.c_int64), ("chain_offset", C.c_int64), ("q_in", C.c_void_p), ("q_out", C.c_void_p),
+                ("stride_chain", C.c_int64), ("stride_dim", C.c_int64)]
+
+
+class Rng(C.Structure):
+    _fields_ = [("seed", C.c_uint64), ("iteration", C.c_uint64), ("p_inject", C.c_void_p), ("u_inject", C.c_void_p),
+                ("u_stride", C.c_int32), ("flags", C.c_int32)]
+
+
+class StepOut(C.Structure):
+    _fields_ = [("p_out", C.c_void_p), ("code", C.c_void_p), ("energies", C.c_void_p), ("avec", C.c_void_p),
+                ("counts", C.c_void_p), ("accept_prob", C.c_void_p)]
+
+
+# every symbol include/hmcb.h declares: name -> (restype, argtypes)
+SIGNATURES = {
+    "hmcb_version": (C.c_int, []),
+    "hmcb_last_error": (C.c_char_p, []),
+    "hmcb_hmc_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double, C.c_int32,
+                                C.POINTER(StepOut), C.c_void_p]),
+    "hmcb_leapfrog": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.c_void_p, C.c_void_p, C.c_int32, C.c_double,
+                                C.c_void_p]),
+    "hmcb_logp_grad": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.c_void_p, C.c_void_p, C.c_void_p]),
+    "hmcb_drhmc_workspace_bytes": (C.c_size_t, [C.POINTER(Model), C.c_int64, C.c_int32]),
+    "hmcb_drhmc_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
+                                  C.c_int32, C.c_double, C.POINTER(StepOut), C.c_void_p, C.c_size_t, C.c_void_p]),
+    "hmcb_probe_fma": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.POINTER(C.c_double),
+                                 C.c_void_p]),
+}
+
+_lib = None
+
+
+class HmcbError(RuntimeError):
+    pass
+
+
+def load():
+    """Load libhmcb.so and set prototypes.  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise HmcbError("libhmcb.so not found at %s -- build it with `python __graft_entry__.py` "
+                        "(there is no CPU fallback)" % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype, fn.argtypes = res, args
+    _lib = lib
+    return lib
+
+
+def check(rc):
+    if rc != 0:
+        msg = load().hmcb_last_error()
+        raise HmcbError("libhmcb error %d: %s" % (rc, msg.decode() if msg else "?"))
+
+
+def ptr(t):
+    """Device pointer of a torch tensor (or None)."""
+    return None if t is None else C.c_void_p(t.data_ptr())

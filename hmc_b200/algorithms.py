@@ -1,0 +1,223 @@
+"""Batched drop-in for the reference's ``src/algorithms.py`` on the hot path:
+``Sampler`` (:3-30), ``DualAveragingStepSize`` (:34-75), ``HMC`` (:79-254),
+``DRHMC`` (:467-555) and the ``alg_dict`` registry (:823-832).
+
+Constructors keep the reference's positional order
+``Cls(log_prob, grad_log_prob=None, log_prob_and_grad=None, invmetric_diag=None)``
+and also accept ``Cls(model)``.  ``step`` / ``sample`` keep their names and
+keyword arguments (``nsamples, burnin, step_size, nleap, [nprops, stepfactor],
+[epsadapt]``); ``q`` may be ``[C, d]`` and every per-chain output gains a
+leading C axis.  Accept codes follow the reference per class: HMC 1/0/-1,
+DRHMC j+1/0.  The debug prints of the reference (:518-521,:547) are not
+reproduced.
+"""
+import numpy as np
+import torch
+
+from . import _lib, dist
+from .engine import Batch
+from .pyhmc import HMC as _PyHMCBase
+
+
+class Sampler:
+    """Result container of ``sample`` (src/algorithms.py:3-30): lists while
+    sampling, stacked arrays after ``to_array``."""
+
+    def __init__(self):
+        self.samples = []
+        self.accepts = []
+        self.Hs = []
+        self.counts = []
+        self.i = 0
+
+    @staticmethod
+    def _stack(v):
+        if len(v) and torch.is_tensor(v[0]):
+            return torch.stack(v)
+        return np.array(v)
+
+    def to_array(self):
+        for key, val in self.__dict__.items():
+            if isinstance(val, list):
+                self.__dict__[key] = self._stack(val)
+
+    def to_list(self):
+        for key, val in self.__dict__.items():
+            if isinstance(val, np.ndarray) or torch.is_tensor(val):
+                self.__dict__[key] = list(val)
+
+    def appends(self, q, acc, Hs, count):
+        self.i += 1
+        self.accepts.append(acc)
+        self.samples.append(q)
+        self.Hs.append(Hs)
+        self.counts.append(count)
+
+    def save(self, path):
+        pass
+
+
+class DualAveragingStepSize:
+    """Nesterov dual averaging of the log step size (src/algorithms.py:34-75).
+    Scalar host arithmetic; with many chains the caller feeds it the chain-mean
+    acceptance statistic (all-reduced over ranks), see HMC.adapt_stepsize."""
+
+    def __init__(self, initial_step_size, target_accept=0.65, gamma=0.05, t0=10.0, kappa=0.75, nadapt=0):
+        self.initial_step_size = initial_step_size
+        self.mu = np.log(10 * initial_step_size)  # shrinkage point, biased upwards
+        self.target_accept = target_accept
+        self.gamma = gamma
+        self.t = t0
+        self.kappa = kappa
+        self.error_sum = 0
+        self.log_averaged_step = 0
+        self.nadapt = nadapt
+
+    def update(self, p_accept):
+        """Feed one acceptance statistic; returns (noisy step size, averaged step size)."""
+        if np.isnan(p_accept) or np.isinf(p_accept):
+            p_accept = 0.0
+        if p_accept > 1:
+            p_accept = 1.0
+        self.error_sum += self.target_accept - p_accept
+        log_step = self.mu - self.error_sum / (np.sqrt(self.t) * self.gamma)
+        eta = self.t ** -self.kappa
+        self.log_averaged_step = eta * log_step + (1 - eta) * self.log_averaged_step
+        self.t += 1
+        return np.exp(log_step), np.exp(self.log_averaged_step)
+
+    def __call__(self, i, p_accept):
+        if i == 0:
+            return self.initial_step_size
+        if i < self.nadapt:
+            step_size, _ = self.update(p_accept)
+        elif i == self.nadapt:
+            _, step_size = self.update(p_accept)
+        else:
+            step_size = np.exp(self.log_averaged_step)
+        return step_size
+
+
+class HMC(_PyHMCBase):
+    """algorithms.HMC (src/algorithms.py:79-254): codes 1/0/-1, the uniform is
+    always consumed (:184)."""
+
+    _rule = _lib.RULE_ALG
+
+    def __init__(self, log_prob, grad_log_prob=None, log_prob_and_grad=None, invmetric_diag=None, **engine_kw):
+        super().__init__(log_prob, grad_log_prob, invmetric_diag, log_prob_and_grad=log_prob_and_grad, **engine_kw)
+        self.log_prob_and_grad = self.model.log_prob_and_grad
+
+    def step(self, q, nleap, step_size, p=None, u=None, **kwargs):
+        """One transition per chain (src/algorithms.py:192-198)."""
+        return self._step(q, nleap, step_size, p=p, u=u)
+
+    def _parse_kwargs_sample(self, **kwargs):
+        self.nsamples = kwargs["nsamples"]
+        self.burnin = kwargs["burnin"]
+        self.step_size = kwargs["step_size"]
+        self.nleap = kwargs["nleap"]
+
+    def _device_q(self, q):
+        b = Batch(q, self.engine.dev, self.engine.dtype)
+        self.engine.check_dim(b)
+        return b
+
+    def adapt_stepsize(self, q, epsadapt, **kwargs):
+        """Dual-averaging warm-up (src/algorithms.py:209-230): epsadapt+1 transitions,
+        each feeding the update with prob = exp(H0-H1) clipped to [0,1], or 0 for a
+        chain that did not move.  With C chains (and R ranks) the statistic is the
+        mean over all chains -- one shared step size, all-reduced over NCCL."""
+        step_size = self.step_size
+        da = DualAveragingStepSize(step_size)
+        self._parse_kwargs_sample(**kwargs)
+        b = self._device_q(q)
+        qd = b.q
+        for i in range(epsadapt + 1):
+            out = self.engine.hmc_step(qd, self.nleap, step_size, self._rule, want_p=False, want_prob=True)
+            qd = out["q"]
+            stat = torch.stack([out["prob"].sum(dtype=torch.float64),
+                                torch.tensor(float(qd.shape[0]), dtype=torch.float64, device=qd.device)])
+            stat = dist.all_reduce_sum(stat)
+            prob = float(stat[0] / stat[1])
+            if i < epsadapt:
+                step_size, _ = da.update(prob)
+            else:
+                _, step_size = da.update(prob)
+                self.step_size = step_size
+        return b.out(qd)
+
+    def sample(self, q, p=None, callback=None, skipburn=True, epsadapt=0, **kwargs):
+        """src/algorithms.py:233-254.  ``accepts`` is kept for every iteration, samples /
+        Hs / counts only for i > burnin (strict, as the reference)."""
+        self._parse_kwargs_sample(**kwargs)
+        state = Sampler()
+        if epsadapt:
+            q = self.adapt_stepsize(q, epsadapt, **kwargs)
+        b = self._device_q(q)
+        qd = b.q
+        for i in range(self.nsamples + self.burnin):
+            out = self.engine.hmc_step(qd, self.nleap, self.step_size, self._rule, want_p=False)
+            qd = out["q"]
+            state.i += 1
+            state.accepts.append(b.out(out["code"].to(torch.float64)))
+            if skipburn & (i > self.burnin):
+                state.samples.append(b.out(qd))
+                state.Hs.append(b.out(out["Hs"]))
+                state.counts.append(b.out(out["counts"]))
+                if callback is not None:
+                    callback(state)
+        state.to_array()
+        return state
+
+
+class DRHMC(HMC):
+    """Delayed-rejection HMC, algorithms.DRHMC (src/algorithms.py:467-555).  One
+    ``step`` is hmcb_drhmc_step: stage kernels over device-compacted lists of the
+    chains still rejecting, ghost recursion (get_num, :474-497) included."""
+
+    def step(self, q, nleap, step_size, nprops, stepfactor, p=None, u=None):
+        """Returns (q, p, code, avec, [Hcount, Vgcount, leapcount]); code = j+1 if
+        accepted at stage j, else 0 (src/algorithms.py:500-530)."""
+        e = self.engine
+        b = self._device_q(q)
+        out = e.drhmc_step(b.q, nleap, step_size, nprops, stepfactor, p=p, u=u)
+        if b.unbatched:
+            cnt = out["counts"][0].tolist()
+            self.Hcount, self.Vgcount, self.leapcount = cnt
+            return b.out(out["q"]), b.out(out["p"]), int(out["code"][0]), b.out(out["avec"]), cnt
+        self.Hcount, self.Vgcount, self.leapcount = out["counts"][:, 0], out["counts"][:, 1], out["counts"][:, 2]
+        return b.out(out["q"]), b.out(out["p"]), b.out(out["code"]), b.out(out["avec"]), b.out(out["counts"])
+
+    def sample(self, q, p=None, callback=None, **kwargs):
+        """src/algorithms.py:534-555: every iteration (burn-in included) is stored."""
+        self._parse_kwargs_sample(**kwargs)
+        state = Sampler()
+        state.avecs = []
+        b = self._device_q(q)
+        qd = b.q
+        for i in range(self.nsamples + self.burnin):
+            out = self.engine.drhmc_step(qd, self.nleap, self.step_size, kwargs["nprops"], kwargs["stepfactor"],
+                                         want_p=False)
+            qd = out["q"]
+            state.i += 1
+            state.samples.append(b.out(qd))
+            state.accepts.append(b.out(out["code"]))
+            state.avecs.append(b.out(out["avec"]))
+            state.counts.append(b.out(out["counts"]))
+            if callback is not None:
+                callback(state)
+        state.to_array()
+        return state
+
+
+def dr_stage_lengths(nleap, nprops, stepfactor):
+    """(L_j, eps scale 1/f^j) per stage as the reference computes them
+    (src/algorithms.py:510-511): int() truncation of nleap*f^j with a float f."""
+    return [int(nleap * stepfactor ** j) for j in range(nprops)], [1.0 / stepfactor ** j for j in range(nprops)]
+
+
+# name -> class registry (src/algorithms.py:823-832); the other keys of the reference
+# ('ghmc', 'pghmc', 'drghmc', 'pdrhmc_metrop', 'pdrhmc_hasting') are later rows of SURVEY.md section 8f
+alg_dict = {"hmc": HMC, "drhmc": DRHMC}
+

@@ -1,0 +1,327 @@
+// api.cu -- C ABI entry points of libhmcb.so (see include/hmcb.h).
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "launch.cuh"
+
+namespace hmcb {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+  set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
+  return HMCB_E_CUDA;
+}
+
+static int query_device_attr(cudaDeviceAttr attr) {
+  int dev = 0, v = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  if (cudaDeviceGetAttribute(&v, attr, dev) != cudaSuccess) return 0;
+  return v;
+}
+
+int sm_count() {
+  static thread_local int cached_dev = -1, cached = 0;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev != cached_dev) {
+    cached = query_device_attr(cudaDevAttrMultiProcessorCount);
+    cached_dev = dev;
+  }
+  return cached > 0 ? cached : 1;
+}
+
+int max_optin_smem() {
+  static thread_local int cached_dev = -1, cached = 0;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev != cached_dev) {
+    cached = query_device_attr(cudaDevAttrMaxSharedMemoryPerBlockOptin);
+    cached_dev = dev;
+  }
+  return cached;
+}
+
+std::vector<Entry>& registry() {
+  static std::vector<Entry> r;
+  return r;
+}
+
+const Entry* choose_entry(const hmcb_model& hm) {
+  const int unitm = hm.invmetric_diag ? 0 : 1;
+  int force_lpc = 0;
+  if (const char* e = getenv("HMCB_LPC")) force_lpc = atoi(e);
+  const Entry* best = nullptr;
+  long best_cost = 0;
+  for (int pass = 0; pass < 2 && !best; ++pass) {
+    for (const Entry& e : registry()) {
+      if (e.kind != hm.kind || e.dtype != hm.dtype || e.unitm != unitm) continue;
+      if (pass == 0 && force_lpc && e.lpc != force_lpc) continue;
+      if (slots_needed(hm.d, e.lpc) > e.epl) continue;
+      if (hm.kind == HMCB_MODEL_ROSENBROCK && (e.epl & 1)) continue;
+      // least padded slots first, then fewest lanes per chain
+      const long cost = (long)e.epl * e.lpc * 64 + e.lpc;
+      if (!best || cost < best_cost) {
+        best = &e;
+        best_cost = cost;
+      }
+    }
+    if (!force_lpc) break;
+  }
+  if (!best)
+    set_error("no compiled kernel shape for model kind %d, dtype %d, d=%d, %s metric", hm.kind, hm.dtype, hm.d,
+              unitm ? "unit" : "diagonal");
+  return best;
+}
+
+static int check_model(const hmcb_model* m) {
+  HMCB_CHECK_ARG(m != nullptr, "model is NULL");
+  HMCB_CHECK_ARG(m->d >= 1, "model dimension d=%d must be >= 1", m->d);
+  HMCB_CHECK_ARG(m->dtype == HMCB_F64 || m->dtype == HMCB_F32, "unknown dtype %d", m->dtype);
+  switch (m->kind) {
+    case HMCB_MODEL_FUNNEL:
+      HMCB_CHECK_ARG(m->d >= 2, "funnel needs d >= 2");
+      HMCB_CHECK_ARG(m->par[0] > 0, "funnel sigma must be > 0");
+      break;
+    case HMCB_MODEL_GAUSSIAN:
+      HMCB_CHECK_ARG(m->dev0 != nullptr, "gaussian needs the precision matrix in dev0");
+      break;
+    case HMCB_MODEL_ROSENBROCK:
+      HMCB_CHECK_ARG(m->d % 2 == 0, "pairwise Rosenbrock needs an even d");
+      HMCB_CHECK_ARG(m->par[2] != 0, "rosenbrock temperature T must be non-zero");
+      break;
+    default:
+      set_error("model kind %d has no transition kernel in this build", m->kind);
+      return HMCB_E_UNSUPPORTED;
+  }
+  return 0;
+}
+
+static int check_chains(const hmcb_chains* c) {
+  HMCB_CHECK_ARG(c != nullptr, "chains is NULL");
+  HMCB_CHECK_ARG(c->n_chains >= 0 && c->n_chains < (int64_t)1 << 31, "n_chains=%lld out of range", (long long)c->n_chains);
+  if (c->n_chains == 0) return 0;
+  HMCB_CHECK_ARG(c->q_in && c->q_out, "q_in/q_out must be device pointers");
+  HMCB_CHECK_ARG(c->stride_chain > 0 && c->stride_dim > 0, "strides must be positive");
+  return 0;
+}
+
+template <typename T>
+static void fill_args(TransArgs<T>& a, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r,
+                      const hmcb_step_out* o) {
+  memset(&a, 0, sizeof(a));
+  a.n_chains = c->n_chains;
+  a.chain_offset = c->chain_offset;
+  a.d = m->d;
+  a.q_in = (const T*)c->q_in;
+  a.q_out = (T*)c->q_out;
+  a.sc = c->stride_chain;
+  a.sd = c->stride_dim;
+  a.seed = r->seed;
+  a.iteration = (uint32_t)r->iteration;
+  a.rng_flags = r->flags;
+  a.p_inject = (const T*)r->p_inject;
+  a.u_inject = r->u_inject;
+  a.u_stride = r->u_stride;
+  if (o) {
+    a.p_out = (T*)o->p_out;
+    a.code = o->code;
+    a.energies = (T*)o->energies;
+    a.avec_out = (T*)o->avec;
+    a.counts = o->counts;
+    a.accept_prob = (T*)o->accept_prob;
+  }
+  a.minv = (const T*)m->invmetric_diag;
+}
+
+template <typename T>
+static int hmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r, int n_leap,
+                      double eps, int rule, const hmcb_step_out* o, cudaStream_t st) {
+  TransArgs<T> a;
+  fill_args(a, m, c, r, o);
+  a.rule = rule;
+  a.nprops = 1;
+  a.L[0] = n_leap;
+  a.eps[0] = (T)eps;
+  return e->fn(*m, OP_HMC, &a, st);
+}
+
+// ------------------------------------------------------------------ DR workspace
+struct DrLayout {
+  size_t off_count, off_list, off_H0, off_avec, off_counts, off_frames, total;
+  int64_t frame_threads;
+};
+
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+static int dr_layout(const Entry* e, const hmcb_model* m, int64_t n_chains, int nprops, DrLayout& L) {
+  LaunchInfo li;
+  int rc = e->fn(*m, OP_QUERY, &li, nullptr);
+  if (rc) return rc;
+  const size_t ts = m->dtype == HMCB_F64 ? 8 : 4;
+  const int64_t groups_per_block = li.threads / li.lpc;
+  int64_t blocks = (n_chains + groups_per_block - 1) / groups_per_block;
+  if (blocks < 1) blocks = 1;
+  if (blocks > li.max_blocks) blocks = li.max_blocks;
+  L.frame_threads = blocks * li.threads;
+  size_t off = 0;
+  L.off_count = off; off = align_up(off + (kMaxProps + 2) * sizeof(int32_t), 256);
+  L.off_list = off;  off = align_up(off + (size_t)kMaxProps * n_chains * sizeof(int32_t), 256);
+  L.off_H0 = off;    off = align_up(off + (size_t)n_chains * ts, 256);
+  L.off_avec = off;  off = align_up(off + (size_t)n_chains * kMaxProps * ts, 256);
+  L.off_counts = off; off = align_up(off + (size_t)n_chains * 3 * sizeof(int32_t), 256);
+  L.off_frames = off;
+  const int nframes = nprops > 1 ? nprops - 1 : 0;
+  off = align_up(off + (size_t)nframes * 2 * li.epl * L.frame_threads * ts, 256);
+  L.total = off;
+  return 0;
+}
+
+template <typename T>
+static int drhmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r, int n_leap,
+                        double eps, int nprops, double stepfactor, const hmcb_step_out* o, void* ws,
+                        const DrLayout& L, cudaStream_t st) {
+  TransArgs<T> a;
+  fill_args(a, m, c, r, o);
+  a.nprops = nprops;
+  for (int j = 0; j < nprops; ++j) {
+    // fac = stepfactor**j; nleapf = int(nleap*fac); step_sizef = step_size/fac (src/algorithms.py:510-511)
+    const double fac = pow(stepfactor, (double)j);
+    a.L[j] = (int32_t)(n_leap * fac);
+    a.eps[j] = (T)(eps / fac);
+  }
+  char* w = (char*)ws;
+  a.ws.count = (int32_t*)(w + L.off_count);
+  a.ws.list = (int32_t*)(w + L.off_list);
+  a.ws.H0 = (T*)(w + L.off_H0);
+  a.ws.avec = (T*)(w + L.off_avec);
+  a.ws.counts = (int32_t*)(w + L.off_counts);
+  a.ws.frames = (T*)(w + L.off_frames);
+  a.ws.frame_threads = L.frame_threads;
+  if (nprops > 1) HMCB_CUDA(cudaMemsetAsync(a.ws.count, 0, (kMaxProps + 2) * sizeof(int32_t), st));
+  a.stage = 0;
+  int rc = e->fn(*m, OP_DR0, &a, st);
+  for (int j = 1; j < nprops && rc == 0; ++j) {
+    a.stage = j;
+    rc = e->fn(*m, OP_DRN, &a, st);
+  }
+  return rc;
+}
+
+}  // namespace hmcb
+
+using namespace hmcb;
+
+extern "C" {
+
+int hmcb_version(void) { return HMCB_VERSION; }
+
+const char* hmcb_last_error(void) { return g_err; }
+
+int hmcb_hmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
+                  double step_size, int32_t rule, const hmcb_step_out* out, void* stream) {
+  int rc;
+  if ((rc = check_model(model))) return rc;
+  if ((rc = check_chains(chains))) return rc;
+  HMCB_CHECK_ARG(rng != nullptr, "rng is NULL");
+  HMCB_CHECK_ARG(rule == HMCB_RULE_PYHMC || rule == HMCB_RULE_ALG, "unknown accept rule %d", rule);
+  HMCB_CHECK_ARG(n_leap >= 0, "n_leap must be >= 0");
+  if (chains->n_chains == 0) return 0;
+  const Entry* e = choose_entry(*model);
+  if (!e) return HMCB_E_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (model->dtype == HMCB_F64) return hmc_step_t<double>(e, model, chains, rng, n_leap, step_size, rule, out, st);
+  return hmc_step_t<float>(e, model, chains, rng, n_leap, step_size, rule, out, st);
+}
+
+int hmcb_leapfrog(const hmcb_model* model, const hmcb_chains* chains, const void* p_in, void* p_out, int32_t n_leap,
+                  double step_size, void* stream) {
+  int rc;
+  if ((rc = check_model(model))) return rc;
+  if ((rc = check_chains(chains))) return rc;
+  HMCB_CHECK_ARG(p_in && p_out, "p_in/p_out must be device pointers");
+  if (chains->n_chains == 0) return 0;
+  const Entry* e = choose_entry(*model);
+  if (!e) return HMCB_E_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (model->dtype == HMCB_F64) {
+    AuxArgs<double> a{chains->n_chains, model->d, (const double*)chains->q_in, (double*)chains->q_out,
+                      chains->stride_chain, chains->stride_dim, (const double*)p_in, (double*)p_out, nullptr, nullptr,
+                      (const double*)model->invmetric_diag, n_leap, step_size};
+    return e->fn(*model, OP_LEAPFROG, &a, st);
+  }
+  AuxArgs<float> a{chains->n_chains, model->d, (const float*)chains->q_in, (float*)chains->q_out,
+                   chains->stride_chain, chains->stride_dim, (const float*)p_in, (float*)p_out, nullptr, nullptr,
+                   (const float*)model->invmetric_diag, n_leap, (float)step_size};
+  return e->fn(*model, OP_LEAPFROG, &a, st);
+}
+
+int hmcb_logp_grad(const hmcb_model* model, const hmcb_chains* chains, void* logp, void* grad, void* stream) {
+  int rc;
+  if ((rc = check_model(model))) return rc;
+  HMCB_CHECK_ARG(chains != nullptr && chains->q_in != nullptr, "chains/q_in is NULL");
+  HMCB_CHECK_ARG(chains->stride_chain > 0 && chains->stride_dim > 0, "strides must be positive");
+  if (chains->n_chains == 0) return 0;
+  const Entry* e = choose_entry(*model);
+  if (!e) return HMCB_E_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (model->dtype == HMCB_F64) {
+    AuxArgs<double> a{chains->n_chains, model->d, (const double*)chains->q_in, nullptr, chains->stride_chain,
+                      chains->stride_dim, nullptr, nullptr, (double*)logp, (double*)grad,
+                      (const double*)model->invmetric_diag, 0, 0.0};
+    return e->fn(*model, OP_LOGPGRAD, &a, st);
+  }
+  AuxArgs<float> a{chains->n_chains, model->d, (const float*)chains->q_in, nullptr, chains->stride_chain,
+                   chains->stride_dim, nullptr, nullptr, (float*)logp, (float*)grad,
+                   (const float*)model->invmetric_diag, 0, 0.0f};
+  return e->fn(*model, OP_LOGPGRAD, &a, st);
+}
+
+size_t hmcb_drhmc_workspace_bytes(const hmcb_model* model, int64_t n_chains, int32_t nprops) {
+  if (check_model(model)) return 0;
+  if (n_chains < 1 || nprops < 1 || nprops > kMaxProps) {
+    set_error("workspace query: n_chains=%lld nprops=%d out of range (nprops <= %d)", (long long)n_chains, nprops, kMaxProps);
+    return 0;
+  }
+  const Entry* e = choose_entry(*model);
+  if (!e) return 0;
+  DrLayout L;
+  if (dr_layout(e, model, n_chains, nprops, L)) return 0;
+  return L.total;
+}
+
+int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
+                    double step_size, int32_t nprops, double stepfactor, const hmcb_step_out* out, void* workspace,
+                    size_t workspace_bytes, void* stream) {
+  int rc;
+  if ((rc = check_model(model))) return rc;
+  if ((rc = check_chains(chains))) return rc;
+  HMCB_CHECK_ARG(rng != nullptr, "rng is NULL");
+  HMCB_CHECK_ARG(nprops >= 1 && nprops <= kMaxProps, "nprops=%d must be in 1..%d", nprops, kMaxProps);
+  HMCB_CHECK_ARG(stepfactor > 0, "stepfactor must be > 0");
+  HMCB_CHECK_ARG(n_leap >= 0, "n_leap must be >= 0");
+  HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= nprops, "u_inject needs u_stride >= nprops");
+  if (chains->n_chains == 0) return 0;
+  const Entry* e = choose_entry(*model);
+  if (!e) return HMCB_E_UNSUPPORTED;
+  DrLayout L;
+  if ((rc = dr_layout(e, model, chains->n_chains, nprops, L))) return rc;
+  if (!workspace || workspace_bytes < L.total) {
+    set_error("drhmc workspace too small: have %zu bytes, need %zu", workspace ? workspace_bytes : (size_t)0, L.total);
+    return HMCB_E_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (model->dtype == HMCB_F64)
+    return drhmc_step_t<double>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, out, workspace, L, st);
+  return drhmc_step_t<float>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, out, workspace, L, st);
+}
+
+}  // extern "C"

@@ -1,0 +1,148 @@
+// common.cuh -- shared device/host helpers for libhmcb (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <math.h>
+
+#include "../../include/hmcb.h"
+
+namespace hmcb {
+
+// ---------------------------------------------------------------- host: errors
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);
+
+#define HMCB_CHECK_ARG(cond, ...)            \
+  do {                                       \
+    if (!(cond)) {                           \
+      hmcb::set_error(__VA_ARGS__);          \
+      return HMCB_E_ARG;                     \
+    }                                        \
+  } while (0)
+
+#define HMCB_CUDA(call)                                        \
+  do {                                                         \
+    cudaError_t e__ = (call);                                  \
+    if (e__ != cudaSuccess) return hmcb::cuda_fail(e__, #call); \
+  } while (0)
+
+int sm_count();  // SM count of the current device (cached per device)
+
+// ---------------------------------------------------------------- lane layout
+// A chain's d elements are spread over LPC adjacent lanes of a warp ("group"),
+// EPL register slots per lane.  Elements are dealt in blocks of 4 (one Philox
+// call yields 4 normals): block b = i/4 lives on lane b % LPC, at slots
+// 4*(b/LPC) .. +3.  Element 0 (the funnel's v) is always lane 0, slot 0, and a
+// Rosenbrock pair (2k, 2k+1) always shares a lane.  Slots whose element index
+// is >= d are padding and hold zeros.
+template <int EPL, int LPC>
+struct Layout {
+  static constexpr int kEPL = EPL;
+  static constexpr int kLPC = LPC;
+  static constexpr int kBlocks = (EPL + 3) / 4;  // element blocks per lane
+  __host__ __device__ static inline int elem(int lane, int slot) {
+    return (((slot >> 2) * LPC + lane) << 2) + (slot & 3);
+  }
+};
+
+// slots per lane needed to hold d elements on LPC lanes (host side, for dispatch)
+inline int slots_needed(int d, int lpc) {
+  int mx = 0;
+  for (int i = 0; i < d; ++i) {
+    int b = i >> 2;
+    int slot = ((b / lpc) << 2) + (i & 3);
+    if (slot + 1 > mx) mx = slot + 1;
+  }
+  return mx;
+}
+
+// ---------------------------------------------------------------- group reductions
+template <int LPC, typename T>
+__device__ __forceinline__ T group_sum(T x) {
+#pragma unroll
+  for (int o = LPC >> 1; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+  return x;
+}
+
+// same, naming only the group's own lanes: safe when groups of one warp diverge
+template <int LPC, typename T>
+__device__ __forceinline__ T group_sum_masked(T x, unsigned mask) {
+#pragma unroll
+  for (int o = LPC >> 1; o > 0; o >>= 1) x += __shfl_xor_sync(mask, x, o);
+  return x;
+}
+
+// ---------------------------------------------------------------- Philox4x32-10
+// Counter-based generator (Salmon et al. 2011).  key = seed; counter =
+// (chain_lo, chain_hi, iteration, stream<<24 | block).  Stateless: a draw is a
+// pure function of (seed, global chain id, iteration, stream, block), so chains
+// give the same results however they are sharded over GPUs or lanes.
+struct Philox {
+  static constexpr uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+  __host__ __device__ static inline void round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+#ifdef __CUDA_ARCH__
+    uint32_t hi0 = __umulhi(M0, c[0]), hi1 = __umulhi(M1, c[2]);
+#else
+    uint32_t hi0 = (uint32_t)(((uint64_t)M0 * c[0]) >> 32), hi1 = (uint32_t)(((uint64_t)M1 * c[2]) >> 32);
+#endif
+    uint32_t lo0 = M0 * c[0], lo1 = M1 * c[2];
+    uint32_t n0 = hi1 ^ c[1] ^ k0, n2 = hi0 ^ c[3] ^ k1;
+    c[0] = n0; c[1] = lo1; c[2] = n2; c[3] = lo0;
+  }
+  __host__ __device__ static inline void gen(uint64_t seed, uint64_t chain, uint32_t iter, uint32_t stream,
+                                             uint32_t block, uint32_t (&out)[4]) {
+    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+    out[0] = (uint32_t)chain; out[1] = (uint32_t)(chain >> 32); out[2] = iter; out[3] = (stream << 24) | (block & 0xFFFFFFu);
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+      round(out, k0, k1);
+      k0 += W0; k1 += W1;
+    }
+  }
+};
+
+enum : uint32_t { STREAM_MOMENTUM = 0, STREAM_ACCEPT = 1, STREAM_STEPSIZE = 2 };
+
+// uniform in [0,1) with 53 bits from two words
+__host__ __device__ inline double u53(uint32_t a, uint32_t b) {
+  return (double)(((uint64_t)(a >> 5) << 26) | (uint64_t)(b >> 6)) * (1.0 / 9007199254740992.0);
+}
+
+// Four standard normals from one Philox block: Box-Muller on two (u1,u2) pairs,
+// transcendental part in f32 (the FP32/SFU pipes are idle next to the FP64
+// leapfrog).  32-bit radius and angle resolution; |z| <= 6.7.
+__device__ __forceinline__ void normal4_f32(const uint32_t (&w)[4], float (&z)[4]) {
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    float u1 = ((float)w[2 * h] + 0.5f) * 2.3283064365386963e-10f;  // (0,1]
+    float r = sqrtf(-2.0f * logf(u1));
+    float s, c;
+    sincospif((float)w[2 * h + 1] * 4.656612873077393e-10f, &s, &c);  // angle in [0, 2pi]
+    z[2 * h] = r * c;
+    z[2 * h + 1] = r * s;
+  }
+}
+
+// Two standard normals in f64 from one Philox block (53-bit uniforms).
+__device__ __forceinline__ void normal2_f64(const uint32_t (&w)[4], double (&z)[2]) {
+  double u1 = 1.0 - u53(w[0], w[1]);  // (0,1]
+  double r = sqrt(-2.0 * log(u1));
+  double s, c;
+  sincospi(2.0 * u53(w[2], w[3]), &s, &c);
+  z[0] = r * c;
+  z[1] = r * s;
+}
+
+// ---------------------------------------------------------------- small math
+template <typename T> __device__ __forceinline__ T t_exp(T x);
+template <> __device__ __forceinline__ double t_exp<double>(double x) { return exp(x); }
+template <> __device__ __forceinline__ float t_exp<float>(float x) { return expf(x); }
+
+template <typename T> __device__ __forceinline__ T t_rsqrt(T x);
+template <> __device__ __forceinline__ double t_rsqrt<double>(double x) { return 1.0 / sqrt(x); }
+template <> __device__ __forceinline__ float t_rsqrt<float>(float x) { return 1.0f / sqrtf(x); }
+
+template <typename T> __device__ __forceinline__ bool t_bad(T x) { return isnan(x) || isinf(x); }
+
+}  // namespace hmcb

@@ -1,0 +1,200 @@
+// launch.cuh -- host side: kernel-configuration registry and launch helpers.
+//
+// Kernels are compiled for a fixed set of (EPL slots per lane, LPC lanes per
+// chain) shapes; at run time the smallest shape that holds the model's d is
+// picked (least padding, then fewest lanes).  Each inst_*.cu registers the
+// shapes it compiled for one (model, dtype).
+#pragma once
+#include <vector>
+
+#include "transition.cuh"
+
+namespace hmcb {
+
+enum Op { OP_HMC = 0, OP_DR0 = 1, OP_DRN = 2, OP_LEAPFROG = 3, OP_LOGPGRAD = 4, OP_QUERY = 5 };
+
+struct LaunchInfo {
+  int threads;        // block size
+  int max_blocks;     // resident blocks on the whole device for this kernel
+  int epl, lpc;
+};
+
+// args is TransArgs<T>* for the transition ops, AuxArgs<T>* for the others, LaunchInfo* for OP_QUERY
+using LaunchFn = int (*)(const hmcb_model& hm, int op, void* args, cudaStream_t st);
+
+struct Entry {
+  int kind, dtype, unitm, epl, lpc;
+  LaunchFn fn;
+};
+
+std::vector<Entry>& registry();
+struct Registrar {
+  explicit Registrar(const Entry& e) { registry().push_back(e); }
+};
+
+// pick the compiled shape for this model; nullptr (+ error set) if none fits
+const Entry* choose_entry(const hmcb_model& hm);
+
+// leapfrog-only / logp+grad kernels share the transition kernel's device code
+template <typename T>
+struct AuxArgs {
+  int64_t n_chains;
+  int32_t d;
+  const T* q_in;
+  T* q_out;
+  int64_t sc, sd;
+  const T* p_in;
+  T* p_out;
+  T* logp;
+  T* grad;
+  const T* minv;
+  int32_t n_leap;
+  T eps;
+};
+
+template <class Model, typename T, int EPL, int LPC, bool UNITM, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) k_aux(const Model model, const AuxArgs<T> a, const int op) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  using Lay = Layout<EPL, LPC>;
+  constexpr int GPB = THREADS / LPC;
+  const int d = a.d;
+  model.block_init(smem_raw, THREADS);
+  GroupCtx<T> c;
+  c.lane = threadIdx.x & (LPC - 1);
+  c.d = d;
+  const int group_in_warp = (threadIdx.x & 31) / LPC;
+  c.mask = (LPC == 32) ? 0xffffffffu : (((1u << LPC) - 1u) << (group_in_warp * LPC));
+  c.smem_q = nullptr;
+  if (Model::kNeedsSmem) c.smem_q = (T*)smem_raw + model.p_smem_elems() + (size_t)(threadIdx.x / LPC) * d;
+  T minv[UNITM ? 1 : EPL];
+  if (!UNITM) {
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) {
+      const int i = Lay::elem(c.lane, s);
+      minv[UNITM ? 0 : s] = (i < d) ? a.minv[i] : T(1);
+    }
+  } else {
+    minv[0] = T(1);
+  }
+  const int64_t total_groups = (int64_t)gridDim.x * GPB;
+  for (int64_t chain = ((int64_t)blockIdx.x * THREADS + threadIdx.x) / LPC; chain < a.n_chains; chain += total_groups) {
+    const int64_t off = chain * a.sc;
+    T q[EPL], p[EPL];
+    load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
+    if (op == OP_LEAPFROG) {
+      load_vec<T, EPL, LPC>(p, a.p_in, off, a.sd, c.lane, d, T(1));
+      T Vs, Ve;
+      leapfrog<Model, T, EPL, LPC, UNITM>(model, q, p, minv, a.n_leap > 1 ? a.n_leap : 1, a.eps, c, Vs, Ve);
+      store_vec<T, EPL, LPC>(q, a.q_out, off, a.sd, c.lane, d);
+      store_vec<T, EPL, LPC>(p, a.p_out, off, a.sd, c.lane, d);
+    } else {
+      // p = 0 - 1*gradV = grad log_prob; V returned
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) p[s] = T(0);
+      const T V = model.template kick<EPL, LPC, true>(q, p, T(1), c);
+      if (a.grad) store_vec<T, EPL, LPC>(p, a.grad, off, a.sd, c.lane, d);
+      if (a.logp && c.lane == 0) a.logp[chain] = -V;
+    }
+  }
+}
+
+template <typename T, int EPL, bool UNITM, bool GAUSS>
+constexpr int min_blocks_for() {
+  // 32-bit registers: q, p (+ metric, + gradient accumulator) plus working set
+  constexpr int words = (2 * EPL + (UNITM ? 0 : EPL) + (GAUSS ? EPL : 0)) * (int)(sizeof(T) / 4) + 56;
+  constexpr int mb = 65536 / (words * 128);
+  return mb < 1 ? 1 : (mb > 8 ? 8 : mb);
+}
+
+int max_optin_smem();  // per-block opt-in shared memory limit of the current device
+
+template <class Model, typename T, int EPL, int LPC, bool UNITM, bool GAUSS>
+int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
+  constexpr int THREADS = 128;
+  constexpr int MINB = min_blocks_for<T, EPL, UNITM, GAUSS>();
+  constexpr int GPB = THREADS / LPC;
+  Model model = Model::make(hm);
+  size_t smem = 0;
+  if constexpr (GAUSS) {
+    // per-group q staging, plus P itself when the block can hold it
+    const size_t stage = (size_t)GPB * hm.d * sizeof(T);
+    const size_t withP = stage + (size_t)hm.d * hm.d * sizeof(T);
+    model.p_in_smem = (withP <= (size_t)max_optin_smem()) ? 1 : 0;
+    smem = model.p_in_smem ? withP : stage;
+  }
+
+  auto prep = [&](auto kernel, int& max_blocks) -> int {
+    if (smem > 48 * 1024) HMCB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    HMCB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, THREADS, smem));
+    if (per_sm < 1) {
+      set_error("kernel shape EPL=%d LPC=%d does not fit on an SM (smem %zu B)", EPL, LPC, smem);
+      return HMCB_E_UNSUPPORTED;
+    }
+    max_blocks = per_sm * sm_count();
+    return 0;
+  };
+  auto grid_for = [&](int64_t items, int max_blocks) -> int {
+    int64_t need = (items + GPB - 1) / GPB;
+    if (need < 1) need = 1;
+    return (int)(need < max_blocks ? need : max_blocks);
+  };
+
+  int max_blocks = 0, rc;
+  switch (op) {
+    case OP_HMC: {
+      auto k = k_transition<Model, T, EPL, LPC, UNITM, MODE_HMC, THREADS, MINB>;
+      if ((rc = prep(k, max_blocks))) return rc;
+      TransArgs<T>& a = *(TransArgs<T>*)args;
+      k<<<grid_for(a.n_chains, max_blocks), THREADS, smem, st>>>(model, a);
+      break;
+    }
+    case OP_DR0: {
+      auto k = k_transition<Model, T, EPL, LPC, UNITM, MODE_DR0, THREADS, MINB>;
+      if ((rc = prep(k, max_blocks))) return rc;
+      TransArgs<T>& a = *(TransArgs<T>*)args;
+      k<<<grid_for(a.n_chains, max_blocks), THREADS, smem, st>>>(model, a);
+      break;
+    }
+    case OP_DRN: {
+      auto k = k_transition<Model, T, EPL, LPC, UNITM, MODE_DRN, THREADS, MINB>;
+      if ((rc = prep(k, max_blocks))) return rc;
+      TransArgs<T>& a = *(TransArgs<T>*)args;
+      // the list length lives on the device: launch the persistent grid the frames were sized for
+      const int grid = (int)(a.ws.frame_threads / THREADS);
+      k<<<grid, THREADS, smem, st>>>(model, a);
+      break;
+    }
+    case OP_LEAPFROG:
+    case OP_LOGPGRAD: {
+      auto k = k_aux<Model, T, EPL, LPC, UNITM, THREADS, MINB>;
+      if ((rc = prep(k, max_blocks))) return rc;
+      AuxArgs<T>& a = *(AuxArgs<T>*)args;
+      k<<<grid_for(a.n_chains, max_blocks), THREADS, smem, st>>>(model, a, op);
+      break;
+    }
+    case OP_QUERY: {
+      auto k = k_transition<Model, T, EPL, LPC, UNITM, MODE_DRN, THREADS, MINB>;
+      if ((rc = prep(k, max_blocks))) return rc;
+      LaunchInfo* li = (LaunchInfo*)args;
+      li->threads = THREADS;
+      li->max_blocks = max_blocks;
+      li->epl = EPL;
+      li->lpc = LPC;
+      return 0;
+    }
+    default:
+      set_error("internal: unknown op %d", op);
+      return HMCB_E_ARG;
+  }
+  HMCB_CUDA(cudaPeekAtLastError());
+  return 0;
+}
+
+// One line per compiled shape:  HMCB_SHAPE(ModelTmpl, KIND, T, DTYPE, UNITM, EPL, LPC)
+#define HMCB_SHAPE(ModelTmpl, KIND, T, DTYPE, UNITM, EPL, LPC)                                              \
+  static hmcb::Registrar reg_##KIND##_##DTYPE##_##UNITM##_##EPL##_##LPC(hmcb::Entry{                        \
+      KIND, DTYPE, UNITM, EPL, LPC,                                                                         \
+      &hmcb::launch_any<hmcb::ModelTmpl<T>, T, EPL, LPC, (UNITM != 0), (KIND == HMCB_MODEL_GAUSSIAN)>});
+
+}  // namespace hmcb

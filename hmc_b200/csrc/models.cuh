@@ -1,0 +1,177 @@
+// models.cuh -- device-side model densities with analytic gradients.
+//
+// A model provides, for the chain whose elements sit in q[EPL] across the LPC
+// lanes of a group (see Layout in common.cuh):
+//
+//   T kick<EPL,LPC,WANT_V>(q, p, h, ctx)   p -= h * grad V(q);  returns V(q) if WANT_V
+//
+// where V = -log_prob.  The gradient never leaves registers: the momentum update
+// is fused into its evaluation.  These are the in-kernel restatements of the
+// numpy callables in hmc_b200/models.py; the funnel follows the reference's Stan
+// text (scripts/models.py:9-19), the others are builder-defined (the reference
+// has no such models).
+#pragma once
+#include "common.cuh"
+
+namespace hmcb {
+
+template <typename T>
+struct GroupCtx {
+  int lane;        // lane within the group, 0..LPC-1
+  int d;           // true dimension
+  unsigned mask;   // warp lanes of this group (shuffle mask)
+  T* smem_q;       // gaussian: per-group staging area of d elements (else unused)
+};
+
+// -------------------------------------------------------------------- funnel
+// V(v,theta) = v^2/(2 s^2) + (n/2) v + exp(-v)/2 * sum(theta^2)
+// dV/dv = v/s^2 + n/2 - exp(-v)/2 * S,  dV/dtheta_i = exp(-v) theta_i
+template <typename T>
+struct FunnelModel {
+  T inv_s2, half_n;
+  static constexpr bool kNeedsSmem = false;
+  __host__ static FunnelModel make(const hmcb_model& m) {
+    FunnelModel f;
+    f.inv_s2 = (T)(1.0 / (m.par[0] * m.par[0]));
+    f.half_n = (T)(0.5 * (m.d - 1));
+    return f;
+  }
+  __host__ __device__ size_t p_smem_elems() const { return 0; }
+  __device__ __forceinline__ void block_init(void*, int) const {}
+
+  template <int EPL, int LPC, bool WANT_V>
+  __device__ __forceinline__ T kick(const T (&q)[EPL], T (&p)[EPL], T h, const GroupCtx<T>& c) const {
+    const bool own_v = (c.lane == 0);
+    // S = sum theta^2: four partial sums so the FMA chain does not serialise
+    T acc[4] = {T(0), T(0), T(0), T(0)};
+    const T t0 = own_v ? T(0) : q[0];
+    acc[0] = t0 * t0;
+#pragma unroll
+    for (int s = 1; s < EPL; ++s) acc[s & 3] = fma(q[s], q[s], acc[s & 3]);
+    T S = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+#pragma unroll
+    for (int o = LPC >> 1; o > 0; o >>= 1) S += __shfl_xor_sync(c.mask, S, o);
+    const T v = (LPC == 1) ? q[0] : __shfl_sync(c.mask, q[0], 0, LPC);
+    const T e = t_exp<T>(-v);
+    const T he = h * e;
+    const T gv = fma(v, inv_s2, half_n) - T(0.5) * e * S;
+    p[0] = own_v ? (p[0] - h * gv) : fma(-he, q[0], p[0]);
+#pragma unroll
+    for (int s = 1; s < EPL; ++s) p[s] = fma(-he, q[s], p[s]);
+    if (WANT_V) return T(0.5) * v * v * inv_s2 + half_n * v + T(0.5) * e * S;
+    return T(0);
+  }
+};
+
+// -------------------------------------------------------------------- pairwise Rosenbrock
+// V = sum_k [(a-u_k)^2 + b (w_k-u_k^2)^2] / T,   (u_k, w_k) = (x[2k], x[2k+1])
+template <typename T>
+struct RosenbrockModel {
+  T a, b, inv_T;
+  static constexpr bool kNeedsSmem = false;
+  __host__ static RosenbrockModel make(const hmcb_model& m) {
+    RosenbrockModel r;
+    r.a = (T)m.par[0];
+    r.b = (T)m.par[1];
+    r.inv_T = (T)(1.0 / m.par[2]);
+    return r;
+  }
+  __host__ __device__ size_t p_smem_elems() const { return 0; }
+  __device__ __forceinline__ void block_init(void*, int) const {}
+
+  template <int EPL, int LPC, bool WANT_V>
+  __device__ __forceinline__ T kick(const T (&q)[EPL], T (&p)[EPL], T h, const GroupCtx<T>& c) const {
+    static_assert(EPL % 2 == 0, "Rosenbrock pairs need an even slot count");
+    T Vl = T(0);
+    const T hs = h * inv_T;
+#pragma unroll
+    for (int s = 0; s < EPL; s += 2) {
+      const bool valid = Layout<EPL, LPC>::elem(c.lane, s) < c.d;  // padding pairs contribute nothing
+      const T u = q[s], w = q[s + 1];
+      const T am = a - u;
+      const T r = fma(-u, u, w);
+      const T br = b * r;
+      const T gu = T(-2) * am - T(4) * u * br;  // dV/du * T
+      const T gw = T(2) * br;                   // dV/dw * T
+      p[s] = valid ? fma(-hs, gu, p[s]) : p[s];
+      p[s + 1] = valid ? fma(-hs, gw, p[s + 1]) : p[s + 1];
+      if (WANT_V) Vl += valid ? fma(am, am, br * r) : T(0);
+    }
+    if (WANT_V) {
+#pragma unroll
+      for (int o = LPC >> 1; o > 0; o >>= 1) Vl += __shfl_xor_sync(c.mask, Vl, o);
+      return Vl * inv_T;
+    }
+    return T(0);
+  }
+};
+
+// -------------------------------------------------------------------- dense Gaussian
+// V = x^T P x / 2, grad V = P x.  P (row-major, symmetric) is copied to shared
+// memory once per block when it fits, else read through L1/L2.  Each group stages
+// its q in shared memory so every lane can read all d elements.
+template <typename T>
+struct GaussianModel {
+  const T* P;      // global
+  int d;
+  int p_in_smem;   // host decision
+  static constexpr bool kNeedsSmem = true;
+  __host__ static GaussianModel make(const hmcb_model& m) {
+    GaussianModel g;
+    g.P = (const T*)m.dev0;
+    g.d = m.d;
+    g.p_in_smem = 0;
+    return g;
+  }
+  // shared layout: [P (d*d) if p_in_smem][per-group q staging: groups_per_block * d]
+  __host__ __device__ size_t p_smem_elems() const { return p_in_smem ? (size_t)d * d : 0; }
+
+  __device__ __forceinline__ void block_init(void* smem, int nthreads) const {
+    if (p_in_smem) {
+      T* sP = (T*)smem;
+      for (int i = threadIdx.x; i < d * d; i += nthreads) sP[i] = P[i];
+      __syncthreads();
+    }
+  }
+
+  template <int EPL, int LPC, bool WANT_V>
+  __device__ __forceinline__ T kick(const T (&q)[EPL], T (&p)[EPL], T h, const GroupCtx<T>& c) const {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const T* Pm = p_in_smem ? (const T*)smem_raw : P;
+    T* sq = c.smem_q;
+    __syncwarp(c.mask);
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) {
+      const int i = Layout<EPL, LPC>::elem(c.lane, s);
+      if (i < d) sq[i] = q[s];
+    }
+    __syncwarp(c.mask);
+    T g[EPL];
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) g[s] = T(0);
+    for (int j = 0; j < d; ++j) {
+      const T qj = sq[j];
+      const T* row = Pm + (size_t)j * d;  // P symmetric: row j == column j
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) {
+        const int i = Layout<EPL, LPC>::elem(c.lane, s);
+        const T pij = (i < d) ? row[i] : T(0);
+        g[s] = fma(pij, qj, g[s]);
+      }
+    }
+    T Vl = T(0);
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) {
+      if (WANT_V) Vl = fma(q[s], g[s], Vl);
+      p[s] = fma(-h, g[s], p[s]);
+    }
+    if (WANT_V) {
+#pragma unroll
+      for (int o = LPC >> 1; o > 0; o >>= 1) Vl += __shfl_xor_sync(c.mask, Vl, o);
+      return T(0.5) * Vl;
+    }
+    return T(0);
+  }
+};
+
+}  // namespace hmcb

@@ -1,0 +1,45 @@
+// probe.cu -- pipe-peak measurement kernel (hmcb_probe_fma): each thread runs
+// ILP independent chains of dependent FMAs held in registers, so the launch is
+// bound by the FP64 (or FP32) FMA pipe and nothing else.  Its measured rate is
+// the denominator for roofline fractions of the leapfrog kernels.
+#include "common.cuh"
+
+namespace hmcb {
+
+template <typename T, int ILP>
+__global__ void __launch_bounds__(256) k_probe_fma(T* sink, long long iters, T a, T b) {
+  T x[ILP];
+#pragma unroll
+  for (int i = 0; i < ILP; ++i) x[i] = (T)(threadIdx.x + i) * (T)1e-3;
+  for (long long it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+#pragma unroll
+      for (int i = 0; i < ILP; ++i) x[i] = fma(x[i], a, b);
+  }
+  T s = T(0);
+#pragma unroll
+  for (int i = 0; i < ILP; ++i) s += x[i];
+  sink[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+}  // namespace hmcb
+
+extern "C" int hmcb_probe_fma(int32_t dtype, int32_t blocks, int32_t threads, int64_t iters, void* sink,
+                              double* fma_count, void* stream) {
+  using namespace hmcb;
+  constexpr int ILP = 8;
+  HMCB_CHECK_ARG(blocks > 0 && threads > 0 && threads <= 256 && iters > 0 && sink, "bad probe arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == HMCB_F64)
+    k_probe_fma<double, ILP><<<blocks, threads, 0, st>>>((double*)sink, iters, 0.999999, 1e-7);
+  else if (dtype == HMCB_F32)
+    k_probe_fma<float, ILP><<<blocks, threads, 0, st>>>((float*)sink, iters, 0.999999f, 1e-7f);
+  else {
+    set_error("unknown dtype %d", dtype);
+    return HMCB_E_ARG;
+  }
+  HMCB_CUDA(cudaPeekAtLastError());
+  if (fma_count) *fma_count = (double)blocks * threads * (double)iters * 8.0 * ILP;
+  return 0;
+}

@@ -1,0 +1,435 @@
+// transition.cuh -- the fused transition kernel: momentum draw, leapfrog
+// trajectories, energies, accept test, counters, for a block of chains whose
+// state lives in registers.
+//
+// One kernel template serves three modes:
+//   MODE_HMC     vanilla HMC transition   (src/pyhmc.py:64-69, src/algorithms.py:192-198)
+//   MODE_DR0     delayed-rejection stage 0 over all chains (src/algorithms.py:500-530, j = 0)
+//   MODE_DRN     delayed-rejection stage J >= 1 over the compacted list of chains
+//                still rejected, including the ghost recursion get_num
+//                (src/algorithms.py:474-497) run as an explicit-stack state machine.
+#pragma once
+#include <cooperative_groups.h>
+
+#include "common.cuh"
+#include "models.cuh"
+
+namespace hmcb {
+namespace cg = cooperative_groups;
+
+enum { MODE_HMC = 0, MODE_DR0 = 1, MODE_DRN = 2 };
+constexpr int kMaxProps = 6;  // max delayed-rejection stages
+
+// Scratch for delayed rejection (caller-owned; carved by the host, see drhmc.cu).
+template <typename T>
+struct DrScratch {
+  int32_t* count;    // [kMaxProps+1] chains queued per stage
+  int32_t* list;     // [kMaxProps][n_chains] local chain ids queued for stage j
+  T* H0;             // [n_chains] energy at (q0,p0)
+  T* avec;           // [n_chains*kMaxProps] running stage acceptance probabilities
+  int32_t* counts;   // [n_chains*3] running Hcount, Vgcount, leapcount
+  T* frames;         // [(kMaxProps-1)*2*EPL*frame_threads] per-thread proposal frames
+  int64_t frame_threads;
+};
+
+template <typename T>
+struct TransArgs {
+  int64_t n_chains, chain_offset;
+  int32_t d;
+  const T* q_in;
+  T* q_out;
+  int64_t sc, sd;
+  uint64_t seed;
+  uint32_t iteration;
+  int32_t rng_flags;
+  const T* p_inject;
+  const double* u_inject;
+  int32_t u_stride;
+  T* p_out;
+  int32_t* code;
+  T* energies;
+  T* avec_out;
+  int32_t* counts;
+  T* accept_prob;
+  const T* minv;     // inverse metric diagonal or nullptr
+  int32_t rule;      // HMCB_RULE_*
+  int32_t nprops, stage;
+  int32_t L[kMaxProps];
+  T eps[kMaxProps];
+  DrScratch<T> ws;
+};
+
+// ------------------------------------------------------------------ state movement
+template <typename T, int EPL, int LPC>
+__device__ __forceinline__ void load_vec(T (&x)[EPL], const T* base, int64_t off, int64_t sd, int lane, int d, T sign) {
+#pragma unroll
+  for (int s = 0; s < EPL; ++s) {
+    const int i = Layout<EPL, LPC>::elem(lane, s);
+    x[s] = (i < d) ? sign * base[off + i * sd] : T(0);
+  }
+}
+
+template <typename T, int EPL, int LPC>
+__device__ __forceinline__ void store_vec(const T (&x)[EPL], T* base, int64_t off, int64_t sd, int lane, int d) {
+#pragma unroll
+  for (int s = 0; s < EPL; ++s) {
+    const int i = Layout<EPL, LPC>::elem(lane, s);
+    if (i < d) base[off + i * sd] = x[s];
+  }
+}
+
+// Four standard normals for element block `blk` of a chain.  Kept out of line:
+// it runs once per block per transition, and inlining its log/sincos bodies into
+// every unrolled slot would dwarf the leapfrog loop in code size.
+struct Normal4 { double z[4]; };
+static __device__ __noinline__ Normal4 philox_normal4(uint64_t seed, uint64_t gchain, uint32_t iter, uint32_t blk, int flags) {
+  Normal4 r;
+  uint32_t w[4];
+  if (flags & HMCB_RNG_NORMAL_F64) {
+    double z2[2];
+    Philox::gen(seed, gchain, iter, STREAM_MOMENTUM, 2 * blk, w);
+    normal2_f64(w, z2);
+    r.z[0] = z2[0]; r.z[1] = z2[1];
+    Philox::gen(seed, gchain, iter, STREAM_MOMENTUM, 2 * blk + 1, w);
+    normal2_f64(w, z2);
+    r.z[2] = z2[0]; r.z[3] = z2[1];
+  } else {
+    float z[4];
+    Philox::gen(seed, gchain, iter, STREAM_MOMENTUM, blk, w);
+    normal4_f32(w, z);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) r.z[k] = (double)z[k];
+  }
+  return r;
+}
+
+// momentum p = z * metricstd, z ~ N(0,1) (src/pyhmc.py:66); z from Philox or injected
+template <typename T, int EPL, int LPC, bool UNITM>
+__device__ __forceinline__ void draw_momentum(T (&p)[EPL], const TransArgs<T>& a, const T (&minv)[UNITM ? 1 : EPL],
+                                              int64_t chain, int lane, int d) {
+  if (a.p_inject) {
+    load_vec<T, EPL, LPC>(p, a.p_inject, chain * a.sc, a.sd, lane, d, T(1));
+  } else {
+    const uint64_t gchain = (uint64_t)(a.chain_offset + chain);
+#pragma unroll
+    for (int b = 0; b < Layout<EPL, LPC>::kBlocks; ++b) {
+      const Normal4 n = philox_normal4(a.seed, gchain, a.iteration, (uint32_t)(b * LPC + lane), a.rng_flags);
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (4 * b + k < EPL) p[4 * b + k] = (Layout<EPL, LPC>::elem(lane, 4 * b + k) < d) ? (T)n.z[k] : T(0);
+    }
+  }
+  if (!UNITM) {
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) p[s] *= t_rsqrt<T>(minv[UNITM ? 0 : s]);
+  }
+}
+
+template <typename T>
+__device__ __forceinline__ double draw_uniform(const TransArgs<T>& a, int64_t chain, int idx) {
+  if (a.u_inject) return a.u_inject[chain * a.u_stride + idx];
+  uint32_t w[4];
+  Philox::gen(a.seed, (uint64_t)(a.chain_offset + chain), a.iteration, STREAM_ACCEPT, (uint32_t)(idx >> 1), w);
+  return (idx & 1) ? u53(w[2], w[3]) : u53(w[0], w[1]);
+}
+
+// KE = 0.5 * sum(p^2 * invmetric) (src/pyhmc.py:18)
+template <typename T, int EPL, int LPC, bool UNITM>
+__device__ __forceinline__ T kinetic(const T (&p)[EPL], const T (&minv)[UNITM ? 1 : EPL], unsigned mask) {
+  T acc[4] = {T(0), T(0), T(0), T(0)};
+#pragma unroll
+  for (int s = 0; s < EPL; ++s) acc[s & 3] = fma(UNITM ? p[s] : p[s] * minv[UNITM ? 0 : s], p[s], acc[s & 3]);
+  T k = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+#pragma unroll
+  for (int o = LPC >> 1; o > 0; o >>= 1) k += __shfl_xor_sync(mask, k, o);
+  return T(0.5) * k;
+}
+
+template <typename T, int EPL, bool UNITM>
+__device__ __forceinline__ void drift(T (&q)[EPL], const T (&p)[EPL], const T (&minv)[UNITM ? 1 : EPL], T eps) {
+#pragma unroll
+  for (int s = 0; s < EPL; ++s) q[s] = fma(eps, UNITM ? p[s] : p[s] * minv[UNITM ? 0 : s], q[s]);
+}
+
+// Leapfrog of N steps (src/pyhmc.py:35-48): half kick, N-1 x (drift, kick), drift,
+// half kick = N+1 gradient evaluations.  Returns V at the start and end points.
+template <class Model, typename T, int EPL, int LPC, bool UNITM>
+__device__ __forceinline__ void leapfrog(const Model& model, T (&q)[EPL], T (&p)[EPL],
+                                         const T (&minv)[UNITM ? 1 : EPL], int N, T eps, const GroupCtx<T>& c,
+                                         T& V_start, T& V_end) {
+  V_start = model.template kick<EPL, LPC, true>(q, p, T(0.5) * eps, c);
+#pragma unroll 1
+  for (int i = 1; i < N; ++i) {
+    drift<T, EPL, UNITM>(q, p, minv, eps);
+    model.template kick<EPL, LPC, false>(q, p, eps, c);
+  }
+  drift<T, EPL, UNITM>(q, p, minv, eps);
+  V_end = model.template kick<EPL, LPC, true>(q, p, T(0.5) * eps, c);
+}
+
+// ------------------------------------------------------------------ the kernel
+// Threads are grouped LPC lanes per chain; a warp carries 32/LPC chains.  Work
+// items (chains, or entries of the stage list) are walked grid-stride so a
+// persistent grid covers any count, including one only known on the device.
+template <class Model, typename T, int EPL, int LPC, bool UNITM, int MODE, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model, const TransArgs<T> a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  using Lay = Layout<EPL, LPC>;
+  constexpr int GPB = THREADS / LPC;
+  const int d = a.d;
+
+  model.block_init(smem_raw, THREADS);
+
+  GroupCtx<T> c;
+  c.lane = threadIdx.x & (LPC - 1);
+  c.d = d;
+  const int group_in_warp = (threadIdx.x & 31) / LPC;
+  c.mask = (LPC == 32) ? 0xffffffffu : (((1u << LPC) - 1u) << (group_in_warp * LPC));
+  c.smem_q = nullptr;
+  if (Model::kNeedsSmem) {
+    // staging area after the model's own shared block (see GaussianModel)
+    T* base = (T*)smem_raw + model.p_smem_elems();
+    c.smem_q = base + (size_t)(threadIdx.x / LPC) * d;
+  }
+
+  T minv[UNITM ? 1 : EPL];
+  if (!UNITM) {
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) {
+      const int i = Lay::elem(c.lane, s);
+      minv[UNITM ? 0 : s] = (i < d) ? a.minv[i] : T(1);
+    }
+  } else {
+    minv[0] = T(1);
+  }
+
+  const int64_t gthread = (int64_t)blockIdx.x * THREADS + threadIdx.x;
+  const int64_t total_groups = (int64_t)gridDim.x * GPB;
+  const int64_t count = (MODE == MODE_DRN) ? (int64_t)a.ws.count[a.stage] : a.n_chains;
+  const int32_t* list = (MODE == MODE_DRN) ? a.ws.list + (int64_t)a.stage * a.n_chains : nullptr;
+  const int J = (MODE == MODE_DRN) ? a.stage : 0;
+
+  for (int64_t item = gthread / LPC; item < count; item += total_groups) {
+    const int64_t chain = (MODE == MODE_DRN) ? (int64_t)list[item] : item;
+    const int64_t qoff = chain * a.sc;
+
+    T q[EPL], p[EPL];
+    int cH, cVg, cLeap;
+
+    if (MODE != MODE_DRN) {
+      // ---------------- single trajectory from (q0, p0): HMC step or DR stage 0
+      load_vec<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d, T(1));
+      draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);
+      const T K0 = kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+      T V0, V1;
+      const int N = a.L[0] > 1 ? a.L[0] : 1;
+      leapfrog<Model, T, EPL, LPC, UNITM>(model, q, p, minv, N, a.eps[0], c, V0, V1);
+      const T H0 = V0 + K0;
+      const T H1 = V1 + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+      cH = 2; cVg = N + 1; cLeap = 1;
+      // sum(q0 - q1) == 0 is the reference's "did not move" test (src/pyhmc.py:57)
+      T dq = T(0);
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) {
+        const int i = Lay::elem(c.lane, s);
+        if (i < d) dq += a.q_in[qoff + i * a.sd] - q[s];
+      }
+      dq = group_sum_masked<LPC, T>(dq, c.mask);
+      T prob = t_exp<T>(H0 - H1);
+
+      bool accept;
+      int code;
+      bool finished = true;
+      if (MODE == MODE_HMC) {
+        const bool bad = t_bad(prob) || dq == T(0);
+        const double u = draw_uniform<T>(a, chain, 0);
+        const T pm = prob < T(1) ? prob : T(1);
+        accept = !bad && !(u > (double)pm);
+        code = bad ? (a.rule == HMCB_RULE_PYHMC ? 2 : -1) : (accept ? 1 : 0);
+        if (c.lane == 0) {
+          if (a.energies) { a.energies[2 * chain] = H0; a.energies[2 * chain + 1] = H1; }
+          if (a.accept_prob) a.accept_prob[chain] = (accept && !t_bad(prob)) ? pm : T(0);
+        }
+      } else {
+        if (dq == T(0)) prob = T(0);
+        if (t_bad(prob)) prob = T(0);
+        const T a0 = prob < T(1) ? prob : T(1);
+        const double u = draw_uniform<T>(a, chain, 0);
+        accept = u < (double)a0;
+        code = accept ? 1 : 0;
+        finished = accept || a.nprops == 1;
+        if (c.lane == 0) {
+          if (finished) {
+            if (a.avec_out) {
+              a.avec_out[chain * a.nprops] = a0;
+              for (int i = 1; i < a.nprops; ++i) a.avec_out[chain * a.nprops + i] = T(0);
+            }
+          } else {
+            a.ws.H0[chain] = H0;
+            a.ws.avec[chain * kMaxProps] = a0;
+            a.ws.counts[3 * chain] = cH; a.ws.counts[3 * chain + 1] = cVg; a.ws.counts[3 * chain + 2] = cLeap;
+            cg::coalesced_group g = cg::coalesced_threads();
+            int base = 0;
+            if (g.thread_rank() == 0) base = atomicAdd(a.ws.count + 1, (int)g.size());
+            base = g.shfl(base, 0);
+            a.ws.list[(int64_t)1 * a.n_chains + base + g.thread_rank()] = (int32_t)chain;
+          }
+        }
+      }
+      if (finished) {
+        if (c.lane == 0) {
+          if (a.code) a.code[chain] = code;
+          if (a.counts) { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = cLeap; }
+        }
+        if (accept) {
+          store_vec<T, EPL, LPC>(q, a.q_out, qoff, a.sd, c.lane, d);
+          if (a.p_out) store_vec<T, EPL, LPC>(p, a.p_out, qoff, a.sd, c.lane, d);
+        } else {
+          if (a.q_out != a.q_in) {
+#pragma unroll
+            for (int s = 0; s < EPL; ++s) {
+              const int i = Lay::elem(c.lane, s);
+              if (i < d) a.q_out[qoff + i * a.sd] = a.q_in[qoff + i * a.sd];
+            }
+          }
+          if (a.p_out) {
+            draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);
+            store_vec<T, EPL, LPC>(p, a.p_out, qoff, a.sd, c.lane, d);
+          }
+        }
+      }
+    } else {
+      // ---------------- DR stage J >= 1: explicit-stack walk of step/get_num
+      // level 0 is DRHMC.step's own loop at j = J; level l >= 1 is a get_num frame
+      // whose base state is the proposal stored in frame[l-1] with p flipped.
+      int lm[kMaxProps], lj[kMaxProps];
+      T lHb[kMaxProps], lpf[kMaxProps], lav[kMaxProps][kMaxProps];
+      int lvl = 0;
+      lm[0] = J + 1; lj[0] = J; lHb[0] = a.ws.H0[chain];
+#pragma unroll
+      for (int i = 0; i < kMaxProps; ++i) lav[0][i] = (i < J) ? a.ws.avec[chain * kMaxProps + i] : T(0);
+      cH = a.ws.counts[3 * chain]; cVg = a.ws.counts[3 * chain + 1]; cLeap = a.ws.counts[3 * chain + 2];
+      const int64_t FT = a.ws.frame_threads;
+      T* fr = a.ws.frames + gthread;  // frame f: q at (2f)*EPL*FT, p at (2f+1)*EPL*FT, slot stride FT
+      T prob_top = T(0);
+
+      for (;;) {
+        const int j = lj[lvl];
+        const int N = a.L[j] > 1 ? a.L[j] : 1;
+        if (lvl == 0) {
+          load_vec<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d, T(1));
+          draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);
+        } else {
+          const T* fq = fr + (int64_t)(2 * (lvl - 1)) * EPL * FT;
+#pragma unroll
+          for (int s = 0; s < EPL; ++s) { q[s] = fq[(int64_t)s * FT]; p[s] = -fq[(int64_t)(EPL + s) * FT]; }
+        }
+        T Vs, Ve;
+        leapfrog<Model, T, EPL, LPC, UNITM>(model, q, p, minv, N, a.eps[j], c, Vs, Ve);
+        const T Hn = Ve + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+        cH += 1; cVg += N + 1; cLeap += 1;
+        T dq = T(0);
+        if (lvl == 0) {
+#pragma unroll
+          for (int s = 0; s < EPL; ++s) {
+            const int i = Lay::elem(c.lane, s);
+            if (i < d) dq += a.q_in[qoff + i * a.sd] - q[s];
+          }
+        } else {
+          const T* fq = fr + (int64_t)(2 * (lvl - 1)) * EPL * FT;
+#pragma unroll
+          for (int s = 0; s < EPL; ++s) dq += fq[(int64_t)s * FT] - q[s];
+        }
+        dq = group_sum_masked<LPC, T>(dq, c.mask);
+        T pf = t_exp<T>(lHb[lvl] - Hn);
+        if (dq == T(0)) pf = T(0);
+
+        if (j > 0) {
+          // the ghost chain from the flipped proposal is needed: push a get_num frame
+          T* fq = fr + (int64_t)(2 * lvl) * EPL * FT;
+#pragma unroll
+          for (int s = 0; s < EPL; ++s) { fq[(int64_t)s * FT] = q[s]; fq[(int64_t)(EPL + s) * FT] = p[s]; }
+          lpf[lvl] = pf;
+          ++lvl;
+          lm[lvl] = j; lj[lvl] = 0; lHb[lvl] = Hn;
+#pragma unroll
+          for (int i = 0; i < kMaxProps; ++i) lav[lvl][i] = T(0);
+          continue;
+        }
+        // j == 0 can only happen inside a ghost frame here (J >= 1)
+        T prob = pf;
+        bool done = false;
+        for (;;) {
+          T ret;
+          bool returning;
+          if (t_bad(prob)) {
+            ret = T(0);
+            returning = true;
+          } else {
+            lav[lvl][lj[lvl]] = prob < T(1) ? prob : T(1);
+            T pr = T(1);
+            for (int i = 0; i < lm[lvl]; ++i) pr *= (T(1) - lav[lvl][i]);
+            if (pr == T(0) || lj[lvl] + 1 == lm[lvl]) { ret = pr; returning = true; }
+            else { lj[lvl] += 1; returning = false; }
+          }
+          if (!returning) break;
+          --lvl;
+          T den = T(1);
+          for (int i = 0; i < lj[lvl]; ++i) den *= (T(1) - lav[lvl][i]);
+          prob = lpf[lvl] * ret / den;
+          if (lvl == 0) { prob_top = prob; done = true; break; }
+        }
+        if (done) break;
+      }
+
+      // ---------------- DRHMC.step's accept test for stage J (src/algorithms.py:523-529)
+      if (t_bad(prob_top)) prob_top = T(0);
+      const T aJ = prob_top < T(1) ? prob_top : T(1);
+      const double u = draw_uniform<T>(a, chain, J);
+      const bool accept = u < (double)aJ;
+      const bool finished = accept || (J == a.nprops - 1);
+      if (c.lane == 0) {
+        if (finished) {
+          if (a.avec_out) {
+            for (int i = 0; i < a.nprops; ++i)
+              a.avec_out[chain * a.nprops + i] = (i < J) ? lav[0][i] : (i == J ? aJ : T(0));
+          }
+          if (a.code) a.code[chain] = accept ? J + 1 : 0;
+          if (a.counts) { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = cLeap; }
+        } else {
+          a.ws.avec[chain * kMaxProps + J] = aJ;
+          a.ws.counts[3 * chain] = cH; a.ws.counts[3 * chain + 1] = cVg; a.ws.counts[3 * chain + 2] = cLeap;
+          cg::coalesced_group g = cg::coalesced_threads();
+          int base = 0;
+          if (g.thread_rank() == 0) base = atomicAdd(a.ws.count + J + 1, (int)g.size());
+          base = g.shfl(base, 0);
+          a.ws.list[(int64_t)(J + 1) * a.n_chains + base + g.thread_rank()] = (int32_t)chain;
+        }
+      }
+      if (finished) {
+        if (accept) {
+          // the stage-J proposal was parked in frame 0
+          const T* fq = fr;
+#pragma unroll
+          for (int s = 0; s < EPL; ++s) { q[s] = fq[(int64_t)s * FT]; p[s] = fq[(int64_t)(EPL + s) * FT]; }
+          store_vec<T, EPL, LPC>(q, a.q_out, qoff, a.sd, c.lane, d);
+          if (a.p_out) store_vec<T, EPL, LPC>(p, a.p_out, qoff, a.sd, c.lane, d);
+        } else {
+          if (a.q_out != a.q_in) {
+#pragma unroll
+            for (int s = 0; s < EPL; ++s) {
+              const int i = Lay::elem(c.lane, s);
+              if (i < d) a.q_out[qoff + i * a.sd] = a.q_in[qoff + i * a.sd];
+            }
+          }
+          if (a.p_out) {
+            draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);
+            store_vec<T, EPL, LPC>(p, a.p_out, qoff, a.sd, c.lane, d);
+          }
+        }
+      }
+    }
+  }
+}
+
+}  // namespace hmcb

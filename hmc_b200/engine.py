@@ -1,0 +1,185 @@
+"""Host-side plumbing shared by the sampler classes: argument normalisation
+(numpy/torch, 1-D/batched), device buffers, and the calls into libhmcb.so.
+
+Chain state at this API is row-major ``[C, d]`` (the reference's batched shape
+precedent, src/pyhmc.py:604-684 and src/utils.py:232-235); kernels address it
+through (stride_chain, stride_dim), so no transposes are made.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from .models import as_model
+
+
+def _require_cuda(device):
+    if not torch.cuda.is_available():
+        raise _lib.HmcbError("hmc_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    if dev.type != "cuda":
+        raise _lib.HmcbError("hmc_b200 samplers run on CUDA devices only, got %r" % (device,))
+    if dev.index is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+    return dev
+
+
+class Batch:
+    """Remembers how the caller passed ``q`` so results go back the same way."""
+
+    def __init__(self, q, device, dtype):
+        self.was_numpy = isinstance(q, np.ndarray) or not torch.is_tensor(q)
+        t = torch.as_tensor(np.asarray(q)) if self.was_numpy else q
+        self.unbatched = t.dim() == 1
+        if self.unbatched:
+            t = t.unsqueeze(0)
+        if t.dim() != 2:
+            raise ValueError("q must be [d] or [C, d]")
+        self.q = t.to(device=device, dtype=dtype).contiguous()
+        self.C, self.d = self.q.shape
+
+    def out(self, t, per_chain=True):
+        """Give a per-chain device tensor back in the caller's convention."""
+        if t is None:
+            return None
+        if self.unbatched and per_chain:
+            t = t[0]
+        return t.cpu().numpy() if self.was_numpy else t
+
+
+class Engine:
+    """One model on one device: owns the hmcb_model block, the RNG position and
+    scratch buffers, and wraps each C-ABI entry point."""
+
+    def __init__(self, log_prob, grad_log_prob=None, log_prob_and_grad=None, invmetric_diag=None, device=None,
+                 dtype=torch.float64, seed=0, chain_offset=0, rng_f64=False):
+        self.model = as_model(log_prob, grad_log_prob, log_prob_and_grad)
+        if dtype not in (torch.float64, torch.float32):
+            raise ValueError("dtype must be torch.float64 or torch.float32")
+        self.dtype = dtype
+        self.invmetric_diag = invmetric_diag
+        self._device_arg = device
+        self.seed = int(seed)
+        self.chain_offset = int(chain_offset)
+        self.iteration = 0
+        self.rng_flags = _lib.RNG_NORMAL_F64 if rng_f64 else 0
+        self._struct = None
+        self._keep = None
+        self._ws = None
+        self.device = None
+
+    # ------------------------------------------------------------------ set-up
+    def _ensure(self):
+        if self._struct is None:
+            self.device = _require_cuda(self._device_arg)
+            self.lib = _lib.load()
+            self._struct, self._keep = self.model.to_struct(self.device, self.dtype, self.invmetric_diag)
+        return self._struct
+
+    @property
+    def dev(self):
+        self._ensure()
+        return self.device
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _chains(self, q_in, q_out):
+        c = _lib.Chains()
+        c.n_chains, c.chain_offset = q_in.shape[0], self.chain_offset
+        c.q_in, c.q_out = q_in.data_ptr(), q_out.data_ptr()
+        c.stride_chain, c.stride_dim = q_in.stride(0), q_in.stride(1)
+        return c
+
+    def _rng(self, p, u, nu, C_):
+        r = _lib.Rng()
+        r.seed, r.iteration, r.flags = self.seed, self.iteration, self.rng_flags
+        keep = []
+        if p is not None:
+            pt = torch.as_tensor(np.asarray(p)) if not torch.is_tensor(p) else p
+            pt = pt.reshape(C_, -1).to(device=self.device, dtype=self.dtype).contiguous()
+            keep.append(pt)
+            r.p_inject = pt.data_ptr()
+        if u is not None:
+            ut = torch.as_tensor(np.asarray(u, dtype=np.float64)) if not torch.is_tensor(u) else u
+            ut = ut.reshape(C_, -1).to(device=self.device, dtype=torch.float64).contiguous()
+            if ut.shape[1] < nu:
+                raise ValueError("u must hold %d uniforms per chain" % nu)
+            keep.append(ut)
+            r.u_inject, r.u_stride = ut.data_ptr(), ut.shape[1]
+        return r, keep
+
+    def check_dim(self, b):
+        if b.d != self.model.d:
+            raise ValueError("q has dimension %d but the model has d=%d" % (b.d, self.model.d))
+
+    # ------------------------------------------------------------------ calls
+    def hmc_step(self, q, n_leap, step_size, rule, p=None, u=None, want_p=True, want_prob=False, q_out=None):
+        """hmcb_hmc_step on device tensor q [C,d]; returns dict of device tensors."""
+        m = self._ensure()
+        C_ = q.shape[0]
+        with torch.cuda.device(self.device):
+            q_out = torch.empty_like(q) if q_out is None else q_out
+            out = {"q": q_out,
+                   "p": torch.empty_like(q) if want_p else None,
+                   "code": torch.empty(C_, dtype=torch.int32, device=self.device),
+                   "Hs": torch.empty((C_, 2), dtype=self.dtype, device=self.device),
+                   "counts": torch.empty((C_, 3), dtype=torch.int32, device=self.device),
+                   "prob": torch.empty(C_, dtype=self.dtype, device=self.device) if want_prob else None}
+            so = _lib.StepOut()
+            so.p_out, so.code, so.energies = _lib.ptr(out["p"]), _lib.ptr(out["code"]), _lib.ptr(out["Hs"])
+            so.counts, so.accept_prob = _lib.ptr(out["counts"]), _lib.ptr(out["prob"])
+            ch = self._chains(q, q_out)
+            r, keep = self._rng(p, u, 1, C_)
+            _lib.check(self.lib.hmcb_hmc_step(C.byref(m), C.byref(ch), C.byref(r), int(n_leap), float(step_size),
+                                              int(rule), C.byref(so), self._stream()))
+        self.iteration += 1
+        out["_keep"] = keep
+        return out
+
+    def drhmc_step(self, q, n_leap, step_size, nprops, stepfactor, p=None, u=None, want_p=True, q_out=None):
+        m = self._ensure()
+        C_ = q.shape[0]
+        with torch.cuda.device(self.device):
+            need = self.lib.hmcb_drhmc_workspace_bytes(C.byref(m), C_, int(nprops))
+            if need == 0:
+                _lib.check(_lib.E_ARG)
+            if self._ws is None or self._ws.numel() < need:
+                self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+            q_out = torch.empty_like(q) if q_out is None else q_out
+            out = {"q": q_out,
+                   "p": torch.empty_like(q) if want_p else None,
+                   "code": torch.empty(C_, dtype=torch.int32, device=self.device),
+                   "avec": torch.empty((C_, nprops), dtype=self.dtype, device=self.device),
+                   "counts": torch.empty((C_, 3), dtype=torch.int32, device=self.device)}
+            so = _lib.StepOut()
+            so.p_out, so.code, so.avec = _lib.ptr(out["p"]), _lib.ptr(out["code"]), _lib.ptr(out["avec"])
+            so.counts = _lib.ptr(out["counts"])
+            ch = self._chains(q, q_out)
+            r, keep = self._rng(p, u, nprops, C_)
+            _lib.check(self.lib.hmcb_drhmc_step(C.byref(m), C.byref(ch), C.byref(r), int(n_leap), float(step_size),
+                                                int(nprops), float(stepfactor), C.byref(so),
+                                                C.c_void_p(self._ws.data_ptr()), self._ws.numel(), self._stream()))
+        self.iteration += 1
+        out["_keep"] = keep
+        return out
+
+    def leapfrog(self, q, p, n_leap, step_size):
+        m = self._ensure()
+        with torch.cuda.device(self.device):
+            q1, p1 = torch.empty_like(q), torch.empty_like(p)
+            ch = self._chains(q, q1)
+            _lib.check(self.lib.hmcb_leapfrog(C.byref(m), C.byref(ch), _lib.ptr(p), _lib.ptr(p1), int(n_leap),
+                                              float(step_size), self._stream()))
+        return q1, p1
+
+    def logp_grad(self, q):
+        m = self._ensure()
+        with torch.cuda.device(self.device):
+            logp = torch.empty(q.shape[0], dtype=self.dtype, device=self.device)
+            grad = torch.empty_like(q)
+            ch = self._chains(q, q)
+            _lib.check(self.lib.hmcb_logp_grad(C.byref(m), C.byref(ch), _lib.ptr(logp), _lib.ptr(grad),
+                                               self._stream()))
+        return logp, grad

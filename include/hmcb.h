@@ -1,0 +1,137 @@
+/* hmcb.h -- C ABI of libhmcb.so, the B200 (sm_100a) batched-chain HMC engine.
+ *
+ * Drop-in boundary for the sampler hot path of modichirag/hmc.  The reference is
+ * pure Python, so there is no FFI in it to bind; each entry point below replaces
+ * the per-chain Python call named in its comment (path:line under the reference
+ * tree) with ONE call over a whole batch of chains.  hmc_b200/_lib.py is the
+ * ctypes binding; INTEGRATION.md shows the stub a reference maintainer would add.
+ *
+ * Conventions
+ *  - Plain pointers and sizes only.  Every buffer is DEVICE memory owned by the
+ *    caller; the library allocates nothing and keeps no state between calls
+ *    besides a thread-local error string.
+ *  - All work is enqueued on `stream` (a cudaStream_t passed as void*); no call
+ *    synchronises the host.  Errors detected at launch are returned.
+ *  - Return value: 0 on success, a negative HMCB_E_* on failure;
+ *    hmcb_last_error() then describes it.
+ *  - Chain state is addressed as base[chain*stride_chain + dim*stride_dim]
+ *    (strides in elements): (d,1) is the row-major [C,d] the Python API takes,
+ *    (1,C) is the structure-of-arrays [d][C] the samplers keep between steps.
+ *  - Element type of q, p, energies and probabilities is model->dtype.
+ */
+#ifndef HMCB_H_
+#define HMCB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HMCB_VERSION 1
+
+enum { HMCB_OK = 0, HMCB_E_ARG = -1, HMCB_E_UNSUPPORTED = -2, HMCB_E_CUDA = -3, HMCB_E_WORKSPACE = -4 };
+
+enum { HMCB_F64 = 0, HMCB_F32 = 1 };
+
+/* Model densities with in-kernel analytic gradients.
+ * They stand where the reference takes log_prob/grad_log_prob callables
+ * (src/algorithms.py:81-89, src/pyhmc.py:7-10). */
+enum { HMCB_MODEL_FUNNEL = 0, HMCB_MODEL_GAUSSIAN = 1, HMCB_MODEL_ROSENBROCK = 2, HMCB_MODEL_LOGISTIC = 3 };
+
+typedef struct hmcb_model {
+  int32_t kind;               /* HMCB_MODEL_* */
+  int32_t d;                  /* dimension of one chain */
+  int32_t dtype;              /* HMCB_F64 / HMCB_F32 */
+  int32_t n_data;             /* logistic: rows of X; else 0 */
+  double par[4];              /* funnel: {sigma}; rosenbrock: {a, b, T}; logistic: {tau} */
+  const void* dev0;           /* gaussian: precision P[d*d] row-major (dtype); logistic: X[n_data*d] */
+  const void* dev1;           /* logistic: y[n_data] */
+  const void* invmetric_diag; /* [d] (dtype) or NULL for the unit metric (src/pyhmc.py:14-19) */
+} hmcb_model;
+
+typedef struct hmcb_chains {
+  int64_t n_chains;
+  int64_t chain_offset;       /* global id of chain 0; keys the RNG so results do not depend on sharding */
+  const void* q_in;           /* current positions */
+  void* q_out;                /* next positions; may equal q_in */
+  int64_t stride_chain;       /* element strides of q_in, q_out, p_out, p_inject */
+  int64_t stride_dim;
+} hmcb_chains;
+
+/* Random draws.  Production: Philox4x32-10 keyed by `seed`, counter = (global
+ * chain id, iteration, stream, block).  Parity ("replay") mode: p_inject and/or
+ * u_inject non-NULL feed the draws the reference would have taken from
+ * np.random.normal / np.random.uniform (src/pyhmc.py:66,59). */
+enum { HMCB_RNG_NORMAL_F64 = 1 };  /* flags: Box-Muller evaluated in f64 instead of f32 */
+typedef struct hmcb_rng {
+  uint64_t seed;
+  uint64_t iteration;
+  const void* p_inject;       /* standard normals, same layout as q (dtype), or NULL */
+  const double* u_inject;     /* uniforms [n_chains, u_stride] or NULL */
+  int32_t u_stride;
+  int32_t flags;
+} hmcb_rng;
+
+/* Per-chain outputs of one transition.  Any pointer may be NULL (not written). */
+typedef struct hmcb_step_out {
+  void* p_out;                /* momentum returned by the step (p1 if accepted else p0), layout of q */
+  int32_t* code;              /* [C] accept code, convention per `rule` */
+  void* energies;             /* [C,2] H0,H1 (hmc) */
+  void* avec;                 /* [C,nprops] stage acceptance probabilities (drhmc) */
+  int32_t* counts;            /* [C,3] Hcount, Vgcount, leapcount (src/pyhmc.py:69) */
+  void* accept_prob;          /* [C] min(1, exp(H0-H1)) with NaN->0, 0 if q did not move
+                                 (what src/algorithms.py:218-224 feeds dual averaging) */
+} hmcb_step_out;
+
+/* Accept-rule conventions:
+ *  PYHMC: codes 1/0/2, uniform consumed only if prob finite and q moved, reject iff u > min(1,prob)
+ *         (src/pyhmc.py:50-61; same in src/adaptivehmc.py:63-74)
+ *  ALG:   codes 1/0/-1, uniform always consumed (src/algorithms.py:175-189) */
+enum { HMCB_RULE_PYHMC = 0, HMCB_RULE_ALG = 1 };
+
+int hmcb_version(void);
+const char* hmcb_last_error(void);
+
+/* One vanilla HMC transition for every chain: momentum draw, n_leap leapfrog
+ * steps (n_leap+1 gradient evaluations), H0/H1, accept test, counters -- one
+ * fused kernel.  Replaces pyhmc.HMC.step / PyHMC.hmc_step (src/pyhmc.py:64-69,
+ * 133-138), algorithms.HMC.step (src/algorithms.py:192-198) and
+ * adaptivehmc.HMC.hmc_step (src/adaptivehmc.py:77-99) called once per chain. */
+int hmcb_hmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng,
+                  int32_t n_leap, double step_size, int32_t rule, const hmcb_step_out* out, void* stream);
+
+/* Leapfrog only: (q,p) -> (q',p') for every chain.  Replaces HMC.leapfrog
+ * (src/pyhmc.py:35-48, src/algorithms.py:133-147).  p_in/p_out use the q layout. */
+int hmcb_leapfrog(const hmcb_model* model, const hmcb_chains* chains, const void* p_in, void* p_out,
+                  int32_t n_leap, double step_size, void* stream);
+
+/* log_prob and grad_log_prob of every chain (model plug-in check; mirrors the
+ * callables at src/algorithms.py:81-89).  logp [C], grad in the q layout. */
+int hmcb_logp_grad(const hmcb_model* model, const hmcb_chains* chains, void* logp, void* grad, void* stream);
+
+/* Delayed-rejection HMC transition, algorithms.DRHMC.step (src/algorithms.py:
+ * 500-530) with its ghost recursion get_num (:474-497).  Stage j integrates
+ * int(n_leap*stepfactor^j) steps of size step_size/stepfactor^j from (q0,p0);
+ * chains rejected at stage j are compacted on the device and only they run
+ * stage j+1.  code = j+1 (accepted at stage j) or 0.  `workspace` is caller-
+ * owned scratch of at least hmcb_drhmc_workspace_bytes(); contents need not be
+ * preserved between calls. */
+size_t hmcb_drhmc_workspace_bytes(const hmcb_model* model, int64_t n_chains, int32_t nprops);
+int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng,
+                    int32_t n_leap, double step_size, int32_t nprops, double stepfactor,
+                    const hmcb_step_out* out, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Measurement probe: a register-resident dependent-FMA loop (FP64 or FP32) used
+ * to measure the pipe peak that roofline fractions are quoted against.
+ * Launches `blocks` x `threads`, each thread doing iters*ilp*unroll FMAs; writes
+ * one value per thread to `sink` (>= blocks*threads elements of dtype).  Returns
+ * the FMA count of the launch through *fma_count. */
+int hmcb_probe_fma(int32_t dtype, int32_t blocks, int32_t threads, int64_t iters, void* sink,
+                   double* fma_count, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HMCB_H_ */

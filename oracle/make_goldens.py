@@ -1,0 +1,99 @@
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference classes
+(/root/reference/src, imported via oracle/ref_loader.py) on replayed draws.
+
+Run in the build container only:  python -m oracle.make_goldens
+Each file stores the inputs (model parameters, q0, normal draws P[T,C,d], uniform
+draws U[T,C,nu], sampler arguments) and what the reference returned for every
+(transition, chain).  The GPU box checks against these without the reference tree.
+"""
+import contextlib
+import io
+import json
+import os
+
+import numpy as np
+
+from . import models, ref_loader, replay
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def build_model(spec):
+    kind = spec["kind"]
+    if kind == "funnel":
+        return models.Funnel(spec["d"], spec.get("sigma", 3.0))
+    if kind == "rosenbrock":
+        return models.Rosenbrock(spec["d"], spec.get("a", 1.0), spec.get("b", 100.0), spec.get("T", 20.0))
+    if kind == "gaussian":
+        return models.CorrGaussian.ar1(spec["d"], spec.get("rho", 0.9))
+    raise ValueError(kind)
+
+
+CASES = [
+    dict(name="hmc_funnel10", cls="pyhmc.HMC", model=dict(kind="funnel", d=10), C=8, T=5, seed=101,
+         args=dict(N=20, step_size=0.1), nu=1),
+    dict(name="hmc_funnel50_metric", cls="pyhmc.PyHMC", model=dict(kind="funnel", d=50), C=6, T=4, seed=102,
+         args=dict(N=15, step_size=0.08), nu=1, metric=True),
+    dict(name="alghmc_rosen8", cls="algorithms.HMC", model=dict(kind="rosenbrock", d=8), C=8, T=5, seed=103,
+         args=dict(N=12, step_size=0.03), nu=1),
+    dict(name="alghmc_gauss12", cls="algorithms.HMC", model=dict(kind="gaussian", d=12), C=8, T=4, seed=104,
+         args=dict(N=10, step_size=0.15), nu=1),
+    dict(name="drhmc_funnel50", cls="algorithms.DRHMC", model=dict(kind="funnel", d=50), C=24, T=4, seed=105,
+         args=dict(nleap=10, step_size=0.4, nprops=3, stepfactor=2), nu=3),
+    dict(name="drhmc_funnel10_np4", cls="algorithms.DRHMC", model=dict(kind="funnel", d=10), C=16, T=4, seed=106,
+         args=dict(nleap=6, step_size=0.7, nprops=4, stepfactor=1.5), nu=4),
+    dict(name="drhmc_rosen6", cls="algorithms.DRHMC", model=dict(kind="rosenbrock", d=6), C=16, T=4, seed=107,
+         args=dict(nleap=8, step_size=0.12, nprops=3, stepfactor=2), nu=3),
+]
+
+
+def run_case(case):
+    modname, clsname = case["cls"].split(".")
+    mod = ref_loader.load(modname)
+    model = build_model(case["model"])
+    d, C, T = model.d, case["C"], case["T"]
+    inv = np.linspace(0.5, 2.0, d) if case.get("metric") else None
+    P, U = replay.make_draws(case["seed"], T, C, d, case["nu"])
+    q0 = np.random.default_rng(case["seed"] + 1000).uniform(-1, 1, (C, d))
+    if case["model"]["kind"] == "rosenbrock":
+        q0 = 1.0 + 0.1 * q0
+    cls = getattr(mod, clsname)
+    if modname == "algorithms":
+        ref = cls(model.log_prob, model.grad_log_prob, invmetric_diag=inv)
+    else:
+        ref = cls(model.log_prob, model.grad_log_prob, invmetric_diag=inv)
+    a = case["args"]
+    is_dr = clsname == "DRHMC"
+    q = np.zeros((T, C, d)); p = np.zeros((T, C, d)); code = np.zeros((T, C)); counts = np.zeros((T, C, 3), dtype=np.int64)
+    aux = np.zeros((T, C, a["nprops"] if is_dr else 2))
+    sink = io.StringIO()
+    with np.errstate(all="ignore"), contextlib.redirect_stdout(sink):
+        for c in range(C):
+            qc = q0[c]
+            for t in range(T):
+                with replay.patched_numpy_random(replay.Draws([P[t, c]], U[t, c])):
+                    if is_dr:
+                        out = ref.step(qc, a["nleap"], a["step_size"], a["nprops"], a["stepfactor"])
+                    elif clsname == "PyHMC":
+                        out = ref.hmc_step(qc, a["N"], a["step_size"])
+                    else:
+                        out = ref.step(qc, a["N"], a["step_size"])
+                qc = out[0]
+                q[t, c], p[t, c], code[t, c], aux[t, c], counts[t, c] = out[0], out[1], out[2], out[3], out[4]
+    np.savez_compressed(os.path.join(OUT, case["name"] + ".npz"), spec=json.dumps(case), q0=q0, P=P, U=U,
+                        invmetric=np.zeros(0) if inv is None else inv, q=q, p=p, code=code, aux=aux, counts=counts)
+    return code
+
+
+def main():
+    assert ref_loader.available(), "the reference tree is needed to make goldens"
+    os.makedirs(OUT, exist_ok=True)
+    for case in CASES:
+        code = run_case(case)
+        vals, n = np.unique(code, return_counts=True)
+        print("%-24s codes %s" % (case["name"], dict(zip(vals.tolist(), n.tolist()))))
+
+
+if __name__ == "__main__":
+    main()
