@@ -1,0 +1,365 @@
+#!/usr/bin/env python
+"""Benchmark of the sampler hot path on the BASELINE.json headline workload:
+Neal's funnel d=50, delayed-rejection HMC (nleap=150, step 0.2 -> lpath 30 as
+scripts_old/jobscripts/run_funnel2.sh:21-22; nprops=3, stepfactor=2), 2^20 chains
+sharded over N GPUs (strong scaling: the chain count is fixed by the config).
+
+A "step" is one DRHMC transition of every chain.  Prints ONE JSON line.
+  value  : gradient evaluations/s (the reference's Vgcount counter, src/pyhmc.py:21-23),
+           chain state resident in HBM
+  e2e    : same metric through the public API with HOST (pinned) buffers, copies timed
+  roofline / cpu_baseline / clocks: see DESIGN.md "Measurement"
+`--impl reference` times the CPU path (the numpy oracle port of the reference's
+DRHMC.step; the reference itself cannot travel to the GPU box) on all host cores.
+"""
+import argparse
+import json
+import multiprocessing as mp
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FLOPS_PER_GRAD = {"funnel": lambda d: 7 * d}  # 7d flops + 1 exp per gradient evaluation
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="hmcb", choices=["hmcb", "reference"])
+    ap.add_argument("--chains", type=int, default=1 << 20)
+    ap.add_argument("--ndim", type=int, default=50)
+    ap.add_argument("--nleap", type=int, default=150)
+    ap.add_argument("--step_size", type=float, default=0.2)
+    ap.add_argument("--nprops", type=int, default=3)
+    ap.add_argument("--stepfactor", type=float, default=2.0)
+    ap.add_argument("--burnin", type=int, default=30)
+    ap.add_argument("--seed", type=int, default=2)
+    ap.add_argument("--cpu_seconds", type=float, default=12.0)
+    ap.add_argument("--no_cpu_baseline", action="store_true")
+    ap.add_argument("--no_e2e", action="store_true")
+    ap.add_argument("--e2e_steps", type=int, default=0)
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------ CPU arm (oracle port on the host cores)
+_W = {}
+
+
+def _cpu_init(d, seed, chains_per_proc, nleap, eps, nprops, f):
+    os.environ["OMP_NUM_THREADS"] = "1"
+    from oracle import models as om
+    ident = mp.current_process()._identity
+    wid = ident[0] if ident else 0
+    rng = np.random.Generator(np.random.PCG64(seed * 1000 + wid))
+    _W.update(model=om.Funnel(d), rng=rng, q=rng.uniform(-1, 1, (chains_per_proc, d)),
+              args=(nleap, eps, nprops, f))
+
+
+def _cpu_step(n_chains):
+    """Advance this worker's first n_chains chains by one DRHMC transition."""
+    from oracle import samplers
+
+    class R:  # the reference draws from numpy's global generator; here a per-worker one
+        normal = staticmethod(lambda size=None: _W["rng"].standard_normal(size))
+        uniform = staticmethod(lambda low=0.0, high=1.0, size=None: _W["rng"].uniform(low, high, size))
+
+    nleap, eps, nprops, f = _W["args"]
+    grads = leaps = 0
+    for c in range(n_chains):
+        q, p, code, avec, cnt = samplers.drhmc_step(_W["model"], _W["q"][c], nleap, eps, nprops, f, R)
+        _W["q"][c] = q
+        grads += cnt[1]
+        leaps += cnt[2]
+    return grads, leaps
+
+
+class CpuArm:
+    def __init__(self, a, chains_per_proc):
+        self.P = os.cpu_count() or 1
+        self.m = chains_per_proc
+        ctx = mp.get_context("fork")
+        self.pool = ctx.Pool(self.P, initializer=_cpu_init,
+                             initargs=(a.ndim, a.seed, chains_per_proc, a.nleap, a.step_size, a.nprops, a.stepfactor))
+
+    def step(self, n_chains=None):
+        n = self.m if n_chains is None else n_chains
+        res = self.pool.map(_cpu_step, [n] * self.P)
+        return sum(r[0] for r in res), sum(r[1] for r in res)
+
+    def close(self):
+        self.pool.close()
+        self.pool.join()
+
+
+def cpu_baseline(a, seconds):
+    """Bounded sample: every host core runs its own chains (one chain per process at a
+    time, as the reference's one-chain-per-MPI-rank layout, scripts_old/jobscripts/
+    run_funnel2.sh:16,42) for about `seconds` of wall time."""
+    arm = CpuArm(a, 64)
+    t0 = time.time()
+    g, _ = arm.step(1)                      # calibrate (also warms the workers)
+    per_chain = max(time.time() - t0, 1e-3)
+    n = int(max(1, min(64, seconds / per_chain)))
+    t0 = time.time()
+    grads, leaps = arm.step(n)
+    dt = time.time() - t0
+    arm.close()
+    return {"value": grads / dt, "unit": "grad_evals/s", "cores": arm.P, "kind": "port",
+            "sample": "%d chains x 1 DRHMC transition on each of %d processes (oracle/samplers.py drhmc_step, numpy), "
+                      "%.1f s wall" % (n, arm.P, dt),
+            "leapfrog_steps_per_s": (grads - leaps) / dt}
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    m = 16
+    arm = CpuArm(a, m)
+    for _ in range(max(a.warmup, 1)):
+        arm.step(2)
+    t0 = time.time()
+    grads = leaps = 0
+    for _ in range(a.steps):
+        g, l = arm.step(m)
+        grads += g
+        leaps += l
+    dt = time.time() - t0
+    arm.close()
+    val = grads / dt
+    line = {"impl": "reference", "metric": "grad_evals_per_sec", "value": val, "unit": "grad_evals/s",
+            "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * dt / a.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(a, sample="each step = %d chains x %d processes x 1 transition" % (m, arm.P)),
+            "cpu_baseline": {"value": val, "unit": "grad_evals/s", "cores": arm.P, "kind": "port",
+                             "sample": "%d steps of %d chain-transitions on %d processes" % (a.steps, m * arm.P, arm.P)},
+            "e2e": {"value": val, "unit": "grad_evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "leapfrog_steps_per_sec": (grads - leaps) / dt, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(a, **extra):
+    cfg = {"workload": "funnel d=%d sigma=3, DRHMC nleap=%d step_size=%g nprops=%d stepfactor=%g, %d chains total, "
+                       "q0~U(-1,1), %d burn-in transitions before timing" %
+                       (a.ndim, a.nleap, a.step_size, a.nprops, a.stepfactor, a.chains, a.burnin),
+           "chains": a.chains, "d": a.ndim, "cache": "inputs larger than L2 (q is %.0f MB per rank at N=1)" %
+                                                    (a.chains * a.ndim * 8 / 1e6)}
+    cfg.update(extra)
+    return cfg
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler(threading.Thread):
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.proc = index, [], None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+
+    def summary(self, t0, t1):
+        rows = [r for t, r in self.rows if t0 <= t <= t1 and len(r) >= 7] or [r for _, r in self.rows if len(r) >= 7]
+        if not rows:
+            return None
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in rows)]
+        sm = sorted(float(r[0]) for r in rows)
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "reasons": reasons,
+                "power_w_max": max(float(r[2]) for r in rows), "samples": len(rows)}
+
+
+# ------------------------------------------------------------------ GPU arm
+def run_hmcb(a):
+    import torch
+
+    from hmc_b200 import _lib, algorithms, dist, models, utils
+
+    rank, world, local = dist.init_from_env()
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    lo, hi = dist.shard_range(a.chains)
+    C, d = hi - lo, a.ndim
+
+    model = models.Funnel(d)
+    dr = algorithms.DRHMC(model, device=dev, seed=a.seed, chain_offset=lo)
+    eng = dr.engine
+    eng._ensure()
+    g = torch.Generator().manual_seed(a.seed)
+    q = (torch.rand(a.chains, d, generator=g, dtype=torch.float64) * 2 - 1)[lo:hi].to(dev).contiguous()
+    nxt = torch.empty_like(q)
+
+    def transition(qi, qo, events=None):
+        return eng.drhmc_step(qi, a.nleap, a.step_size, a.nprops, a.stepfactor, want_p=False, q_out=qo,
+                              stage_events=events, want_avec=False)
+
+    for _ in range(a.burnin):
+        transition(q, nxt)
+        q, nxt = nxt, q
+    mom = utils.RunningMoments(eng, C, d)
+
+    # FP64 pipe peak of this GPU, measured now (MEASURED_PEAKS.json carries only HBM and bf16 numbers)
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    sink = torch.empty(sms * 8 * 256, dtype=torch.float64, device=dev)
+    cnt = _lib.C.c_double(0)
+    best = 0.0
+    for it in range(4):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _lib.check(eng.lib.hmcb_probe_fma(_lib.F64, sms * 8, 256, 4000, _lib.ptr(sink), _lib.C.byref(cnt), eng._stream()))
+        e1.record()
+        torch.cuda.synchronize()
+        if it:
+            best = max(best, 2.0 * cnt.value / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+    fp64_peak_tflops = best
+
+    for _ in range(a.warmup):
+        out = transition(q, nxt)
+        q, nxt = nxt, q
+        mom.add(q)
+    mom.reset()
+
+    clocks = ClockSampler(local)
+    clocks.start()
+    time.sleep(0.3)
+    K = a.steps
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(a.nprops + 1)] for _ in range(K)]
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    counts_log, code_log = [], []
+    dist.barrier()
+    torch.cuda.synchronize()
+    t_wall0 = time.time()
+    start.record()
+    for k in range(K):
+        out = transition(q, nxt, evs[k])
+        q, nxt = nxt, q
+        mom.add(q)
+        counts_log.append(out["counts"])
+        code_log.append(out["code"])
+    end.record()
+    torch.cuda.synchronize()
+    dist.barrier()
+    t_wall1 = time.time()
+    ms = torch.tensor([start.elapsed_time(end)], dtype=torch.float64, device=dev)
+    if world > 1:
+        torch.distributed.all_reduce(ms, op=torch.distributed.ReduceOp.MAX)
+    ms_total = float(ms[0])
+    clocks.stop()
+
+    tot = torch.zeros(3, dtype=torch.float64, device=dev)
+    for c in counts_log:
+        tot += c.sum(dim=0, dtype=torch.float64)
+    stage_ms = torch.tensor([[evs[k][j].elapsed_time(evs[k][j + 1]) for j in range(a.nprops)] for k in range(K)],
+                            dtype=torch.float64, device=dev)
+    n_stage1 = torch.stack([(c != 1).sum() for c in code_log]).double().mean()
+    acc_rate = torch.stack([(c > 0).double().mean() for c in code_log]).mean()
+    stats = torch.cat([tot, stage_ms.mean(dim=0), n_stage1[None], acc_rate[None] * C])
+    dist.all_reduce_sum(stats[:3])
+    dist.all_reduce_sum(stats[-1:])
+    grads, leaps = float(stats[1]), float(stats[2])
+    sec = ms_total * 1e-3
+    value = grads / sec
+    fpg = FLOPS_PER_GRAD["funnel"](d)
+
+    # ESS over the timed transitions from streamed per-chain means (utils.get_ess_true), all ranks
+    ess = mom.ess_true(model.true_mean(), model.true_std())
+    rhat = mom.rhat()
+    mean, std = mom.mean_std()
+    ess_min = float(ess.min())
+
+    # roofline of the dominant kernel: DR stage 0 (every chain integrates nleap steps)
+    L0 = max(a.nleap, 1)
+    st_ms = stats[3:3 + a.nprops].tolist()
+    s0_flops = C * (L0 + 1) * fpg
+    achieved = s0_flops / (st_ms[0] * 1e-3) / 1e12
+    roofline = {"bound": "fp64", "kernel": "k_transition<Funnel,f64,MODE_DR0> (DR stage 0)",
+                "achieved": achieved, "peak": fp64_peak_tflops, "unit": "TFLOP/s",
+                "frac": achieved / fp64_peak_tflops if fp64_peak_tflops else None, "traffic": None,
+                "peak_source": "hmcb_probe_fma: register-resident DFMA loop measured in this run on this GPU "
+                               "(MEASURED_PEAKS.json has no FP64 figure)",
+                "algorithmic_flops_per_launch": s0_flops, "avg_launch_ms": st_ms[0],
+                "stage_ms": st_ms, "step_frac_all_stages": grads / world * fpg / sec / 1e12 / fp64_peak_tflops}
+
+    # end to end: public API, pinned host buffers in, host results out, every step
+    e2e = None
+    if not a.no_e2e:
+        Ke = a.e2e_steps or max(3, min(K, 8))
+        qh = torch.empty((C, d), dtype=torch.float64).pin_memory()
+        qh.copy_(q)
+        dr_e = algorithms.DRHMC(model, device=dev, seed=a.seed + 1, chain_offset=lo)
+        for _ in range(2):
+            r = dr_e.step(qh, a.nleap, a.step_size, a.nprops, a.stepfactor)
+            qh = r[0]
+        dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.time()
+        g_e2e = 0
+        for _ in range(Ke):
+            r = dr_e.step(qh, a.nleap, a.step_size, a.nprops, a.stepfactor)
+            qh = r[0]
+            g_e2e += int(r[4][:, 1].sum())
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.time() - t0], dtype=torch.float64, device=dev)
+        ge = torch.tensor([float(g_e2e)], dtype=torch.float64, device=dev)
+        if world > 1:
+            torch.distributed.all_reduce(dt, op=torch.distributed.ReduceOp.MAX)
+            dist.all_reduce_sum(ge)
+        h2d = C * d * 8
+        d2h = C * d * 8 * 2 + C * 4 + C * a.nprops * 8 + C * 12
+        e2e = {"value": float(ge[0]) / float(dt[0]), "unit": "grad_evals/s", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "steps": Ke, "ms_per_step": 1e3 * float(dt[0]) / Ke,
+               "api": "hmc_b200.algorithms.DRHMC.step(q_pinned_host, ...) -> host (q, p, code, avec, counts)"}
+
+    if rank != 0:
+        return
+    cpu = None
+    if not a.no_cpu_baseline and world == 1:
+        cpu = cpu_baseline(a, a.cpu_seconds)
+    line = {"metric": "grad_evals_per_sec", "value": value, "unit": "grad_evals/s", "n_gpus": world, "steps": K,
+            "warmup": a.warmup, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(a),
+            "leapfrog_steps_per_sec": (grads - leaps) / sec,
+            "ess_per_sec": ess_min / sec, "ess_min": ess_min, "ess_note": "min over dims of utils.get_ess_true over the "
+            "%d timed transitions of all chains (analytic funnel mean/std); chains started at U(-1,1), so it includes "
+            "remaining burn-in bias" % K,
+            "grad_evals_per_transition": grads / (K * a.chains), "accept_rate": float(stats[-1]) / a.chains,
+            "rhat_max": float(rhat.max()), "v_mean": float(mean[0]), "v_std": float(std[0]),
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks.summary(t_wall0, t_wall1),
+            "gpu_launches": K * (a.nprops + 1),
+            "gpu_launches_note": "per step: %d DR stage kernels + 1 moments kernel (all libhmcb.so)" % a.nprops}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_hmcb(a)
+
+
+if __name__ == "__main__":
+    main()

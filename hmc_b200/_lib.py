@@ -29,6 +29,10 @@ class Rng(C.Structure):
                 ("u_stride", C.c_int32), ("flags", C.c_int32)]
 
 
+class Profile(C.Structure):
+    _fields_ = [("events", C.c_void_p * (MAX_PROPS + 1))]
+
+
 class StepOut(C.Structure):
     _fields_ = [("p_out", C.c_void_p), ("code", C.c_void_p), ("energies", C.c_void_p), ("avec", C.c_void_p),
                 ("counts", C.c_void_p), ("accept_prob", C.c_void_p)]
@@ -45,7 +49,12 @@ SIGNATURES = {
     "hmcb_logp_grad": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.c_void_p, C.c_void_p, C.c_void_p]),
     "hmcb_drhmc_workspace_bytes": (C.c_size_t, [C.POINTER(Model), C.c_int64, C.c_int32]),
     "hmcb_drhmc_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
-                                  C.c_int32, C.c_double, C.POINTER(StepOut), C.c_void_p, C.c_size_t, C.c_void_p]),
+                                  C.c_int32, C.c_double, C.POINTER(StepOut), C.c_void_p, C.c_size_t,
+                                  C.POINTER(Profile), C.c_void_p]),
+    "hmcb_moments_accumulate": (C.c_int, [C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_int64, C.c_int64,
+                                          C.c_void_p, C.c_void_p, C.c_void_p]),
+    "hmcb_moments_reduce": (C.c_int, [C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_double,
+                                      C.c_void_p, C.c_void_p, C.c_void_p]),
     "hmcb_probe_fma": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.POINTER(C.c_double),
                                  C.c_void_p]),
 }

@@ -188,7 +188,7 @@ static int dr_layout(const Entry* e, const hmcb_model* m, int64_t n_chains, int 
 template <typename T>
 static int drhmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r, int n_leap,
                         double eps, int nprops, double stepfactor, const hmcb_step_out* o, void* ws,
-                        const DrLayout& L, cudaStream_t st) {
+                        const DrLayout& L, const hmcb_profile* prof, cudaStream_t st) {
   TransArgs<T> a;
   fill_args(a, m, c, r, o);
   a.nprops = nprops;
@@ -208,10 +208,13 @@ static int drhmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* 
   a.ws.frame_threads = L.frame_threads;
   if (nprops > 1) HMCB_CUDA(cudaMemsetAsync(a.ws.count, 0, (kMaxProps + 2) * sizeof(int32_t), st));
   a.stage = 0;
+  if (prof && prof->events[0]) HMCB_CUDA(cudaEventRecord((cudaEvent_t)prof->events[0], st));
   int rc = e->fn(*m, OP_DR0, &a, st);
+  if (prof && prof->events[1] && rc == 0) HMCB_CUDA(cudaEventRecord((cudaEvent_t)prof->events[1], st));
   for (int j = 1; j < nprops && rc == 0; ++j) {
     a.stage = j;
     rc = e->fn(*m, OP_DRN, &a, st);
+    if (prof && prof->events[j + 1] && rc == 0) HMCB_CUDA(cudaEventRecord((cudaEvent_t)prof->events[j + 1], st));
   }
   return rc;
 }
@@ -300,7 +303,7 @@ size_t hmcb_drhmc_workspace_bytes(const hmcb_model* model, int64_t n_chains, int
 
 int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
                     double step_size, int32_t nprops, double stepfactor, const hmcb_step_out* out, void* workspace,
-                    size_t workspace_bytes, void* stream) {
+                    size_t workspace_bytes, const hmcb_profile* profile, void* stream) {
   int rc;
   if ((rc = check_model(model))) return rc;
   if ((rc = check_chains(chains))) return rc;
@@ -320,8 +323,8 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
   }
   cudaStream_t st = (cudaStream_t)stream;
   if (model->dtype == HMCB_F64)
-    return drhmc_step_t<double>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, out, workspace, L, st);
-  return drhmc_step_t<float>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, out, workspace, L, st);
+    return drhmc_step_t<double>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, out, workspace, L, profile, st);
+  return drhmc_step_t<float>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, out, workspace, L, profile, st);
 }
 
 }  // extern "C"

@@ -26,17 +26,20 @@ def _require_cuda(device):
 
 
 class Batch:
-    """Remembers how the caller passed ``q`` so results go back the same way."""
+    """Remembers how the caller passed ``q`` so results go back the same way:
+    numpy in -> numpy out; CPU torch tensor in (pinned or not) -> pinned CPU torch
+    tensors out; CUDA tensor in -> CUDA tensors out (no copies)."""
 
     def __init__(self, q, device, dtype):
         self.was_numpy = isinstance(q, np.ndarray) or not torch.is_tensor(q)
         t = torch.as_tensor(np.asarray(q)) if self.was_numpy else q
+        self.host = (not self.was_numpy) and t.device.type == "cpu"
         self.unbatched = t.dim() == 1
         if self.unbatched:
             t = t.unsqueeze(0)
         if t.dim() != 2:
             raise ValueError("q must be [d] or [C, d]")
-        self.q = t.to(device=device, dtype=dtype).contiguous()
+        self.q = t.to(device=device, dtype=dtype, non_blocking=True).contiguous()
         self.C, self.d = self.q.shape
 
     def out(self, t, per_chain=True):
@@ -45,7 +48,14 @@ class Batch:
             return None
         if self.unbatched and per_chain:
             t = t[0]
-        return t.cpu().numpy() if self.was_numpy else t
+        if self.was_numpy:
+            return t.cpu().numpy()
+        if self.host:
+            # pinned staging from torch's caching host allocator; copy_ synchronises
+            buf = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+            buf.copy_(t)
+            return buf
+        return t
 
 
 class Engine:
@@ -138,7 +148,8 @@ class Engine:
         out["_keep"] = keep
         return out
 
-    def drhmc_step(self, q, n_leap, step_size, nprops, stepfactor, p=None, u=None, want_p=True, q_out=None):
+    def drhmc_step(self, q, n_leap, step_size, nprops, stepfactor, p=None, u=None, want_p=True, q_out=None,
+                   stage_events=None, want_avec=True):
         m = self._ensure()
         C_ = q.shape[0]
         with torch.cuda.device(self.device):
@@ -151,7 +162,7 @@ class Engine:
             out = {"q": q_out,
                    "p": torch.empty_like(q) if want_p else None,
                    "code": torch.empty(C_, dtype=torch.int32, device=self.device),
-                   "avec": torch.empty((C_, nprops), dtype=self.dtype, device=self.device),
+                   "avec": torch.empty((C_, nprops), dtype=self.dtype, device=self.device) if want_avec else None,
                    "counts": torch.empty((C_, 3), dtype=torch.int32, device=self.device)}
             so = _lib.StepOut()
             so.p_out, so.code, so.avec = _lib.ptr(out["p"]), _lib.ptr(out["code"]), _lib.ptr(out["avec"])
@@ -160,9 +171,41 @@ class Engine:
             r, keep = self._rng(p, u, nprops, C_)
             _lib.check(self.lib.hmcb_drhmc_step(C.byref(m), C.byref(ch), C.byref(r), int(n_leap), float(step_size),
                                                 int(nprops), float(stepfactor), C.byref(so),
-                                                C.c_void_p(self._ws.data_ptr()), self._ws.numel(), self._stream()))
+                                                C.c_void_p(self._ws.data_ptr()), self._ws.numel(),
+                                                self._profile(stage_events), self._stream()))
         self.iteration += 1
         out["_keep"] = keep
+        return out
+
+    @staticmethod
+    def _profile(stage_events):
+        """torch.cuda.Event list (enable_timing=True) -> hmcb_profile, or NULL."""
+        if not stage_events:
+            return None
+        prof = _lib.Profile()
+        for i, ev in enumerate(stage_events):
+            prof.events[i] = ev.cuda_event
+        return C.byref(prof)
+
+    # ------------------------------------------------------------------ streamed moments
+    def moments_accumulate(self, q, msum, msumsq):
+        self._ensure()
+        dt = _lib.F64 if self.dtype == torch.float64 else _lib.F32
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.hmcb_moments_accumulate(dt, q.shape[0], q.shape[1], _lib.ptr(q), q.stride(0),
+                                                        q.stride(1), _lib.ptr(msum), _lib.ptr(msumsq), self._stream()))
+
+    def moments_reduce(self, msum, msumsq, n_samples, true_mean=None):
+        """[4,d] float64 device tensor: sum_c m, sum_c m^2, sum_c s2, sum_c (m-mu)^2."""
+        self._ensure()
+        dt = _lib.F64 if self.dtype == torch.float64 else _lib.F32
+        d = msum.shape[1]
+        with torch.cuda.device(self.device):
+            out = torch.empty((4, d), dtype=torch.float64, device=self.device)
+            mu = None if true_mean is None else torch.as_tensor(np.asarray(true_mean, dtype=np.float64),
+                                                                device=self.device)
+            _lib.check(self.lib.hmcb_moments_reduce(dt, msum.shape[0], d, _lib.ptr(msum), _lib.ptr(msumsq),
+                                                    float(n_samples), _lib.ptr(mu), _lib.ptr(out), self._stream()))
         return out
 
     def leapfrog(self, q, p, n_leap, step_size):

@@ -118,10 +118,32 @@ int hmcb_logp_grad(const hmcb_model* model, const hmcb_chains* chains, void* log
  * stage j+1.  code = j+1 (accepted at stage j) or 0.  `workspace` is caller-
  * owned scratch of at least hmcb_drhmc_workspace_bytes(); contents need not be
  * preserved between calls. */
+#define HMCB_MAX_PROPS 6
+/* Optional per-stage timing: cudaEvent_t handles (as void*) recorded on `stream`
+ * before stage 0, between stages and after the last one (nprops+1 events).  The
+ * reference's only timing is time.time() around its sample loop
+ * (scripts_old/funnel/funnelmpi.py:148,164-165). */
+typedef struct hmcb_profile {
+  void* events[HMCB_MAX_PROPS + 1];
+} hmcb_profile;
 size_t hmcb_drhmc_workspace_bytes(const hmcb_model* model, int64_t n_chains, int32_t nprops);
 int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng,
                     int32_t n_leap, double step_size, int32_t nprops, double stepfactor,
-                    const hmcb_step_out* out, void* workspace, size_t workspace_bytes, void* stream);
+                    const hmcb_step_out* out, void* workspace, size_t workspace_bytes,
+                    const hmcb_profile* profile /* may be NULL */, void* stream);
+
+/* Streamed sample moments (the reference stores samples[T,C,d] and post-processes,
+ * src/utils.py:8-27,207-237; at 2^20 chains that does not fit, so each transition is
+ * folded into per-chain running sums).  sum/sumsq are contiguous [C,d] (dtype),
+ * updated in place: sum += q, sumsq += q*q. */
+int hmcb_moments_accumulate(int32_t dtype, int64_t n_chains, int32_t d, const void* q, int64_t stride_chain,
+                            int64_t stride_dim, void* sum, void* sumsq, void* stream);
+/* Cross-chain reduction of per-chain mean m and variance s2 (ddof=1) over n_samples:
+ * out[4*d] doubles (device) = sum_c m, sum_c m^2, sum_c s2, sum_c (m - true_mean)^2 per
+ * dimension -- the quantities utils.get_ess_true (src/utils.py:23-27) and R-hat need;
+ * this small vector is what is all-reduced across GPUs.  true_mean [d] may be NULL (0). */
+int hmcb_moments_reduce(int32_t dtype, int64_t n_chains, int32_t d, const void* sum, const void* sumsq,
+                        double n_samples, const double* true_mean, double* out, void* stream);
 
 /* Measurement probe: a register-resident dependent-FMA loop (FP64 or FP32) used
  * to measure the pipe peak that roofline fractions are quoted against.
