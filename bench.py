@@ -41,7 +41,7 @@ def parse():
     ap.add_argument("--step_size", type=float, default=0.2)
     ap.add_argument("--nprops", type=int, default=3)
     ap.add_argument("--stepfactor", type=float, default=2.0)
-    ap.add_argument("--burnin", type=int, default=30)
+    ap.add_argument("--burnin", type=int, default=200)
     ap.add_argument("--seed", type=int, default=2)
     ap.add_argument("--cpu_seconds", type=float, default=12.0)
     ap.add_argument("--no_cpu_baseline", action="store_true")
@@ -105,16 +105,17 @@ def cpu_baseline(a, seconds):
     time, as the reference's one-chain-per-MPI-rank layout, scripts_old/jobscripts/
     run_funnel2.sh:16,42) for about `seconds` of wall time."""
     arm = CpuArm(a, 64)
+    arm.step(1)                             # warm the workers (imports, first-touch)
+    grads = leaps = nsteps = 0
     t0 = time.time()
-    g, _ = arm.step(1)                      # calibrate (also warms the workers)
-    per_chain = max(time.time() - t0, 1e-3)
-    n = int(max(1, min(64, seconds / per_chain)))
-    t0 = time.time()
-    grads, leaps = arm.step(n)
+    while time.time() - t0 < seconds:
+        g, l = arm.step(4)
+        grads, leaps, nsteps = grads + g, leaps + l, nsteps + 1
     dt = time.time() - t0
+    n = 4 * nsteps
     arm.close()
     return {"value": grads / dt, "unit": "grad_evals/s", "cores": arm.P, "kind": "port",
-            "sample": "%d chains x 1 DRHMC transition on each of %d processes (oracle/samplers.py drhmc_step, numpy), "
+            "sample": "%d DRHMC chain-transitions on each of %d processes (oracle/samplers.py drhmc_step, numpy), "
                       "%.1f s wall" % (n, arm.P, dt),
             "leapfrog_steps_per_s": (grads - leaps) / dt}
 
@@ -159,6 +160,10 @@ def workload_config(a, **extra):
 
 # ------------------------------------------------------------------ clocks
 class ClockSampler(threading.Thread):
+    """nvidia-smi in a subprocess (the profiling recipe's clocks line), sampling every
+    50 ms while the timed region runs.  In-process NVML polling was tried and rejected:
+    its driver calls stalled kernel launches and inflated ms_per_step."""
+
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -169,26 +174,31 @@ class ClockSampler(threading.Thread):
     def run(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             for line in self.proc.stdout:
                 self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
-        except Exception:
-            pass
+        except Exception as e:
+            self.error = repr(e)
 
     def stop(self):
         if self.proc:
             self.proc.terminate()
 
     def summary(self, t0, t1):
-        rows = [r for t, r in self.rows if t0 <= t <= t1 and len(r) >= 7] or [r for _, r in self.rows if len(r) >= 7]
+        good = [(t, r) for t, r in self.rows if len(r) >= 7]
+        rows = [r for t, r in good if t0 <= t <= t1 + 0.05]
+        note = "sampled inside the timed region"
+        if not rows and good:   # region shorter than the sampling period: nearest sample
+            rows = [min(good, key=lambda tr: abs(tr[0] - 0.5 * (t0 + t1)))[1]]
+            note = "timed region shorter than the 50 ms sampling period: nearest sample"
         if not rows:
-            return None
+            return {"error": getattr(self, "error", "no samples")}
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in rows)]
         sm = sorted(float(r[0]) for r in rows)
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "reasons": reasons,
-                "power_w_max": max(float(r[2]) for r in rows), "samples": len(rows)}
+                "power_w_max": max(float(r[2]) for r in rows), "samples": len(rows), "note": note}
 
 
 # ------------------------------------------------------------------ GPU arm
@@ -244,7 +254,7 @@ def run_hmcb(a):
 
     clocks = ClockSampler(local)
     clocks.start()
-    time.sleep(0.3)
+    time.sleep(0.5)
     K = a.steps
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(a.nprops + 1)] for _ in range(K)]
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

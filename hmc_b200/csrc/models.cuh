@@ -42,18 +42,26 @@ struct FunnelModel {
   template <int EPL, int LPC, bool WANT_V>
   __device__ __forceinline__ T kick(const T (&q)[EPL], T (&p)[EPL], T h, const GroupCtx<T>& c) const {
     const bool own_v = (c.lane == 0);
+    // exp(-v) first: its dependent chain then overlaps the independent sums below
+    const T v = (LPC == 1) ? q[0] : __shfl_sync(c.mask, q[0], 0, LPC);
+    const T e = t_exp_loop<T>(-v);
+    const T he = h * e;
     // S = sum theta^2: four partial sums so the FMA chain does not serialise
-    T acc[4] = {T(0), T(0), T(0), T(0)};
+    constexpr int NA = HMCB_FUNNEL_NACC;
+    T acc[NA];
+#pragma unroll
+    for (int i = 0; i < NA; ++i) acc[i] = T(0);
     const T t0 = own_v ? T(0) : q[0];
     acc[0] = t0 * t0;
 #pragma unroll
-    for (int s = 1; s < EPL; ++s) acc[s & 3] = fma(q[s], q[s], acc[s & 3]);
-    T S = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+    for (int s = 1; s < EPL; ++s) acc[s % NA] = fma(q[s], q[s], acc[s % NA]);
+#pragma unroll
+    for (int w = NA >> 1; w > 0; w >>= 1)
+#pragma unroll
+      for (int i = 0; i < w; ++i) acc[i] += acc[i + w];
+    T S = acc[0];
 #pragma unroll
     for (int o = LPC >> 1; o > 0; o >>= 1) S += __shfl_xor_sync(c.mask, S, o);
-    const T v = (LPC == 1) ? q[0] : __shfl_sync(c.mask, q[0], 0, LPC);
-    const T e = t_exp<T>(-v);
-    const T he = h * e;
     const T gv = fma(v, inv_s2, half_n) - T(0.5) * e * S;
     p[0] = own_v ? (p[0] - h * gv) : fma(-he, q[0], p[0]);
 #pragma unroll

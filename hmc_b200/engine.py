@@ -184,6 +184,8 @@ class Engine:
             return None
         prof = _lib.Profile()
         for i, ev in enumerate(stage_events):
+            if not ev.cuda_event:
+                ev.record()  # torch creates the cudaEvent_t lazily, at the first record
             prof.events[i] = ev.cuda_event
         return C.byref(prof)
 
