@@ -38,6 +38,16 @@ class StepOut(C.Structure):
                 ("counts", C.c_void_p), ("accept_prob", C.c_void_p)]
 
 
+class MalaIO(C.Structure):
+    _fields_ = [("V_in", C.c_void_p), ("Vg_in", C.c_void_p), ("V_out", C.c_void_p), ("Vg_out", C.c_void_p),
+                ("code", C.c_void_p), ("n_accept", C.c_void_p), ("counts", C.c_void_p)]
+
+
+class AdhmcOut(C.Structure):
+    _fields_ = [("p_out", C.c_void_p), ("code", C.c_void_p), ("probs", C.c_void_p), ("aux", C.c_void_p),
+                ("counts", C.c_void_p)]
+
+
 # every symbol include/hmcb.h declares: name -> (restype, argtypes)
 SIGNATURES = {
     "hmcb_version": (C.c_int, []),
@@ -55,6 +65,12 @@ SIGNATURES = {
                                           C.c_void_p, C.c_void_p, C.c_void_p]),
     "hmcb_moments_reduce": (C.c_int, [C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_double,
                                       C.c_void_p, C.c_void_p, C.c_void_p]),
+    "hmcb_mala_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_double, C.c_int32,
+                                 C.POINTER(MalaIO), C.c_void_p]),
+    "hmcb_adhmc_eps0_workspace_bytes": (C.c_size_t, [C.POINTER(Model), C.c_int64]),
+    "hmcb_adhmc_eps0_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32,
+                                       C.POINTER(C.c_double), C.c_int32, C.c_int32, C.POINTER(AdhmcOut), C.c_void_p,
+                                       C.c_size_t, C.c_void_p]),
     "hmcb_probe_fma": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.POINTER(C.c_double),
                                  C.c_void_p]),
 }

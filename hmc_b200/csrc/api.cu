@@ -55,7 +55,7 @@ std::vector<Entry>& registry() {
   return r;
 }
 
-const Entry* choose_entry(const hmcb_model& hm) {
+const Entry* choose_entry(const hmcb_model& hm, int max_epl) {
   const int unitm = hm.invmetric_diag ? 0 : 1;
   int force_lpc = 0;
   if (const char* e = getenv("HMCB_LPC")) force_lpc = atoi(e);
@@ -65,7 +65,7 @@ const Entry* choose_entry(const hmcb_model& hm) {
     for (const Entry& e : registry()) {
       if (e.kind != hm.kind || e.dtype != hm.dtype || e.unitm != unitm) continue;
       if (pass == 0 && force_lpc && e.lpc != force_lpc) continue;
-      if (slots_needed(hm.d, e.lpc) > e.epl) continue;
+      if (slots_needed(hm.d, e.lpc) > e.epl || e.epl > max_epl) continue;
       if (hm.kind == HMCB_MODEL_ROSENBROCK && (e.epl & 1)) continue;
       // least padded slots first, then fewest lanes per chain
       const long cost = (long)e.epl * e.lpc * 64 + e.lpc;
@@ -219,6 +219,55 @@ static int drhmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* 
   return rc;
 }
 
+template <typename T>
+static int mala_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r, double eps,
+                       int n_steps, const hmcb_mala_io* io, cudaStream_t st) {
+  MalaArgs<T> a;
+  memset(&a, 0, sizeof(a));
+  a.n_chains = c->n_chains; a.chain_offset = c->chain_offset; a.d = m->d;
+  a.q_in = (const T*)c->q_in; a.q_out = (T*)c->q_out; a.sc = c->stride_chain; a.sd = c->stride_dim;
+  a.seed = r->seed; a.iteration = (uint32_t)r->iteration; a.rng_flags = r->flags;
+  a.z_inject = (const T*)r->p_inject; a.u_inject = r->u_inject; a.u_stride = r->u_stride;
+  a.eps = (T)eps; a.n_steps = n_steps;
+  if (io) {
+    a.V_in = (const T*)io->V_in; a.Vg_in = (const T*)io->Vg_in; a.V_out = (T*)io->V_out; a.Vg_out = (T*)io->Vg_out;
+    a.code = io->code; a.n_accept = io->n_accept; a.counts = io->counts;
+  }
+  return e->fn(*m, OP_MALA, &a, st);
+}
+
+static int ad_frame_threads(const Entry* e, const hmcb_model* m, int64_t n_chains, int64_t& ft, int& epl) {
+  LaunchInfo li;
+  int rc = e->fn(*m, OP_QUERY_AD, &li, nullptr);
+  if (rc) return rc;
+  const int64_t gpb = li.threads / li.lpc;
+  int64_t blocks = (n_chains + gpb - 1) / gpb;
+  if (blocks < 1) blocks = 1;
+  if (blocks > li.max_blocks) blocks = li.max_blocks;
+  ft = blocks * li.threads;
+  epl = li.epl;
+  return 0;
+}
+
+template <typename T>
+static int adhmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r, int n_leap,
+                        const double* steps, int ntry, int nsteps, const hmcb_adhmc_out* o, void* ws, int64_t ft,
+                        cudaStream_t st) {
+  AdArgs<T> a;
+  memset(&a, 0, sizeof(a));
+  a.n_chains = c->n_chains; a.chain_offset = c->chain_offset; a.d = m->d;
+  a.q_in = (const T*)c->q_in; a.q_out = (T*)c->q_out; a.sc = c->stride_chain; a.sd = c->stride_dim;
+  a.seed = r->seed; a.iteration = (uint32_t)r->iteration; a.rng_flags = r->flags;
+  a.p_inject = (const T*)r->p_inject; a.u_inject = r->u_inject; a.u_stride = r->u_stride;
+  a.minv = (const T*)m->invmetric_diag;
+  a.n_leap = n_leap; a.ntry = ntry; a.nsteps = nsteps;
+  for (int i = 0; i < ntry; ++i) { a.steps[i] = steps[i]; a.pwts[i] = pow(steps[i], 0.5); }
+  if (o) { a.p_out = (T*)o->p_out; a.code = o->code; a.probs = (T*)o->probs; a.aux = (T*)o->aux; a.counts = o->counts; }
+  a.frames = (T*)ws;
+  a.frame_threads = ft;
+  return e->fn(*m, OP_ADHMC, &a, st);
+}
+
 }  // namespace hmcb
 
 using namespace hmcb;
@@ -325,6 +374,63 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
   if (model->dtype == HMCB_F64)
     return drhmc_step_t<double>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, out, workspace, L, profile, st);
   return drhmc_step_t<float>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, out, workspace, L, profile, st);
+}
+
+int hmcb_mala_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, double eps,
+                   int32_t n_steps, const hmcb_mala_io* io, void* stream) {
+  int rc;
+  if ((rc = check_model(model))) return rc;
+  if ((rc = check_chains(chains))) return rc;
+  HMCB_CHECK_ARG(rng != nullptr, "rng is NULL");
+  HMCB_CHECK_ARG(n_steps >= 1, "n_steps must be >= 1");
+  HMCB_CHECK_ARG(eps > 0, "eps must be > 0");
+  HMCB_CHECK_ARG(!rng->p_inject || n_steps == 1, "injected normals are only defined for n_steps == 1");
+  HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= n_steps, "u_inject needs u_stride >= n_steps");
+  if (chains->n_chains == 0) return 0;
+  hmcb_model mm = *model;
+  mm.invmetric_diag = nullptr;  // the reference's MALA never uses its metric (src/mala.py:45-60)
+  const Entry* e = choose_entry(mm, kMalaMaxEpl);
+  if (!e) return HMCB_E_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (model->dtype == HMCB_F64) return mala_step_t<double>(e, &mm, chains, rng, eps, n_steps, io, st);
+  return mala_step_t<float>(e, &mm, chains, rng, eps, n_steps, io, st);
+}
+
+size_t hmcb_adhmc_eps0_workspace_bytes(const hmcb_model* model, int64_t n_chains) {
+  if (check_model(model) || n_chains < 1) return 0;
+  const Entry* e = choose_entry(*model);
+  if (!e) return 0;
+  int64_t ft;
+  int epl;
+  if (ad_frame_threads(e, model, n_chains, ft, epl)) return 0;
+  return (size_t)4 * epl * ft * (model->dtype == HMCB_F64 ? 8 : 4);
+}
+
+int hmcb_adhmc_eps0_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
+                         const double* steps, int32_t ntry, int32_t nsteps, const hmcb_adhmc_out* out,
+                         void* workspace, size_t workspace_bytes, void* stream) {
+  int rc;
+  if ((rc = check_model(model))) return rc;
+  if ((rc = check_chains(chains))) return rc;
+  HMCB_CHECK_ARG(rng != nullptr && steps != nullptr, "rng/steps is NULL");
+  HMCB_CHECK_ARG(ntry >= 2 && ntry <= kMaxTry, "ntry=%d must be in 2..%d", ntry, kMaxTry);
+  HMCB_CHECK_ARG(n_leap >= 1 && nsteps >= 1, "n_leap and nsteps must be >= 1");
+  HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= 3, "u_inject needs u_stride >= 3");
+  if (chains->n_chains == 0) return 0;
+  const Entry* e = choose_entry(*model);
+  if (!e) return HMCB_E_UNSUPPORTED;
+  int64_t ft;
+  int epl;
+  if ((rc = ad_frame_threads(e, model, chains->n_chains, ft, epl))) return rc;
+  const size_t need = (size_t)4 * epl * ft * (model->dtype == HMCB_F64 ? 8 : 4);
+  if (!workspace || workspace_bytes < need) {
+    set_error("adhmc workspace too small: have %zu bytes, need %zu", workspace ? workspace_bytes : (size_t)0, need);
+    return HMCB_E_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (model->dtype == HMCB_F64)
+    return adhmc_step_t<double>(e, model, chains, rng, n_leap, steps, ntry, nsteps, out, workspace, ft, st);
+  return adhmc_step_t<float>(e, model, chains, rng, n_leap, steps, ntry, nsteps, out, workspace, ft, st);
 }
 
 }  // extern "C"

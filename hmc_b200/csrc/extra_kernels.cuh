@@ -1,0 +1,360 @@
+// extra_kernels.cuh -- MALA (src/mala.py) and AdHMC_eps0 (src/adaptivehmc.py:105-192)
+// transitions, built from the same register-resident pieces as transition.cuh.
+#pragma once
+#include "transition.cuh"
+
+namespace hmcb {
+
+// ------------------------------------------------------------------ MALA
+// One step (src/mala.py:45-60,24-42): z ~ N(0,I); q1 = q - eps^2/2 grad V(q) + eps z;
+// prob = exp(V(q)-V(q1)) * exp(lognum - logden) with the Gaussian proposal densities;
+// code 2 on NaN/inf/no-move, else reject iff u > min(1,prob).  V(q), grad V(q) are
+// carried between steps (the reference caches them, :49-52,60): 1 gradient per step.
+// n_steps steps are fused in one launch with q, grad V(q), q1, grad V(q1) in registers,
+// so the kernel is FP64-bound instead of paying 32d bytes of HBM per gradient.
+template <typename T>
+struct MalaArgs {
+  int64_t n_chains, chain_offset;
+  int32_t d;
+  const T* q_in;
+  T* q_out;
+  int64_t sc, sd;
+  uint64_t seed;
+  uint32_t iteration;
+  int32_t rng_flags;
+  const T* z_inject;       // [C,d] layout of q (only meaningful for n_steps == 1)
+  const double* u_inject;  // [C,u_stride]
+  int32_t u_stride;
+  T eps;
+  int32_t n_steps;
+  const T* V_in;           // [C] cached V(q) or nullptr
+  const T* Vg_in;          // layout of q, cached grad V(q), or nullptr
+  T* V_out;
+  T* Vg_out;
+  int32_t* code;           // [C] code of the last step
+  int32_t* n_accept;       // [C] accepted steps among n_steps
+  int32_t* counts;         // [C,3] Hcount(0), Vgcount, leapcount(0)
+};
+
+template <class Model, typename T, int EPL, int LPC, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) k_mala(const Model model, const MalaArgs<T> a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  using Lay = Layout<EPL, LPC>;
+  constexpr int GPB = THREADS / LPC;
+  const int d = a.d;
+  model.block_init(smem_raw, THREADS);
+  GroupCtx<T> c;
+  c.lane = threadIdx.x & (LPC - 1);
+  c.d = d;
+  const int group_in_warp = (threadIdx.x & 31) / LPC;
+  c.mask = (LPC == 32) ? 0xffffffffu : (((1u << LPC) - 1u) << (group_in_warp * LPC));
+  c.smem_q = nullptr;
+  if (Model::kNeedsSmem) c.smem_q = (T*)smem_raw + model.p_smem_elems() + (size_t)(threadIdx.x / LPC) * d;
+
+  const T half_e2 = T(0.5) * a.eps * a.eps;  // 0.5*eps**2
+  const T e2 = a.eps * a.eps;
+  const int64_t total_groups = (int64_t)gridDim.x * GPB;
+  for (int64_t chain = ((int64_t)blockIdx.x * THREADS + threadIdx.x) / LPC; chain < a.n_chains; chain += total_groups) {
+    const int64_t off = chain * a.sc;
+    const uint64_t gchain = (uint64_t)(a.chain_offset + chain);
+    T q[EPL], g[EPL], q1[EPL], g1[EPL];
+    load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
+    int nvg = 0, nacc = 0, code = 0;
+    T Vq;
+    if (a.Vg_in) {
+      load_vec<T, EPL, LPC>(g, a.Vg_in, off, a.sd, c.lane, d, T(1));
+      Vq = a.V_in ? a.V_in[chain] : T(0);
+    }
+    if (!a.Vg_in || !a.V_in) {
+      T tmp[EPL];
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) tmp[s] = T(0);
+      const T V = model.template kick<EPL, LPC, true>(q, tmp, T(-1), c);  // tmp = +grad V
+      if (!a.Vg_in) {
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) g[s] = tmp[s];
+        nvg += 1;
+      }
+      if (!a.V_in) Vq = V;
+    }
+    for (int k = 0; k < a.n_steps; ++k) {
+      // proposal
+      if (a.z_inject) {
+        load_vec<T, EPL, LPC>(q1, a.z_inject, off, a.sd, c.lane, d, T(1));
+      } else {
+#pragma unroll
+        for (int b = 0; b < Lay::kBlocks; ++b) {
+          const Normal4 n = philox_normal4(a.seed, gchain, a.iteration + (uint32_t)k, (uint32_t)(b * LPC + c.lane), a.rng_flags);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (4 * b + j < EPL) q1[4 * b + j] = (Lay::elem(c.lane, 4 * b + j) < d) ? (T)n.z[j] : T(0);
+        }
+      }
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) {
+        q1[s] = (q[s] - half_e2 * g[s]) + a.eps * q1[s];
+        g1[s] = T(0);
+      }
+      const T V1 = model.template kick<EPL, LPC, true>(q1, g1, T(-1), c);
+      nvg += 1;
+      // Hastings ratio exactly as the reference forms it (src/mala.py:24-30)
+      T ln = T(0), ld = T(0), dq = T(0);
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) {
+        const T mu0 = q[s] - half_e2 * g[s];
+        const T mu1 = q1[s] - half_e2 * g1[s];
+        const T a0 = q1[s] - mu0, a1 = q[s] - mu1;
+        ld = fma(a0, a0, ld);
+        ln = fma(a1, a1, ln);
+        dq += q[s] - q1[s];
+      }
+      ld = group_sum_masked<LPC, T>(ld, c.mask);
+      ln = group_sum_masked<LPC, T>(ln, c.mask);
+      dq = group_sum_masked<LPC, T>(dq, c.mask);
+      const T logden = T(-0.5) * ld / e2, lognum = T(-0.5) * ln / e2;
+      const T prob = t_exp<T>(Vq - V1) * t_exp<T>(lognum - logden);
+      const bool bad = t_bad(prob) || dq == T(0);
+      bool accept = false;
+      if (!bad) {
+        double u;
+        if (a.u_inject) {
+          u = a.u_inject[chain * a.u_stride + k];
+        } else {
+          uint32_t w[4];
+          Philox::gen(a.seed, gchain, a.iteration + (uint32_t)k, STREAM_ACCEPT, 0, w);
+          u = u53(w[0], w[1]);
+        }
+        const T pm = prob < T(1) ? prob : T(1);
+        accept = !(u > (double)pm);
+      }
+      code = bad ? 2 : (accept ? 1 : 0);
+      if (accept) {
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) { q[s] = q1[s]; g[s] = g1[s]; }
+        Vq = V1;
+        nacc += 1;
+      }
+    }
+    store_vec<T, EPL, LPC>(q, a.q_out, off, a.sd, c.lane, d);
+    if (a.Vg_out) store_vec<T, EPL, LPC>(g, a.Vg_out, off, a.sd, c.lane, d);
+    if (c.lane == 0) {
+      if (a.V_out) a.V_out[chain] = Vq;
+      if (a.code) a.code[chain] = code;
+      if (a.n_accept) a.n_accept[chain] = nacc;
+      if (a.counts) { a.counts[3 * chain] = 0; a.counts[3 * chain + 1] = nvg; a.counts[3 * chain + 2] = 0; }
+    }
+  }
+}
+
+// ------------------------------------------------------------------ AdHMC_eps0
+// Per-transition random step size (src/adaptivehmc.py:111-192): ntry log-spaced trial
+// step sizes, nsteps leapfrog steps each from (q0,p0); weights exp(H0-H_i) sqrt(eps_i)
+// normalised; inverse-CDF draw of a bin, uniform within the bin; main trajectory of
+// n_leap steps; the same sweep from (q1,-p1) gives the reverse probability; Hastings
+// factor pb/pf multiplies exp(H0-H1).  Base states live in per-thread scratch frames.
+constexpr int kMaxTry = 64;
+
+template <typename T>
+struct AdArgs {
+  int64_t n_chains, chain_offset;
+  int32_t d;
+  const T* q_in;
+  T* q_out;
+  int64_t sc, sd;
+  uint64_t seed;
+  uint32_t iteration;
+  int32_t rng_flags;
+  const T* p_inject;
+  const double* u_inject;
+  int32_t u_stride;
+  const T* minv;
+  int32_t n_leap, ntry, nsteps;
+  double steps[kMaxTry];   // trial step sizes (host-computed np.logspace)
+  double pwts[kMaxTry];    // steps**0.5
+  T* p_out;
+  int32_t* code;
+  T* probs;                // [C,3] prob, prob/hastings, hastings
+  T* aux;                  // [C,3] pf_den, pb_num, eps
+  int32_t* counts;         // [C,3]
+  T* frames;               // [4*EPL*frame_threads]: p0, q1, p1 (+1 spare)
+  int64_t frame_threads;
+};
+
+template <typename T>
+__device__ __forceinline__ double draw_uniform_ad(const AdArgs<T>& a, int64_t chain, uint64_t gchain, int idx) {
+  if (a.u_inject) return a.u_inject[chain * a.u_stride + idx];
+  uint32_t w[4];
+  Philox::gen(a.seed, gchain, a.iteration, STREAM_STEPSIZE, (uint32_t)(idx >> 1), w);
+  return (idx & 1) ? u53(w[2], w[3]) : u53(w[0], w[1]);
+}
+
+template <class Model, typename T, int EPL, int LPC, bool UNITM, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) k_adhmc_eps0(const Model model, const AdArgs<T> a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  using Lay = Layout<EPL, LPC>;
+  constexpr int GPB = THREADS / LPC;
+  const int d = a.d;
+  model.block_init(smem_raw, THREADS);
+  GroupCtx<T> c;
+  c.lane = threadIdx.x & (LPC - 1);
+  c.d = d;
+  const int group_in_warp = (threadIdx.x & 31) / LPC;
+  c.mask = (LPC == 32) ? 0xffffffffu : (((1u << LPC) - 1u) << (group_in_warp * LPC));
+  c.smem_q = nullptr;
+  if (Model::kNeedsSmem) c.smem_q = (T*)smem_raw + model.p_smem_elems() + (size_t)(threadIdx.x / LPC) * d;
+  T minv[UNITM ? 1 : EPL];
+  if (!UNITM) {
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) {
+      const int i = Lay::elem(c.lane, s);
+      minv[UNITM ? 0 : s] = (i < d) ? a.minv[i] : T(1);
+    }
+  } else {
+    minv[0] = T(1);
+  }
+  const int64_t gthread = (int64_t)blockIdx.x * THREADS + threadIdx.x;
+  const int64_t FT = a.frame_threads;
+  T* f_p0 = a.frames + gthread;
+  T* f_q1 = f_p0 + (int64_t)EPL * FT;
+  T* f_p1 = f_q1 + (int64_t)EPL * FT;
+  const int64_t total_groups = (int64_t)gridDim.x * GPB;
+  const int ntry = a.ntry;
+
+  for (int64_t chain = gthread / LPC; chain < a.n_chains; chain += total_groups) {
+    const int64_t off = chain * a.sc;
+    const uint64_t gchain = (uint64_t)(a.chain_offset + chain);
+    T q[EPL], p[EPL];
+    int cH = 0, cVg = 0, cLeap = 0;
+    T pp[kMaxTry];
+
+    // draw p0 and park it
+    {
+      TransArgs<T> ta;
+      ta.chain_offset = a.chain_offset; ta.sc = a.sc; ta.sd = a.sd; ta.seed = a.seed; ta.iteration = a.iteration;
+      ta.rng_flags = a.rng_flags; ta.p_inject = a.p_inject;
+      draw_momentum<T, EPL, LPC, UNITM>(p, ta, minv, chain, c.lane, d);
+    }
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) f_p0[(int64_t)s * FT] = p[s];
+
+    // sweep(from forward base or reverse base): fills pp[] normalised; returns H at the base
+    auto sweep = [&](bool reverse, T& Hbase) {
+      T sum = T(0);
+      for (int i = 0; i <= ntry; ++i) {
+        // i == 0 evaluates H at the base through a zero-length "trajectory" (kick with h=0)
+        if (!reverse) {
+          load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
+#pragma unroll
+          for (int s = 0; s < EPL; ++s) p[s] = f_p0[(int64_t)s * FT];
+        } else {
+#pragma unroll
+          for (int s = 0; s < EPL; ++s) { q[s] = f_q1[(int64_t)s * FT]; p[s] = -f_p1[(int64_t)s * FT]; }
+        }
+        if (i == 0) {
+          const T K = kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+          T tmp[EPL];
+#pragma unroll
+          for (int s = 0; s < EPL; ++s) tmp[s] = T(0);
+          Hbase = model.template kick<EPL, LPC, true>(q, tmp, T(0), c) + K;
+          cH += 1;
+          continue;
+        }
+        T Vs, Ve;
+        const int N = a.nsteps > 1 ? a.nsteps : 1;
+        leapfrog<Model, T, EPL, LPC, UNITM>(model, q, p, minv, N, (T)a.steps[i - 1], c, Vs, Ve);
+        const T Hi = Ve + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+        cH += 1; cVg += N + 1; cLeap += 1;
+        T w = t_exp<T>(Hbase - Hi) * (T)a.pwts[i - 1];
+        if (t_bad(w)) w = T(0);
+        pp[i - 1] = w;
+        sum += w;
+      }
+      for (int i = 0; i < ntry; ++i) pp[i] = pp[i] / sum;
+    };
+
+    // forward sweep: get_stepsize(q0, p0) (src/adaptivehmc.py:180 -> :111-131).  The
+    // reference evaluates H0 twice (hmc_step :163 and get_stepsize :112): count both.
+    T H0;
+    sweep(false, H0);
+    cH += 1;
+    T cdf_min = pp[0], run = T(0);
+    int isx = -1;
+    const double u0 = draw_uniform_ad(a, chain, gchain, 0);
+    // cdf = cumsum(pp); sx = U(low=cdf.min()); isx = last index with sx > cdf
+    {
+      T r2 = T(0);
+      for (int i = 0; i < ntry; ++i) { r2 += pp[i]; if (i == 0 || r2 < cdf_min) cdf_min = r2; }
+      const T sx = cdf_min + (T(1) - cdf_min) * (T)u0;
+      for (int i = 0; i < ntry; ++i) { run += pp[i]; if (sx > run) isx = i; }
+    }
+    bool broken = (isx < 0) || (isx > ntry - 2);   // the reference raises IndexError here; we reject (code 2)
+    if (isx < 0) isx = 0;
+    if (isx > ntry - 2) isx = ntry - 2;
+    const double u1 = draw_uniform_ad(a, chain, gchain, 1);
+    const T ss = (T)(a.steps[isx] + (a.steps[isx + 1] - a.steps[isx]) * u1);
+    const T pf_den = pp[isx + 1];
+
+    // main trajectory from (q0, p0)
+    load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) p[s] = f_p0[(int64_t)s * FT];
+    T Vs, Ve;
+    const int Nm = a.n_leap > 1 ? a.n_leap : 1;
+    leapfrog<Model, T, EPL, LPC, UNITM>(model, q, p, minv, Nm, ss, c, Vs, Ve);
+    const T H1 = Ve + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+    cH += 1; cVg += Nm + 1; cLeap += 1;
+    T dq = T(0);
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) {
+      const int i = Lay::elem(c.lane, s);
+      if (i < d) dq += a.q_in[off + i * a.sd] - q[s];
+      f_q1[(int64_t)s * FT] = q[s];
+      f_p1[(int64_t)s * FT] = p[s];
+    }
+    dq = group_sum_masked<LPC, T>(dq, c.mask);
+
+    // reverse sweep: get_stepsize(q1, -p1, eps=ss) (:182 -> :132-134)
+    T Hb;
+    sweep(true, Hb);
+    int jb = -1;
+    for (int i = ntry - 1; i >= 0; --i) if (a.steps[i] > (double)ss) jb = i;
+    if (jb < 0) { jb = ntry - 1; broken = true; }
+    const T pb_num = pp[jb];
+    const T hast = pb_num / pf_den;
+    const T prob = t_exp<T>(H0 - H1) * hast;
+    const bool bad = broken || t_bad(prob) || dq == T(0);
+    bool accept = false;
+    if (!bad) {
+      const double u2 = draw_uniform_ad(a, chain, gchain, 2);
+      const T pm = prob < T(1) ? prob : T(1);
+      accept = !(u2 > (double)pm);
+    }
+    if (c.lane == 0) {
+      if (a.code) a.code[chain] = bad ? 2 : (accept ? 1 : 0);
+      if (a.probs) { a.probs[3 * chain] = prob; a.probs[3 * chain + 1] = prob / hast; a.probs[3 * chain + 2] = hast; }
+      if (a.aux) { a.aux[3 * chain] = pf_den; a.aux[3 * chain + 1] = pb_num; a.aux[3 * chain + 2] = ss; }
+      if (a.counts) { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = cLeap; }
+    }
+    if (accept) {
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) { q[s] = f_q1[(int64_t)s * FT]; p[s] = f_p1[(int64_t)s * FT]; }
+      store_vec<T, EPL, LPC>(q, a.q_out, off, a.sd, c.lane, d);
+      if (a.p_out) store_vec<T, EPL, LPC>(p, a.p_out, off, a.sd, c.lane, d);
+    } else {
+      if (a.q_out != a.q_in) {
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) {
+          const int i = Lay::elem(c.lane, s);
+          if (i < d) a.q_out[off + i * a.sd] = a.q_in[off + i * a.sd];
+        }
+      }
+      if (a.p_out) {
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) p[s] = f_p0[(int64_t)s * FT];
+        store_vec<T, EPL, LPC>(p, a.p_out, off, a.sd, c.lane, d);
+      }
+    }
+  }
+}
+
+}  // namespace hmcb

@@ -7,11 +7,13 @@
 #pragma once
 #include <vector>
 
-#include "transition.cuh"
+#include "extra_kernels.cuh"
 
 namespace hmcb {
 
-enum Op { OP_HMC = 0, OP_DR0 = 1, OP_DRN = 2, OP_LEAPFROG = 3, OP_LOGPGRAD = 4, OP_QUERY = 5 };
+enum Op { OP_HMC = 0, OP_DR0 = 1, OP_DRN = 2, OP_LEAPFROG = 3, OP_LOGPGRAD = 4, OP_QUERY = 5, OP_MALA = 6, OP_ADHMC = 7,
+          OP_QUERY_AD = 8 };
+constexpr int kMalaMaxEpl = 28;  // MALA keeps q, grad, q1, grad1 in registers: 4*EPL values per lane
 
 struct LaunchInfo {
   int threads;        // block size
@@ -33,7 +35,7 @@ struct Registrar {
 };
 
 // pick the compiled shape for this model; nullptr (+ error set) if none fits
-const Entry* choose_entry(const hmcb_model& hm);
+const Entry* choose_entry(const hmcb_model& hm, int max_epl = 1 << 30);
 
 // leapfrog-only / logp+grad kernels share the transition kernel's device code
 template <typename T>
@@ -172,6 +174,36 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
       AuxArgs<T>& a = *(AuxArgs<T>*)args;
       k<<<grid_for(a.n_chains, max_blocks), THREADS, smem, st>>>(model, a, op);
       break;
+    }
+    case OP_MALA: {
+      if constexpr (EPL <= kMalaMaxEpl) {
+        constexpr int MB = min_blocks_for<T, 2 * EPL, true, false>();
+        auto k = k_mala<Model, T, EPL, LPC, THREADS, MB>;
+        if ((rc = prep(k, max_blocks))) return rc;
+        MalaArgs<T>& a = *(MalaArgs<T>*)args;
+        k<<<grid_for(a.n_chains, max_blocks), THREADS, smem, st>>>(model, a);
+        break;
+      } else {
+        set_error("internal: MALA is not compiled for EPL=%d", EPL);
+        return HMCB_E_UNSUPPORTED;
+      }
+    }
+    case OP_ADHMC: {
+      auto k = k_adhmc_eps0<Model, T, EPL, LPC, UNITM, THREADS, MINB>;
+      if ((rc = prep(k, max_blocks))) return rc;
+      AdArgs<T>& a = *(AdArgs<T>*)args;
+      k<<<(int)(a.frame_threads / THREADS), THREADS, smem, st>>>(model, a);
+      break;
+    }
+    case OP_QUERY_AD: {
+      auto k = k_adhmc_eps0<Model, T, EPL, LPC, UNITM, THREADS, MINB>;
+      if ((rc = prep(k, max_blocks))) return rc;
+      LaunchInfo* li = (LaunchInfo*)args;
+      li->threads = THREADS;
+      li->max_blocks = max_blocks;
+      li->epl = EPL;
+      li->lpc = LPC;
+      return 0;
     }
     case OP_QUERY: {
       auto k = k_transition<Model, T, EPL, LPC, UNITM, MODE_DRN, THREADS, MINB>;

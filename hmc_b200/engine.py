@@ -177,6 +177,58 @@ class Engine:
         out["_keep"] = keep
         return out
 
+    def mala_step(self, q, eps, n_steps=1, V=None, Vg=None, z=None, u=None, q_out=None):
+        """hmcb_mala_step on device tensor q [C,d]; V [C] / Vg [C,d] are the cached
+        potential and its gradient (None on the first call)."""
+        m = self._ensure()
+        C_ = q.shape[0]
+        with torch.cuda.device(self.device):
+            q_out = torch.empty_like(q) if q_out is None else q_out
+            out = {"q": q_out, "V": torch.empty(C_, dtype=self.dtype, device=self.device), "Vg": torch.empty_like(q),
+                   "code": torch.empty(C_, dtype=torch.int32, device=self.device),
+                   "n_accept": torch.empty(C_, dtype=torch.int32, device=self.device),
+                   "counts": torch.empty((C_, 3), dtype=torch.int32, device=self.device)}
+            io = _lib.MalaIO()
+            io.V_in, io.Vg_in = _lib.ptr(V), _lib.ptr(Vg)
+            io.V_out, io.Vg_out, io.code = _lib.ptr(out["V"]), _lib.ptr(out["Vg"]), _lib.ptr(out["code"])
+            io.n_accept, io.counts = _lib.ptr(out["n_accept"]), _lib.ptr(out["counts"])
+            ch = self._chains(q, q_out)
+            r, keep = self._rng(z, u, n_steps, C_)
+            _lib.check(self.lib.hmcb_mala_step(C.byref(m), C.byref(ch), C.byref(r), float(eps), int(n_steps),
+                                               C.byref(io), self._stream()))
+        self.iteration += int(n_steps)
+        out["_keep"] = keep
+        return out
+
+    def adhmc_eps0_step(self, q, n_leap, steps, nsteps, p=None, u=None, q_out=None):
+        m = self._ensure()
+        C_ = q.shape[0]
+        steps = np.ascontiguousarray(steps, dtype=np.float64)
+        with torch.cuda.device(self.device):
+            need = self.lib.hmcb_adhmc_eps0_workspace_bytes(C.byref(m), C_)
+            if need == 0:
+                _lib.check(_lib.E_ARG)
+            if self._ws is None or self._ws.numel() < need:
+                self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+            q_out = torch.empty_like(q) if q_out is None else q_out
+            out = {"q": q_out, "p": torch.empty_like(q),
+                   "code": torch.empty(C_, dtype=torch.int32, device=self.device),
+                   "probs": torch.empty((C_, 3), dtype=self.dtype, device=self.device),
+                   "aux": torch.empty((C_, 3), dtype=self.dtype, device=self.device),
+                   "counts": torch.empty((C_, 3), dtype=torch.int32, device=self.device)}
+            so = _lib.AdhmcOut()
+            so.p_out, so.code, so.probs = _lib.ptr(out["p"]), _lib.ptr(out["code"]), _lib.ptr(out["probs"])
+            so.aux, so.counts = _lib.ptr(out["aux"]), _lib.ptr(out["counts"])
+            ch = self._chains(q, q_out)
+            r, keep = self._rng(p, u, 3, C_)
+            _lib.check(self.lib.hmcb_adhmc_eps0_step(
+                C.byref(m), C.byref(ch), C.byref(r), int(n_leap), steps.ctypes.data_as(C.POINTER(C.c_double)),
+                int(steps.size), int(nsteps), C.byref(so), C.c_void_p(self._ws.data_ptr()), self._ws.numel(),
+                self._stream()))
+        self.iteration += 1
+        out["_keep"] = keep
+        return out
+
     @staticmethod
     def _profile(stage_events):
         """torch.cuda.Event list (enable_timing=True) -> hmcb_profile, or NULL."""

@@ -145,6 +145,41 @@ int hmcb_moments_accumulate(int32_t dtype, int64_t n_chains, int32_t d, const vo
 int hmcb_moments_reduce(int32_t dtype, int64_t n_chains, int32_t d, const void* sum, const void* sumsq,
                         double n_samples, const double* true_mean, double* out, void* stream);
 
+/* MALA, mala.MALA.step + metropolis (src/mala.py:45-60,24-42), n_steps >= 1 steps
+ * fused per launch.  V(q) and grad V(q) are carried between calls as the reference
+ * carries them through its return values (:60): pass V_in/Vg_in = NULL on the first
+ * call.  rng->p_inject holds the standard normals z (n_steps == 1 only); codes 1/0/2.
+ * The reference's MALA ignores its invmetric_diag; so does this. */
+typedef struct hmcb_mala_io {
+  const void* V_in;    /* [C] V(q) = -log_prob(q), or NULL */
+  const void* Vg_in;   /* grad V(q), layout of q, or NULL */
+  void* V_out;         /* [C] */
+  void* Vg_out;        /* layout of q */
+  int32_t* code;       /* [C] code of the last step */
+  int32_t* n_accept;   /* [C] accepted steps among n_steps */
+  int32_t* counts;     /* [C,3] Hcount (0), Vgcount, leapcount (0) */
+} hmcb_mala_io;
+int hmcb_mala_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, double eps,
+                   int32_t n_steps, const hmcb_mala_io* io, void* stream);
+
+/* AdHMC_eps0.hmc_step with Tint = 0 (src/adaptivehmc.py:138-192) and its step-size
+ * draw get_stepsize (:111-134).  `steps` is a HOST array of the ntry trial step sizes
+ * (np.logspace(log10(smin), log10(smax), ntry), computed by the caller so that the
+ * values are bit-identical to numpy's).  Uniform draws, in the reference's order:
+ * u[0] bin draw, u[1] within-bin draw, u[2] accept test.  Codes 1/0/2; where the
+ * reference would raise IndexError (all trial weights NaN) the chain gets code 2. */
+typedef struct hmcb_adhmc_out {
+  void* p_out;         /* layout of q */
+  int32_t* code;       /* [C] */
+  void* probs;         /* [C,3] prob, prob/hastings, hastings */
+  void* aux;           /* [C,3] pf_den, pb_num, eps */
+  int32_t* counts;     /* [C,3] */
+} hmcb_adhmc_out;
+size_t hmcb_adhmc_eps0_workspace_bytes(const hmcb_model* model, int64_t n_chains);
+int hmcb_adhmc_eps0_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
+                         const double* steps, int32_t ntry, int32_t nsteps, const hmcb_adhmc_out* out,
+                         void* workspace, size_t workspace_bytes, void* stream);
+
 /* Measurement probe: a register-resident dependent-FMA loop (FP64 or FP32) used
  * to measure the pipe peak that roofline fractions are quoted against.
  * Launches `blocks` x `threads`, each thread doing iters*ilp*unroll FMAs; writes

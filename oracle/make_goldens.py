@@ -86,6 +86,70 @@ def run_case(case):
     return code
 
 
+MALA_CASES = [
+    dict(name="mala_funnel10", model=dict(kind="funnel", d=10), C=8, T=6, seed=201, eps=0.15),
+    dict(name="mala_rosen8", model=dict(kind="rosenbrock", d=8), C=8, T=6, seed=202, eps=0.04),
+    dict(name="mala_gauss12", model=dict(kind="gaussian", d=12), C=8, T=6, seed=203, eps=0.2),
+]
+
+ADHMC_CASES = [
+    dict(name="adhmc_funnel10", model=dict(kind="funnel", d=10), C=12, T=4, seed=301,
+         args=dict(Nleap=8, smin=0.01, smax=0.5, ntry=6, nsteps=2)),
+    dict(name="adhmc_rosen4", model=dict(kind="rosenbrock", d=4), C=12, T=4, seed=302,
+         args=dict(Nleap=10, smin=0.005, smax=0.2, ntry=8, nsteps=1)),
+]
+
+
+def _q0(case, model):
+    q0 = np.random.default_rng(case["seed"] + 1000).uniform(-1, 1, (case["C"], model.d))
+    if case["model"]["kind"] == "rosenbrock":
+        q0 = 1.0 + 0.1 * q0
+    return q0
+
+
+def run_mala(case):
+    mala = ref_loader.load("mala")
+    model = build_model(case["model"])
+    d, C, T = model.d, case["C"], case["T"]
+    P, U = replay.make_draws(case["seed"], T, C, d, 1)
+    q0 = _q0(case, model)
+    ref = mala.MALA(model.log_prob, model.grad_log_prob)
+    q = np.zeros((T, C, d)); Vg = np.zeros((T, C, d)); V = np.zeros((T, C)); code = np.zeros((T, C))
+    with np.errstate(all="ignore"), contextlib.redirect_stdout(io.StringIO()):
+        for c in range(C):
+            qc, Vc, Vgc = q0[c], None, None
+            for t in range(T):
+                with replay.patched_numpy_random(replay.Draws([P[t, c]], U[t, c])):
+                    qc, acc, Vc, Vgc = ref.step(qc, case["eps"], Vc, Vgc)
+                q[t, c], code[t, c], V[t, c], Vg[t, c] = qc, acc, Vc, Vgc
+    np.savez_compressed(os.path.join(OUT, case["name"] + ".npz"), spec=json.dumps(case), q0=q0, P=P, U=U, q=q,
+                        code=code, V=V, Vg=Vg)
+    return code
+
+
+def run_adhmc(case):
+    ad = ref_loader.load("adaptivehmc")
+    model = build_model(case["model"])
+    d, C, T = model.d, case["C"], case["T"]
+    P, U = replay.make_draws(case["seed"], T, C, d, 3)
+    q0 = _q0(case, model)
+    ref = ad.AdHMC_eps0(model.log_prob, model.grad_log_prob)
+    a = case["args"]
+    q = np.zeros((T, C, d)); p = np.zeros((T, C, d)); code = np.zeros((T, C))
+    probs = np.zeros((T, C, 3)); aux = np.zeros((T, C, 3)); counts = np.zeros((T, C, 3), dtype=np.int64)
+    with np.errstate(all="ignore"), contextlib.redirect_stdout(io.StringIO()):
+        for c in range(C):
+            qc = q0[c]
+            for t in range(T):
+                with replay.patched_numpy_random(replay.Draws([P[t, c]], U[t, c])):
+                    out = ref.hmc_step(qc, a["Nleap"], smin=a["smin"], smax=a["smax"], ntry=a["ntry"], nsteps=a["nsteps"])
+                qc = out[0]
+                q[t, c], p[t, c], code[t, c], probs[t, c], aux[t, c], counts[t, c] = out
+    np.savez_compressed(os.path.join(OUT, case["name"] + ".npz"), spec=json.dumps(case), q0=q0, P=P, U=U, q=q, p=p,
+                        code=code, probs=probs, aux=aux, counts=counts)
+    return code
+
+
 def main():
     assert ref_loader.available(), "the reference tree is needed to make goldens"
     os.makedirs(OUT, exist_ok=True)
@@ -93,6 +157,10 @@ def main():
         code = run_case(case)
         vals, n = np.unique(code, return_counts=True)
         print("%-24s codes %s" % (case["name"], dict(zip(vals.tolist(), n.tolist()))))
+    for cases, fn in ((MALA_CASES, run_mala), (ADHMC_CASES, run_adhmc)):
+        for case in cases:
+            vals, n = np.unique(fn(case), return_counts=True)
+            print("%-24s codes %s" % (case["name"], dict(zip(vals.tolist(), n.tolist()))))
 
 
 if __name__ == "__main__":
