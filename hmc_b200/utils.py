@@ -113,31 +113,57 @@ class RunningMoments:
     def reduce(self, true_mean=None):
         """Global (all ranks) [4,d] sums and the global chain count."""
         out = self.engine.moments_reduce(self.sum, self.sumsq, self.n, true_mean)
-        cnt = torch.tensor([float(self.sum.shape[0])], dtype=torch.float64, device=out.device)
-        packed = torch.cat([out.reshape(-1), cnt])
-        dist.all_reduce_sum(packed)
-        return packed[:-1].reshape(4, -1), float(packed[-1])
+        return all_reduce_sums(out, self.sum.shape[0])
 
     def ess_true(self, true_mean, true_std):
-        """utils.get_ess_true over all chains of all ranks: (std/rms)^2 * C with
-        rms^2 = mean_c (mean_t x - mean)^2 (src/utils.py:23-27)."""
+        """utils.get_ess_true over all chains of all ranks (src/utils.py:23-27)."""
         sums, C = self.reduce(true_mean)
-        std = torch.as_tensor(np.asarray(true_std, dtype=np.float64), device=sums.device)
-        return (std ** 2 / (sums[3] / C)) * C
+        return ess_from_sums(sums, C, true_std)
 
     def rhat(self):
-        """Potential scale reduction from per-chain means and variances (Gelman-Rubin;
-        not in the reference's src/, which only calls arviz.rhat in post-processing)."""
         sums, C = self.reduce()
-        T = float(self.n)
-        W = sums[2] / C
-        var_m = (sums[1] - sums[0] ** 2 / C) / (C - 1.0)
-        return torch.sqrt(((T - 1.0) / T * W + var_m) / W)
+        return rhat_from_sums(sums, C, float(self.n))
 
     def mean_std(self):
         """Pooled mean and std over all chains and samples."""
         sums, C = self.reduce()
-        mean = sums[0] / C
-        T = float(self.n)
-        ex2 = (sums[2] * (T - 1.0) / T + sums[1]) / C   # E_c[ biased var + m^2 ]
-        return mean, torch.sqrt(torch.clamp(ex2 - mean ** 2, min=0.0))
+        return mean_std_from_sums(sums, C, float(self.n))
+
+
+def local_moment_sums(x, true_mean=None):
+    """The [4,d] block hmcb_moments_reduce produces, from stored samples x[T,C,d] (torch):
+    sum_c m, sum_c m^2, sum_c s2 (ddof=1), sum_c (m-mu)^2.  Host-side twin used by the
+    CPU (gloo) tests of the cross-rank arithmetic."""
+    m = x.mean(0)
+    s2 = x.var(0, unbiased=True) if x.shape[0] > 1 else torch.zeros_like(m)
+    mu = torch.zeros(x.shape[2], dtype=x.dtype) if true_mean is None else torch.as_tensor(
+        np.asarray(true_mean, dtype=np.float64)).to(x.dtype)
+    return torch.stack([m.sum(0), (m * m).sum(0), s2.sum(0), ((m - mu) ** 2).sum(0)]).to(torch.float64)
+
+
+def all_reduce_sums(sums, n_chains_local):
+    """All-reduce the [4,d] block and the chain count over the process group."""
+    packed = torch.cat([sums.reshape(-1), torch.tensor([float(n_chains_local)], dtype=torch.float64,
+                                                       device=sums.device)])
+    dist.all_reduce_sum(packed)
+    return packed[:-1].reshape(4, -1), float(packed[-1])
+
+
+def ess_from_sums(sums, C, true_std):
+    """(std/rms)^2 * C with rms^2 = mean_c (mean_t x - mean)^2 (src/utils.py:23-27)."""
+    std = torch.as_tensor(np.asarray(true_std, dtype=np.float64), device=sums.device)
+    return (std ** 2 / (sums[3] / C)) * C
+
+
+def rhat_from_sums(sums, C, T):
+    """Potential scale reduction from per-chain means and variances (Gelman-Rubin; not in
+    the reference's src/, which only calls arviz.rhat in post-processing)."""
+    W = sums[2] / C
+    var_m = (sums[1] - sums[0] ** 2 / C) / (C - 1.0)
+    return torch.sqrt(((T - 1.0) / T * W + var_m) / W)
+
+
+def mean_std_from_sums(sums, C, T):
+    mean = sums[0] / C
+    ex2 = (sums[2] * (T - 1.0) / T + sums[1]) / C   # E_c[ biased var + m^2 ]
+    return mean, torch.sqrt(torch.clamp(ex2 - mean ** 2, min=0.0))
