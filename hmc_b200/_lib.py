@@ -12,6 +12,7 @@ MODEL_FUNNEL, MODEL_GAUSSIAN, MODEL_ROSENBROCK, MODEL_LOGISTIC = 0, 1, 2, 3
 RULE_PYHMC, RULE_ALG = 0, 1
 RNG_NORMAL_F64 = 1
 MAX_PROPS = 6
+STATIC_SCRATCH_BYTES = 32 << 20
 
 
 class Model(C.Structure):
@@ -61,6 +62,8 @@ SIGNATURES = {
     "hmcb_drhmc_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
                                   C.c_int32, C.c_double, C.POINTER(StepOut), C.c_void_p, C.c_size_t,
                                   C.POINTER(Profile), C.c_void_p]),
+    "hmcb_drhmc_step_static": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
+                                         C.c_int32, C.c_double, C.POINTER(StepOut), C.c_void_p]),
     "hmcb_moments_accumulate": (C.c_int, [C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_int64, C.c_int64,
                                           C.c_void_p, C.c_void_p, C.c_void_p]),
     "hmcb_moments_reduce": (C.c_int, [C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_double,

@@ -3,6 +3,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "launch.cuh"
 
 namespace hmcb {
@@ -268,6 +270,43 @@ static int adhmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* 
   return e->fn(*m, OP_ADHMC, &a, st);
 }
 
+// ------------------------------------------------------------------ built-in scratch (hmcb_drhmc_step_static)
+// Scratch for callers that cannot supply a workspace.  The name below is only a handle in
+// host code: the device address has to be asked for (once per device, with that device
+// current) and it is that address which goes into the kernel arguments.
+static __device__ __align__(256) unsigned char g_static_scratch[HMCB_STATIC_SCRATCH_BYTES];
+
+// Device code of this file may name the array directly; this clears the stage counters,
+// the only part of the scratch that must start from zero.
+__global__ void k_static_scratch_clear_counters() {
+  if (threadIdx.x < 64) reinterpret_cast<int32_t*>(g_static_scratch)[threadIdx.x] = 0;
+}
+
+static std::mutex g_static_mu;
+static void* g_static_ptr[128];
+static bool g_static_ready[128];
+
+// First use on the current device: resolve and cache the array's device address.
+static int static_scratch_ptr(void** out) {
+  int dev = 0;
+  HMCB_CUDA(cudaGetDevice(&dev));
+  HMCB_CHECK_ARG(dev >= 0 && dev < 128, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_ready[dev]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_static_scratch)");
+    if (p == nullptr) {
+      set_error("built-in scratch has no device address on device %d", dev);
+      return HMCB_E_CUDA;
+    }
+    g_static_ptr[dev] = p;
+    g_static_ready[dev] = true;
+  }
+  *out = g_static_ptr[dev];
+  return 0;
+}
+
 }  // namespace hmcb
 
 using namespace hmcb;
@@ -374,6 +413,42 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
   if (model->dtype == HMCB_F64)
     return drhmc_step_t<double>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, out, workspace, L, profile, st);
   return drhmc_step_t<float>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, out, workspace, L, profile, st);
+}
+
+int hmcb_drhmc_step_static(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
+                           double step_size, int32_t nprops, double stepfactor, const hmcb_step_out* out,
+                           void* stream) {
+  int rc;
+  if ((rc = check_model(model))) return rc;
+  if ((rc = check_chains(chains))) return rc;
+  HMCB_CHECK_ARG(rng != nullptr, "rng is NULL");
+  HMCB_CHECK_ARG(nprops >= 1 && nprops <= kMaxProps, "nprops=%d must be in 1..%d", nprops, kMaxProps);
+  HMCB_CHECK_ARG(stepfactor > 0, "stepfactor must be > 0");
+  HMCB_CHECK_ARG(n_leap >= 0, "n_leap must be >= 0");
+  HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= nprops, "u_inject needs u_stride >= nprops");
+  if (chains->n_chains == 0) return 0;
+  const Entry* e = choose_entry(*model);
+  if (!e) return HMCB_E_UNSUPPORTED;
+  DrLayout L;
+  if ((rc = dr_layout(e, model, chains->n_chains, nprops, L))) return rc;
+  if (L.total > (size_t)HMCB_STATIC_SCRATCH_BYTES) {
+    set_error("built-in scratch too small: n_chains=%lld, d=%d, nprops=%d needs %zu bytes, the library holds %u "
+              "(HMCB_STATIC_SCRATCH_BYTES); split the batch or call hmcb_drhmc_step with your own workspace",
+              (long long)chains->n_chains, model->d, nprops, L.total, (unsigned)HMCB_STATIC_SCRATCH_BYTES);
+    return HMCB_E_WORKSPACE;
+  }
+  void* scratch = nullptr;
+  if ((rc = static_scratch_ptr(&scratch))) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // the previous call's lists and frames are overwritten as they are produced; only the
+  // stage counters are read before being written
+  k_static_scratch_clear_counters<<<1, 64, 0, st>>>();
+  HMCB_CUDA(cudaPeekAtLastError());
+  if (model->dtype == HMCB_F64)
+    return drhmc_step_t<double>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, out, scratch, L,
+                                nullptr, st);
+  return drhmc_step_t<float>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, out, scratch, L, nullptr,
+                             st);
 }
 
 int hmcb_mala_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, double eps,

@@ -132,6 +132,31 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
                     const hmcb_step_out* out, void* workspace, size_t workspace_bytes,
                     const hmcb_profile* profile /* may be NULL */, void* stream);
 
+/* hmcb_drhmc_step without a caller-supplied workspace.  No counterpart in the
+ * reference (its Python never manages device memory); added for hosts that cannot
+ * give us scratch: a thin C / ctypes caller that only holds the q and output buffers
+ * some other framework handed it and has no device allocator of its own, or a process
+ * whose device memory is already fully reserved by the application's pool, or a
+ * sampling loop where cudaMalloc is unwelcome because it synchronises the device.
+ * The stage lists, per-chain running state and proposal frames then live in an array
+ * built into the library, HMCB_STATIC_SCRATCH_BYTES large, which every GPU that loads
+ * libhmcb.so holds until the process exits.  This entry point allocates nothing.
+ *  - Limit: the call is refused (HMCB_E_WORKSPACE, with the byte counts in
+ *    hmcb_last_error()) when hmcb_drhmc_workspace_bytes(model, n_chains, nprops) would
+ *    exceed HMCB_STATIC_SCRATCH_BYTES -- e.g. about 19,000 chains of the d=50 funnel at
+ *    nprops=3.  Larger batches: split them, or use hmcb_drhmc_step.
+ *  - The first call on each device looks up the array's device address and caches it;
+ *    make that first call outside any stream capture.
+ *  - All calls share the one array and it keeps whatever the previous call left; the
+ *    stage counters are cleared at the start of every call, nothing else needs to be.
+ *    Two calls whose kernels can overlap on the GPU (different streams, or two host
+ *    threads on one device) race on it: serialise them.
+ * Same arguments, outputs and results as hmcb_drhmc_step. */
+#define HMCB_STATIC_SCRATCH_BYTES (32u << 20)
+int hmcb_drhmc_step_static(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng,
+                           int32_t n_leap, double step_size, int32_t nprops, double stepfactor,
+                           const hmcb_step_out* out, void* stream);
+
 /* Streamed sample moments (the reference stores samples[T,C,d] and post-processes,
  * src/utils.py:8-27,207-237; at 2^20 chains that does not fit, so each transition is
  * folded into per-chain running sums).  sum/sumsq are contiguous [C,d] (dtype),
