@@ -222,10 +222,18 @@ def run_hmcb(a):
     q = (torch.rand(a.chains, d, generator=g, dtype=torch.float64) * 2 - 1)[lo:hi].to(dev).contiguous()
     nxt = torch.empty_like(q)
 
-    def transition(qi, qo, events=None):
-        return eng.drhmc_step(qi, a.nleap, a.step_size, a.nprops, a.stepfactor, want_p=False, q_out=qo,
-                              stage_events=events, want_avec=False)
+    K = a.steps
+    counts_log = torch.zeros((K + 1, C, 3), dtype=torch.int32, device=dev)   # slot K: scratch for untimed steps
+    code_log = torch.zeros((K + 1, C), dtype=torch.int32, device=dev)
 
+    def transition(qi, qo, events=None, slot=K):
+        # every output buffer is preallocated: no allocator traffic inside the timed loop
+        return eng.drhmc_step(qi, a.nleap, a.step_size, a.nprops, a.stepfactor, want_p=False, q_out=qo,
+                              stage_events=events, want_avec=False, code_out=code_log[slot],
+                              counts_out=counts_log[slot])
+
+    clocks = ClockSampler(local)
+    clocks.start()
     for _ in range(a.burnin):
         transition(q, nxt)
         q, nxt = nxt, q
@@ -252,23 +260,24 @@ def run_hmcb(a):
         mom.add(q)
     mom.reset()
 
-    clocks = ClockSampler(local)
-    clocks.start()
-    time.sleep(0.5)
-    K = a.steps
+    # nvidia-smi was started before burn-in; its start-up (NVML init over every GPU of the box) stalls
+    # kernel launches for a moment, so it must be past that before the timed region begins
+    t_wait = time.time()
+    while len(clocks.rows) < 3 and time.time() - t_wait < 10.0:
+        time.sleep(0.05)
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(a.nprops + 1)] for _ in range(K)]
+    for row in evs:
+        for ev in row:
+            ev.record()      # creates the cudaEvent_t handles now, not inside the timed loop
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    counts_log, code_log = [], []
     dist.barrier()
     torch.cuda.synchronize()
     t_wall0 = time.time()
     start.record()
     for k in range(K):
-        out = transition(q, nxt, evs[k])
+        transition(q, nxt, evs[k], slot=k)
         q, nxt = nxt, q
         mom.add(q)
-        counts_log.append(out["counts"])
-        code_log.append(out["code"])
     end.record()
     torch.cuda.synchronize()
     dist.barrier()
@@ -279,13 +288,11 @@ def run_hmcb(a):
     ms_total = float(ms[0])
     clocks.stop()
 
-    tot = torch.zeros(3, dtype=torch.float64, device=dev)
-    for c in counts_log:
-        tot += c.sum(dim=0, dtype=torch.float64)
+    tot = counts_log[:K].sum(dim=(0, 1), dtype=torch.float64)
     stage_ms = torch.tensor([[evs[k][j].elapsed_time(evs[k][j + 1]) for j in range(a.nprops)] for k in range(K)],
                             dtype=torch.float64, device=dev)
-    n_stage1 = torch.stack([(c != 1).sum() for c in code_log]).double().mean()
-    acc_rate = torch.stack([(c > 0).double().mean() for c in code_log]).mean()
+    n_stage1 = (code_log[:K] != 1).sum(dim=1).double().mean()
+    acc_rate = (code_log[:K] > 0).double().mean()
     stats = torch.cat([tot, stage_ms.mean(dim=0), n_stage1[None], acc_rate[None] * C])
     dist.all_reduce_sum(stats[:3])
     dist.all_reduce_sum(stats[-1:])
@@ -358,6 +365,7 @@ def run_hmcb(a):
             "grad_evals_per_transition": grads / (K * a.chains), "accept_rate": float(stats[-1]) / a.chains,
             "rhat_max": float(rhat.max()), "v_mean": float(mean[0]), "v_std": float(std[0]),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks.summary(t_wall0, t_wall1),
+            "device_busy_frac": (sum(st_ms) + 0.35) / (ms_total / K),
             "gpu_launches": K * (a.nprops + 1),
             "gpu_launches_note": "per step: %d DR stage kernels + 1 moments kernel (all libhmcb.so)" % a.nprops}
     print(json.dumps(line), flush=True)

@@ -149,7 +149,9 @@ class Engine:
         return out
 
     def drhmc_step(self, q, n_leap, step_size, nprops, stepfactor, p=None, u=None, want_p=True, q_out=None,
-                   stage_events=None, want_avec=True):
+                   stage_events=None, want_avec=True, code_out=None, counts_out=None):
+        """hmcb_drhmc_step on device tensor q [C,d].  q_out / code_out / counts_out let a
+        caller reuse its own output buffers (no allocation inside a timed loop)."""
         m = self._ensure()
         C_ = q.shape[0]
         with torch.cuda.device(self.device):
@@ -161,9 +163,10 @@ class Engine:
             q_out = torch.empty_like(q) if q_out is None else q_out
             out = {"q": q_out,
                    "p": torch.empty_like(q) if want_p else None,
-                   "code": torch.empty(C_, dtype=torch.int32, device=self.device),
+                   "code": torch.empty(C_, dtype=torch.int32, device=self.device) if code_out is None else code_out,
                    "avec": torch.empty((C_, nprops), dtype=self.dtype, device=self.device) if want_avec else None,
-                   "counts": torch.empty((C_, 3), dtype=torch.int32, device=self.device)}
+                   "counts": torch.empty((C_, 3), dtype=torch.int32, device=self.device)
+                   if counts_out is None else counts_out}
             so = _lib.StepOut()
             so.p_out, so.code, so.avec = _lib.ptr(out["p"]), _lib.ptr(out["code"]), _lib.ptr(out["avec"])
             so.counts = _lib.ptr(out["counts"])
