@@ -153,6 +153,13 @@ static int hmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c,
   a.nprops = 1;
   a.L[0] = n_leap;
   a.eps[0] = (T)eps;
+  if constexpr (sizeof(T) == 8) {
+    // dense Gaussian, f64, unit metric, d <= 104: gradient on the FP64 tensor path
+    if (m->kind == HMCB_MODEL_GAUSSIAN && !getenv("HMCB_GAUSS_GENERIC")) {
+      const int rc = gauss_dmma_hmc(*m, a, st);
+      if (rc != 1) return rc;
+    }
+  }
   return e->fn(*m, OP_HMC, &a, st);
 }
 

@@ -82,13 +82,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_mala(const Model model, const
       if (a.z_inject) {
         load_vec<T, EPL, LPC>(q1, a.z_inject, off, a.sd, c.lane, d, T(1));
       } else {
-#pragma unroll
-        for (int b = 0; b < Lay::kBlocks; ++b) {
-          const Normal4 n = philox_normal4(a.seed, gchain, a.iteration + (uint32_t)k, (uint32_t)(b * LPC + c.lane), a.rng_flags);
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            if (4 * b + j < EPL) q1[4 * b + j] = (Lay::elem(c.lane, 4 * b + j) < d) ? (T)n.z[j] : T(0);
-        }
+        fill_normals<T, EPL, LPC>(q1, a.seed, gchain, a.iteration + (uint32_t)k, c.lane, d, a.rng_flags);
       }
 #pragma unroll
       for (int s = 0; s < EPL; ++s) {

@@ -110,6 +110,9 @@ constexpr int min_blocks_for() {
 
 int max_optin_smem();  // per-block opt-in shared memory limit of the current device
 
+// gauss_dmma.cu: dense-Gaussian HMC transition on the FP64 tensor path; returns 1 when it does not apply
+int gauss_dmma_hmc(const hmcb_model& hm, const TransArgs<double>& a, cudaStream_t st);
+
 template <class Model, typename T, int EPL, int LPC, bool UNITM, bool GAUSS>
 int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
   constexpr int THREADS = 128;

@@ -60,47 +60,105 @@ struct TransArgs {
 };
 
 // ------------------------------------------------------------------ state movement
+// stride_dim == 1 (row-major [C,d], the API's layout) is special-cased so that element
+// addresses are "row pointer + compile-time offset": no per-element 64-bit index math.
 template <typename T, int EPL, int LPC>
 __device__ __forceinline__ void load_vec(T (&x)[EPL], const T* base, int64_t off, int64_t sd, int lane, int d, T sign) {
+  if (sd == 1) {
+    const T* row = base + off + 4 * lane;
 #pragma unroll
-  for (int s = 0; s < EPL; ++s) {
-    const int i = Layout<EPL, LPC>::elem(lane, s);
-    x[s] = (i < d) ? sign * base[off + i * sd] : T(0);
+    for (int s = 0; s < EPL; ++s) {
+      const int i = Layout<EPL, LPC>::elem(lane, s);
+      x[s] = (i < d) ? sign * row[Layout<EPL, LPC>::elem(0, s)] : T(0);
+    }
+  } else {
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) {
+      const int i = Layout<EPL, LPC>::elem(lane, s);
+      x[s] = (i < d) ? sign * base[off + i * sd] : T(0);
+    }
   }
 }
 
 template <typename T, int EPL, int LPC>
 __device__ __forceinline__ void store_vec(const T (&x)[EPL], T* base, int64_t off, int64_t sd, int lane, int d) {
+  if (sd == 1) {
+    T* row = base + off + 4 * lane;
 #pragma unroll
-  for (int s = 0; s < EPL; ++s) {
-    const int i = Layout<EPL, LPC>::elem(lane, s);
-    if (i < d) base[off + i * sd] = x[s];
+    for (int s = 0; s < EPL; ++s) {
+      const int i = Layout<EPL, LPC>::elem(lane, s);
+      if (i < d) row[Layout<EPL, LPC>::elem(0, s)] = x[s];
+    }
+  } else {
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) {
+      const int i = Layout<EPL, LPC>::elem(lane, s);
+      if (i < d) base[off + i * sd] = x[s];
+    }
   }
 }
 
-// Four standard normals for element block `blk` of a chain.  Kept out of line:
-// it runs once per block per transition, and inlining its log/sincos bodies into
-// every unrolled slot would dwarf the leapfrog loop in code size.
-struct Normal4 { double z[4]; };
-static __device__ __noinline__ Normal4 philox_normal4(uint64_t seed, uint64_t gchain, uint32_t iter, uint32_t blk, int flags) {
-  Normal4 r;
-  uint32_t w[4];
-  if (flags & HMCB_RNG_NORMAL_F64) {
-    double z2[2];
-    Philox::gen(seed, gchain, iter, STREAM_MOMENTUM, 2 * blk, w);
-    normal2_f64(w, z2);
-    r.z[0] = z2[0]; r.z[1] = z2[1];
-    Philox::gen(seed, gchain, iter, STREAM_MOMENTUM, 2 * blk + 1, w);
-    normal2_f64(w, z2);
-    r.z[2] = z2[0]; r.z[3] = z2[1];
-  } else {
-    float z[4];
-    Philox::gen(seed, gchain, iter, STREAM_MOMENTUM, blk, w);
-    normal4_f32(w, z);
+// sum over the chain of (ref[i] - x[i]) -- the reference's "did not move" test
+// (q0-q1).sum()==0, src/pyhmc.py:57 -- with four partial sums (the serial 50-add chain
+// behind 50 loads was 20% of the L=1 kernel).  Caller reduces over the group's lanes.
+template <typename T, int EPL, int LPC>
+__device__ __forceinline__ T diff_sum(const T (&x)[EPL], const T* base, int64_t off, int64_t sd, int lane, int d) {
+  T r[EPL];
+  load_vec<T, EPL, LPC>(r, base, off, sd, lane, d, T(1));
+  T acc[4] = {T(0), T(0), T(0), T(0)};
 #pragma unroll
-    for (int k = 0; k < 4; ++k) r.z[k] = (double)z[k];
+  for (int s = 0; s < EPL; ++s) acc[s & 3] += r[s] - x[s];   // padded slots: 0 - 0
+  return (acc[0] + acc[1]) + (acc[2] + acc[3]);
+}
+
+// Standard normals for every slot of this lane.  The generator runs as a ROLLED loop
+// over the lane's 4-element blocks that parks its output in a small local-memory array,
+// and only then are the values copied into the (compile-time indexed) register slots.
+// Inlining the Philox rounds and log/sincos bodies into every unrolled slot made the
+// kernel 26k instructions; calling an out-of-line function per block instead spilled the
+// ~100 live state registers around each call and cost 0.55 ms per 2^20-chain transition
+// (a quarter of the L=150 kernel).  The loop form has neither problem.
+template <typename T, int EPL, int LPC>
+__device__ __forceinline__ void fill_normals(T (&z)[EPL], uint64_t seed, uint64_t gchain, uint32_t iter, int lane,
+                                             int d, int flags) {
+  constexpr int NB = Layout<EPL, LPC>::kBlocks;
+  if (flags & HMCB_RNG_NORMAL_F64) {
+    double zl[4 * NB];
+#pragma unroll 1
+    for (int b = 0; b < NB; ++b) {
+      const uint32_t blk = (uint32_t)(b * LPC + lane);
+      uint32_t w[4];
+      double z2[2];
+      Philox::gen(seed, gchain, iter, STREAM_MOMENTUM, 2 * blk, w);
+      normal2_f64(w, z2);
+      zl[4 * b] = z2[0]; zl[4 * b + 1] = z2[1];
+      Philox::gen(seed, gchain, iter, STREAM_MOMENTUM, 2 * blk + 1, w);
+      normal2_f64(w, z2);
+      zl[4 * b + 2] = z2[0]; zl[4 * b + 3] = z2[1];
+    }
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) z[s] = (Layout<EPL, LPC>::elem(lane, s) < d) ? (T)zl[s] : T(0);
+  } else {
+    constexpr int UNR = NB >= 4 ? 4 : NB;          // independent blocks in flight per iteration
+    constexpr int NBP = (NB + UNR - 1) / UNR * UNR;
+    float zl[4 * NBP];
+#pragma unroll 1
+    for (int b0 = 0; b0 < NBP; b0 += UNR) {
+      uint32_t w[UNR][4];
+      float z4[UNR][4];
+#pragma unroll
+      for (int j = 0; j < UNR; ++j) Philox::gen(seed, gchain, iter, STREAM_MOMENTUM, (uint32_t)((b0 + j) * LPC + lane), w[j]);
+#pragma unroll
+      for (int j = 0; j < UNR; ++j) normal4_f32(w[j], z4[j]);
+#pragma unroll
+      for (int j = 0; j < UNR; ++j) {
+        zl[4 * (b0 + j)] = z4[j][0]; zl[4 * (b0 + j) + 1] = z4[j][1];
+        zl[4 * (b0 + j) + 2] = z4[j][2]; zl[4 * (b0 + j) + 3] = z4[j][3];
+      }
+    }
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) z[s] = (Layout<EPL, LPC>::elem(lane, s) < d) ? (T)zl[s] : T(0);
   }
-  return r;
 }
 
 // momentum p = z * metricstd, z ~ N(0,1) (src/pyhmc.py:66); z from Philox or injected
@@ -110,14 +168,7 @@ __device__ __forceinline__ void draw_momentum(T (&p)[EPL], const TransArgs<T>& a
   if (a.p_inject) {
     load_vec<T, EPL, LPC>(p, a.p_inject, chain * a.sc, a.sd, lane, d, T(1));
   } else {
-    const uint64_t gchain = (uint64_t)(a.chain_offset + chain);
-#pragma unroll
-    for (int b = 0; b < Layout<EPL, LPC>::kBlocks; ++b) {
-      const Normal4 n = philox_normal4(a.seed, gchain, a.iteration, (uint32_t)(b * LPC + lane), a.rng_flags);
-#pragma unroll
-      for (int k = 0; k < 4; ++k)
-        if (4 * b + k < EPL) p[4 * b + k] = (Layout<EPL, LPC>::elem(lane, 4 * b + k) < d) ? (T)n.z[k] : T(0);
-    }
+    fill_normals<T, EPL, LPC>(p, a.seed, (uint64_t)(a.chain_offset + chain), a.iteration, lane, d, a.rng_flags);
   }
   if (!UNITM) {
 #pragma unroll
@@ -218,8 +269,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
 
     if (MODE != MODE_DRN) {
       // ---------------- single trajectory from (q0, p0): HMC step or DR stage 0
+      draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);  // before q: few live registers
       load_vec<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d, T(1));
-      draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);
       const T K0 = kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
       T V0, V1;
       const int N = a.L[0] > 1 ? a.L[0] : 1;
@@ -228,12 +279,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
       const T H1 = V1 + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
       cH = 2; cVg = N + 1; cLeap = 1;
       // sum(q0 - q1) == 0 is the reference's "did not move" test (src/pyhmc.py:57)
-      T dq = T(0);
-#pragma unroll
-      for (int s = 0; s < EPL; ++s) {
-        const int i = Lay::elem(c.lane, s);
-        if (i < d) dq += a.q_in[qoff + i * a.sd] - q[s];
-      }
+      T dq = diff_sum<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d);
       dq = group_sum_masked<LPC, T>(dq, c.mask);
       T prob = t_exp<T>(H0 - H1);
 
@@ -330,11 +376,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
         cH += 1; cVg += N + 1; cLeap += 1;
         T dq = T(0);
         if (lvl == 0) {
-#pragma unroll
-          for (int s = 0; s < EPL; ++s) {
-            const int i = Lay::elem(c.lane, s);
-            if (i < d) dq += a.q_in[qoff + i * a.sd] - q[s];
-          }
+          dq = diff_sum<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d);
         } else {
           const T* fq = fr + (int64_t)(2 * (lvl - 1)) * EPL * FT;
 #pragma unroll

@@ -48,6 +48,7 @@ int main(int argc, char** argv) {
   const int64_t C = argc > 1 ? atoll(argv[1]) : (1 << 20);
   const int L = argc > 2 ? atoi(argv[2]) : 150;
   const int d = argc > 3 ? atoi(argv[3]) : 50;
+  const int soa = argc > 4 ? atoi(argv[4]) : 0;   // 1: structure-of-arrays [d][C] strides
   const int reps = 5;
   constexpr int THREADS = 128;
   double *q, *qo, *sink;
@@ -59,7 +60,7 @@ int main(int argc, char** argv) {
   hmcb_model hm{}; hm.kind = HMCB_MODEL_FUNNEL; hm.d = d; hm.dtype = HMCB_F64; hm.par[0] = 3.0;
   auto model = FunnelModel<double>::make(hm);
   TransArgs<double> a{};
-  a.n_chains = C; a.d = d; a.q_in = q; a.q_out = qo; a.sc = d; a.sd = 1; a.seed = 1; a.nprops = 1; a.L[0] = L; a.eps[0] = 0.05;
+  a.n_chains = C; a.d = d; a.q_in = q; a.q_out = qo; a.sc = soa ? 1 : d; a.sd = soa ? C : 1; a.seed = 1; a.nprops = 1; a.L[0] = L; a.eps[0] = 0.05;
   auto k = k_transition<FunnelModel<double>, double, KB_EPL, KB_LPC, true, MODE_HMC, THREADS, KB_MINB>;
   int per_sm = 0;
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, THREADS, 0);
@@ -82,8 +83,8 @@ int main(int argc, char** argv) {
   cudaError_t err = cudaDeviceSynchronize();
   const double peak = 2.0 * 148 * 8 * 256 * 4000.0 * 64 / (pk * 1e-3) / 1e12;
   const double ach = (double)C * (L + 1) * 7.0 * d / (best * 1e-3) / 1e12;
-  printf("EPL=%d LPC=%d regs=%d stack=%zu blocks/SM=%d grid=%d  C=%lld L=%d d=%d  %.3f ms  %.2f TF/s algorithmic = %.3f of measured DFMA peak %.2f TF/s  (%s)\n",
-         KB_EPL, KB_LPC, fa.numRegs, fa.localSizeBytes, per_sm, grid, (long long)C, L, d, best, ach, ach / peak, peak,
+  printf("%s EPL=%d LPC=%d regs=%d stack=%zu blocks/SM=%d grid=%d  C=%lld L=%d d=%d  %.3f ms  %.2f TF/s algorithmic = %.3f of measured DFMA peak %.2f TF/s  (%s)\n",
+         soa ? "SoA" : "row-major", KB_EPL, KB_LPC, fa.numRegs, fa.localSizeBytes, per_sm, grid, (long long)C, L, d, best, ach, ach / peak, peak,
          cudaGetErrorString(err));
   return 0;
 }
