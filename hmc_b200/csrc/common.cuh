@@ -117,18 +117,20 @@ __host__ __device__ inline double u53(uint32_t a, uint32_t b) {
   return (double)(((uint64_t)(a >> 5) << 26) | (uint64_t)(b >> 6)) * (1.0 / 9007199254740992.0);
 }
 
-// Four standard normals from one Philox block: Box-Muller on two (u1,u2) pairs,
-// transcendental part in f32 (the FP32/SFU pipes are idle next to the FP64
-// leapfrog).  32-bit radius and angle resolution; |z| <= 6.7.
+// Four standard normals from one Philox block: Box-Muller on two (u1,u2) pairs in f32
+// with the hardware approximations (MUFU lg2 / sqrt / sin / cos; about 13 instructions
+// per pair against ~70 for the libdevice logf/sincospif bodies -- the momentum draw was
+// a third of the L=20 kernel).  Absolute error of a variate ~1e-6, 32-bit radius and
+// angle resolution, |z| <= 6.7: far below Monte Carlo resolution for a momentum refresh.
+// HMCB_RNG_NORMAL_F64 selects the exact f64 generator below instead.
 __device__ __forceinline__ void normal4_f32(const uint32_t (&w)[4], float (&z)[4]) {
 #pragma unroll
   for (int h = 0; h < 2; ++h) {
-    float u1 = ((float)w[2 * h] + 0.5f) * 2.3283064365386963e-10f;  // (0,1]
-    float r = sqrtf(-2.0f * logf(u1));
-    float s, c;
-    sincospif((float)w[2 * h + 1] * 4.656612873077393e-10f, &s, &c);  // angle in [0, 2pi]
-    z[2 * h] = r * c;
-    z[2 * h + 1] = r * s;
+    const float u1 = ((float)w[2 * h] + 0.5f) * 2.3283064365386963e-10f;   // (0,1]
+    const float r = sqrtf(-1.3862943611198906f * __log2f(u1));              // sqrt(-2 ln u1)
+    const float th = (float)w[2 * h + 1] * 1.4629180792671596e-09f;         // 2 pi u2, in [0, 2 pi]
+    z[2 * h] = r * __cosf(th);
+    z[2 * h + 1] = r * __sinf(th);
   }
 }
 

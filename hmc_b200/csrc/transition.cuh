@@ -103,11 +103,24 @@ __device__ __forceinline__ void store_vec(const T (&x)[EPL], T* base, int64_t of
 // behind 50 loads was 20% of the L=1 kernel).  Caller reduces over the group's lanes.
 template <typename T, int EPL, int LPC>
 __device__ __forceinline__ T diff_sum(const T (&x)[EPL], const T* base, int64_t off, int64_t sd, int lane, int d) {
-  T r[EPL];
-  load_vec<T, EPL, LPC>(r, base, off, sd, lane, d, T(1));
   T acc[4] = {T(0), T(0), T(0), T(0)};
+  const T* row = base + off + (sd == 1 ? 4 * lane : 0);
+  // chunks of 8 loads keep the extra live registers small: the state already fills the file
 #pragma unroll
-  for (int s = 0; s < EPL; ++s) acc[s & 3] += r[s] - x[s];   // padded slots: 0 - 0
+  for (int s0 = 0; s0 < EPL; s0 += 8) {
+    T r[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int s = s0 + k;
+      if (s < EPL) {
+        const int i = Layout<EPL, LPC>::elem(lane, s);
+        r[k] = (i < d) ? (sd == 1 ? row[Layout<EPL, LPC>::elem(0, s)] : base[off + i * sd]) : T(0);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      if (s0 + k < EPL) acc[k & 3] += r[k] - x[s0 + k];   // padded slots: 0 - 0
+  }
   return (acc[0] + acc[1]) + (acc[2] + acc[3]);
 }
 
@@ -269,8 +282,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
 
     if (MODE != MODE_DRN) {
       // ---------------- single trajectory from (q0, p0): HMC step or DR stage 0
-      draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);  // before q: few live registers
-      load_vec<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d, T(1));
+      load_vec<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d, T(1));    // loads in flight under the RNG
+      draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);
       const T K0 = kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
       T V0, V1;
       const int N = a.L[0] > 1 ? a.L[0] : 1;
