@@ -180,6 +180,15 @@ class DRHMC(HMC):
         """Returns (q, p, code, avec, [Hcount, Vgcount, leapcount]); code = j+1 if
         accepted at stage j, else 0 (src/algorithms.py:500-530)."""
         e = self.engine
+        if torch.is_tensor(q) and q.device.type == "cpu" and q.dim() == 2 and p is None and u is None \
+                and q.shape[0] >= 8192:
+            # host-resident batch: chunked copy/compute pipeline (same results, see Engine.drhmc_step_host)
+            e._ensure()
+            if q.shape[1] != self.model.d:
+                raise ValueError("q has dimension %d but the model has d=%d" % (q.shape[1], self.model.d))
+            h = e.drhmc_step_host(q.to(e.dtype), nleap, step_size, nprops, stepfactor)
+            self.Hcount, self.Vgcount, self.leapcount = h["counts"][:, 0], h["counts"][:, 1], h["counts"][:, 2]
+            return h["q"], h["p"], h["code"], h["avec"], h["counts"]
         b = self._device_q(q)
         out = e.drhmc_step(b.q, nleap, step_size, nprops, stepfactor, p=p, u=u)
         if b.unbatched:

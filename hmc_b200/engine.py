@@ -76,7 +76,9 @@ class Engine:
         self.rng_flags = _lib.RNG_NORMAL_F64 if rng_f64 else 0
         self._struct = None
         self._keep = None
-        self._ws = None
+        self._ws = None          # adhmc scratch
+        self._ws_pool = {}       # drhmc scratch, one per concurrent stream slot
+        self._streams = None
         self.device = None
 
     # ------------------------------------------------------------------ set-up
@@ -95,9 +97,9 @@ class Engine:
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
-    def _chains(self, q_in, q_out):
+    def _chains(self, q_in, q_out, extra_offset=0):
         c = _lib.Chains()
-        c.n_chains, c.chain_offset = q_in.shape[0], self.chain_offset
+        c.n_chains, c.chain_offset = q_in.shape[0], self.chain_offset + int(extra_offset)
         c.q_in, c.q_out = q_in.data_ptr(), q_out.data_ptr()
         c.stride_chain, c.stride_dim = q_in.stride(0), q_in.stride(1)
         return c
@@ -149,7 +151,8 @@ class Engine:
         return out
 
     def drhmc_step(self, q, n_leap, step_size, nprops, stepfactor, p=None, u=None, want_p=True, q_out=None,
-                   stage_events=None, want_avec=True, code_out=None, counts_out=None):
+                   stage_events=None, want_avec=True, code_out=None, counts_out=None, extra_offset=0, ws_slot=0,
+                   advance=True):
         """hmcb_drhmc_step on device tensor q [C,d].  q_out / code_out / counts_out let a
         caller reuse its own output buffers (no allocation inside a timed loop)."""
         m = self._ensure()
@@ -158,8 +161,9 @@ class Engine:
             need = self.lib.hmcb_drhmc_workspace_bytes(C.byref(m), C_, int(nprops))
             if need == 0:
                 _lib.check(_lib.E_ARG)
-            if self._ws is None or self._ws.numel() < need:
-                self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+            ws = self._ws_pool.get(ws_slot)
+            if ws is None or ws.numel() < need:
+                ws = self._ws_pool[ws_slot] = torch.empty(need, dtype=torch.uint8, device=self.device)
             q_out = torch.empty_like(q) if q_out is None else q_out
             out = {"q": q_out,
                    "p": torch.empty_like(q) if want_p else None,
@@ -170,15 +174,57 @@ class Engine:
             so = _lib.StepOut()
             so.p_out, so.code, so.avec = _lib.ptr(out["p"]), _lib.ptr(out["code"]), _lib.ptr(out["avec"])
             so.counts = _lib.ptr(out["counts"])
-            ch = self._chains(q, q_out)
+            ch = self._chains(q, q_out, extra_offset)
             r, keep = self._rng(p, u, nprops, C_)
             _lib.check(self.lib.hmcb_drhmc_step(C.byref(m), C.byref(ch), C.byref(r), int(n_leap), float(step_size),
                                                 int(nprops), float(stepfactor), C.byref(so),
-                                                C.c_void_p(self._ws.data_ptr()), self._ws.numel(),
+                                                C.c_void_p(ws.data_ptr()), ws.numel(),
                                                 self._profile(stage_events), self._stream()))
-        self.iteration += 1
+        if advance:
+            self.iteration += 1
         out["_keep"] = keep
         return out
+
+    def drhmc_step_host(self, q_host, n_leap, step_size, nprops, stepfactor, want_p=True, n_chunks=8):
+        """One DR transition for chain state living in HOST memory: the batch is cut into
+        chunks of chains that flow H2D copy -> stage kernels -> D2H copy on three streams, so
+        the copy engines (one per direction) and the SMs work at the same time.  Chains are
+        independent and draws are keyed by global chain id, so the result is bit-identical to
+        the one-shot call.  q_host: CPU tensor [C,d] (pinned for full copy speed); returns
+        pinned CPU tensors."""
+        m = self._ensure()
+        C_, d = q_host.shape
+        n_chunks = max(1, min(int(n_chunks), (C_ + 4095) // 4096))
+        pin = dict(pin_memory=True)
+        host = {"q": torch.empty((C_, d), dtype=self.dtype, **pin),
+                "p": torch.empty((C_, d), dtype=self.dtype, **pin) if want_p else None,
+                "code": torch.empty(C_, dtype=torch.int32, **pin),
+                "avec": torch.empty((C_, nprops), dtype=self.dtype, **pin),
+                "counts": torch.empty((C_, 3), dtype=torch.int32, **pin)}
+        if self._streams is None:
+            with torch.cuda.device(self.device):
+                self._streams = [torch.cuda.Stream(device=self.device) for _ in range(3)]
+        cur = torch.cuda.current_stream(self.device)
+        bounds = [(i * C_) // n_chunks for i in range(n_chunks + 1)]
+        for st in self._streams:
+            st.wait_stream(cur)
+        for i in range(n_chunks):
+            lo, hi = bounds[i], bounds[i + 1]
+            if hi == lo:
+                continue
+            st = self._streams[i % 3]
+            with torch.cuda.stream(st):
+                qd = torch.empty((hi - lo, d), dtype=self.dtype, device=self.device)
+                qd.copy_(q_host[lo:hi], non_blocking=True)
+                out = self.drhmc_step(qd, n_leap, step_size, nprops, stepfactor, want_p=want_p, extra_offset=lo,
+                                      ws_slot=i % 3, advance=False)
+                for k in ("q", "p", "code", "avec", "counts"):
+                    if host[k] is not None:
+                        host[k][lo:hi].copy_(out[k], non_blocking=True)
+        for st in self._streams:
+            st.synchronize()
+        self.iteration += 1
+        return host
 
     def mala_step(self, q, eps, n_steps=1, V=None, Vg=None, z=None, u=None, q_out=None):
         """hmcb_mala_step on device tensor q [C,d]; V [C] / Vg [C,d] are the cached
