@@ -1,0 +1,371 @@
+// logreg.cuh -- Bayesian logistic-regression gradient on the 5th-generation tensor cores
+// (tcgen05.mma, accumulators in TMEM).  This is the one model where chains x data is a
+// real dense GEMM:   Z = Theta X^T  ->  R = sigmoid(Z) - y  ->  G = R X   (+ prior term),
+// shaped like attention with K = V = X and a sigmoid in place of the softmax:
+//
+//   per CTA: one tile of 128 chains (TMEM lanes), one slab of data rows, walked in blocks
+//   of 128 rows.  Per block:
+//     GEMM1  Z^T[128 chains x 128 rows] = Theta[128 x D] * X_blk^T      (A, B from smem)
+//     epilogue: Z^T TMEM -> registers (thread = chain) -> r = sigmoid(z) - y -> fp16 hi/lo
+//               -> back to TMEM as the A operand of GEMM2; log-likelihood summed per thread
+//     GEMM2  G[128 chains x D] += R^T[128 x 128 rows] * X_blk           (A from TMEM, B from smem)
+//   Z and R never touch shared or global memory.
+//
+// Precision: operands are split x = hi + lo with hi, lo in fp16 after a power-of-two
+// pre-scaling (per matrix for X, per chain for Theta, fixed for R), and each product is
+// three MMAs, hi*hi + hi*lo + lo*hi, into one fp32 accumulator: ~2^-21 relative operand
+// error at the fp16 tensor rate, half the shared-memory footprint of a 3xTF32 scheme.
+//
+// Shared-memory operand layout: the no-swizzle canonical "core matrix" tiling of the
+// UMMA descriptors -- 8 rows x 16 bytes (8 fp16), 128 B per core matrix.  An X block is
+// stored once, as cm(row_blk, dim_blk) at (dim_blk*16 + row_blk)*128 B, and is read by
+// GEMM1 as a K-major B operand (MN = rows, K = dims: SBO = 128, LBO = 2048) and by GEMM2
+// as an MN-major B operand (MN = dims, K = rows: SBO = 2048, LBO = 128): the 8x8 core
+// matrix has the same bytes under both readings.
+#pragma once
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+
+namespace hmcb {
+namespace lr {
+
+constexpr int kD = 128;        // padded feature dimension (K of GEMM1, N of GEMM2)
+constexpr int kTileC = 128;    // chains per CTA (M of both GEMMs = TMEM lanes)
+constexpr int kTileR = 128;    // data rows per block (N of GEMM1, K of GEMM2)
+constexpr int kRScaleLog2 = 10;  // residual r in (-1,1) is stored as r * 2^10
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// D[tmem] (+)= A[smem] * B[smem]
+__device__ __forceinline__ void mma_ss(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem]
+__device__ __forceinline__ void mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// 32 lanes x 32 consecutive 32-bit columns: thread t of the warp gets lane (base lane + t)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};" ::
+          "r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+      "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+      "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// ------------------------------------------------------------------ descriptors
+// shared-memory matrix descriptor, no swizzle (layout_type 0), version 1 (Blackwell)
+__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;
+}
+// instruction descriptor: fp16 x fp16 -> fp32, M x N, majors (0 = K-major, 1 = MN-major)
+__host__ __device__ constexpr uint32_t instr_desc(int M, int N, int a_major, int b_major) {
+  return (1u << 4)              // c_format = F32
+         | (0u << 7)            // a_format = F16
+         | (0u << 10)           // b_format = F16
+         | ((uint32_t)a_major << 15) | ((uint32_t)b_major << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// byte offset of element (row, col) of a [rows x 128] fp16 operand in the core-matrix tiling
+__host__ __device__ __forceinline__ uint32_t cm_offset(int row, int col) {
+  return (uint32_t)(((col >> 3) * 16 + (row >> 3)) * 128 + (row & 7) * 16 + (col & 7) * 2);
+}
+
+struct GradArgs {
+  const __half* Xh;      // [n_rows_pad][kD] pre-split, pre-scaled by 2^x_scale_log2
+  const __half* Xl;
+  const float* y;        // [n_rows_pad]
+  const float* theta;    // [n_chains][d] fp32
+  float* Gpart;          // [n_slabs][n_chains][kD]
+  float* Vpart;          // [n_slabs][n_chains] or nullptr
+  int64_t n_chains;
+  int32_t d;             // true feature count (<= kD)
+  int32_t n_rows;        // true row count
+  int32_t rows_per_slab; // multiple of kTileR
+  int32_t n_slabs;
+  int32_t x_scale_log2;
+};
+
+// One CTA = (chain tile, slab).  128 threads: thread t <-> chain t of the tile <-> TMEM lane t.
+template <bool WANT_V>
+__global__ void __launch_bounds__(128, 1) k_logreg_grad(const GradArgs a) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  __half* sTh = reinterpret_cast<__half*>(smem);             // 32 KB Theta hi
+  __half* sTl = sTh + kTileC * kD;                            // 32 KB Theta lo
+  __half* sXh = sTl + kTileC * kD;                            // 32 KB X block hi
+  __half* sXl = sXh + kTileR * kD;                            // 32 KB X block lo
+  float* sY = reinterpret_cast<float*>(sXl + kTileR * kD);    // 512 B
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sY + kTileR);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 2);
+
+  const int t = threadIdx.x, warp = t >> 5;
+  const int tile = blockIdx.x, slab = blockIdx.y;
+  const int64_t chain = (int64_t)tile * kTileC + t;
+  const bool live = chain < a.n_chains;
+
+  if (warp == 0) tmem_alloc(tmem_slot, 512);
+  if (t == 0) {
+    mbar_init(bar, 1);
+    fence_barrier_init();
+  }
+  // Theta tile: thread = chain; per-chain power-of-two scale so that max |theta'| ~ 2^9
+  float tmax = 0.f;
+  const float* th = a.theta + (live ? chain : 0) * a.d;
+  for (int k = 0; k < a.d; ++k) tmax = fmaxf(tmax, fabsf(th[k]));
+  int te = 0;
+  if (tmax > 0.f) {
+    int ex;
+    frexpf(tmax, &ex);      // tmax = m * 2^ex, m in [0.5,1)
+    te = 10 - ex;
+  }
+  const float tscale = ldexpf(1.0f, te);
+  for (int k = 0; k < kD; ++k) {
+    const float v = (live && k < a.d) ? th[k] * tscale : 0.f;
+    const __half h = __float2half_rn(v);
+    const __half l = __float2half_rn(v - __half2float(h));
+    const uint32_t off = cm_offset(t, k);
+    *reinterpret_cast<__half*>(reinterpret_cast<unsigned char*>(sTh) + off) = h;
+    *reinterpret_cast<__half*>(reinterpret_cast<unsigned char*>(sTl) + off) = l;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tZ = tmem;            // 128 columns: Z^T accumulator
+  const uint32_t tPh = tmem + 128;     // 64 columns: R^T hi (fp16 pairs)
+  const uint32_t tPl = tmem + 192;     // 64 columns: R^T lo
+  const uint32_t tG = tmem + 256;      // 128 columns: G accumulator
+  const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
+
+  const float zscale = ldexpf(1.0f, -(a.x_scale_log2 + te));
+  const float rscale = ldexpf(1.0f, kRScaleLog2);
+  constexpr uint32_t idesc1 = instr_desc(kTileC, kTileR, 0, 0);   // Theta (K-major) x X_blk (K-major)
+  constexpr uint32_t idesc2 = instr_desc(kTileC, kD, 0, 1);       // R^T (TMEM) x X_blk (MN-major)
+
+  const int row0 = slab * a.rows_per_slab;
+  const int row1 = min(row0 + a.rows_per_slab, (a.n_rows + kTileR - 1) / kTileR * kTileR);
+  float vsum = 0.f;
+  uint32_t parity = 0;
+  bool first = true;
+  for (int rb = row0; rb < row1; rb += kTileR) {
+    // ---- stage the X block (hi and lo) in the core-matrix tiling: 16-byte chunks = 8 dims of one row
+    for (int c = t; c < kTileR * (kD / 8); c += 128) {
+      const int r = c >> 4, db = c & 15;             // row in block, dim block
+      const uint4 vh = *reinterpret_cast<const uint4*>(a.Xh + (size_t)(rb + r) * kD + db * 8);
+      const uint4 vl = *reinterpret_cast<const uint4*>(a.Xl + (size_t)(rb + r) * kD + db * 8);
+      const uint32_t off = (uint32_t)((db * 16 + (r >> 3)) * 128 + (r & 7) * 16);
+      *reinterpret_cast<uint4*>(reinterpret_cast<unsigned char*>(sXh) + off) = vh;
+      *reinterpret_cast<uint4*>(reinterpret_cast<unsigned char*>(sXl) + off) = vl;
+    }
+    if (t < kTileR) sY[t] = a.y[rb + t];
+    fence_proxy_async();
+    __syncthreads();
+
+    // ---- GEMM1: Z^T = Theta_hi X_hi^T + Theta_hi X_lo^T + Theta_lo X_hi^T
+    if (t == 0) {
+      tc_fence_after();
+      const uint32_t aTh = smem_u32(sTh), aTl = smem_u32(sTl), aXh = smem_u32(sXh), aXl = smem_u32(sXl);
+#pragma unroll
+      for (int kk = 0; kk < kD / 16; ++kk) {
+        const uint32_t ko = (uint32_t)kk * 2 * 2048;     // two core matrices along K per MMA
+        mma_ss(tZ, smem_desc(aTh + ko, 2048, 128), smem_desc(aXh + ko, 2048, 128), idesc1, kk > 0);
+      }
+#pragma unroll
+      for (int kk = 0; kk < kD / 16; ++kk) {
+        const uint32_t ko = (uint32_t)kk * 2 * 2048;
+        mma_ss(tZ, smem_desc(aTh + ko, 2048, 128), smem_desc(aXl + ko, 2048, 128), idesc1, 1);
+      }
+#pragma unroll
+      for (int kk = 0; kk < kD / 16; ++kk) {
+        const uint32_t ko = (uint32_t)kk * 2 * 2048;
+        mma_ss(tZ, smem_desc(aTl + ko, 2048, 128), smem_desc(aXh + ko, 2048, 128), idesc1, 1);
+      }
+      tc_commit(bar);
+    }
+    mbar_wait(bar, parity);
+    parity ^= 1;
+    tc_fence_after();
+
+    // ---- epilogue: thread = chain; 128 data rows in 4 chunks of 32 columns
+#pragma unroll 1
+    for (int ch = 0; ch < 4; ++ch) {
+      uint32_t zr[32];
+      tmem_ld32(tZ + lane_base + ch * 32, zr);
+      tmem_ld_wait();
+      uint32_t ph[16], pl[16];
+#pragma unroll
+      for (int j = 0; j < 32; j += 2) {
+        float rr[2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int row = rb + ch * 32 + j + e;
+          const float z = __uint_as_float(zr[j + e]) * zscale;
+          const float yv = sY[ch * 32 + j + e];
+          const float ez = __expf(-fabsf(z));                    // in (0,1]
+          const float sig_abs = 1.0f / (1.0f + ez);              // sigmoid(|z|)
+          const float sig = z >= 0.f ? sig_abs : 1.0f - sig_abs;
+          const bool ok = row < a.n_rows;
+          rr[e] = ok ? (sig - yv) * rscale : 0.f;
+          if (WANT_V && ok) vsum += (fmaxf(z, 0.f) + log1pf(ez)) - yv * z;   // softplus(z) - y z
+        }
+        const __half h0 = __float2half_rn(rr[0]), h1 = __float2half_rn(rr[1]);
+        const __half l0 = __float2half_rn(rr[0] - __half2float(h0)), l1 = __float2half_rn(rr[1] - __half2float(h1));
+        ph[j >> 1] = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
+        pl[j >> 1] = (uint32_t)__half_as_ushort(l0) | ((uint32_t)__half_as_ushort(l1) << 16);
+      }
+      // 32 data rows = 16 packed fp16x2 columns per chunk
+      asm volatile(
+          "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(
+              tPh + lane_base + ch * 16),
+          "r"(ph[0]), "r"(ph[1]), "r"(ph[2]), "r"(ph[3]), "r"(ph[4]), "r"(ph[5]), "r"(ph[6]), "r"(ph[7]), "r"(ph[8]),
+          "r"(ph[9]), "r"(ph[10]), "r"(ph[11]), "r"(ph[12]), "r"(ph[13]), "r"(ph[14]), "r"(ph[15])
+          : "memory");
+      asm volatile(
+          "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(
+              tPl + lane_base + ch * 16),
+          "r"(pl[0]), "r"(pl[1]), "r"(pl[2]), "r"(pl[3]), "r"(pl[4]), "r"(pl[5]), "r"(pl[6]), "r"(pl[7]), "r"(pl[8]),
+          "r"(pl[9]), "r"(pl[10]), "r"(pl[11]), "r"(pl[12]), "r"(pl[13]), "r"(pl[14]), "r"(pl[15])
+          : "memory");
+    }
+    tmem_st_wait();
+    tc_fence_before();
+    __syncthreads();
+
+    // ---- GEMM2: G += R_hi X_hi + R_hi X_lo + R_lo X_hi     (K = 128 rows, 16 per MMA = 8 TMEM columns)
+    if (t == 0) {
+      tc_fence_after();
+      const uint32_t aXh = smem_u32(sXh), aXl = smem_u32(sXl);
+#pragma unroll
+      for (int kk = 0; kk < kTileR / 16; ++kk) {
+        const uint32_t ko = (uint32_t)kk * 2 * 128;      // two core matrices along K (= rows) per MMA
+        mma_ts(tG, tPh + kk * 8, smem_desc(aXh + ko, 128, 2048), idesc2, (!first || kk > 0) ? 1 : 0);
+      }
+#pragma unroll
+      for (int kk = 0; kk < kTileR / 16; ++kk) {
+        const uint32_t ko = (uint32_t)kk * 2 * 128;
+        mma_ts(tG, tPh + kk * 8, smem_desc(aXl + ko, 128, 2048), idesc2, 1);
+      }
+#pragma unroll
+      for (int kk = 0; kk < kTileR / 16; ++kk) {
+        const uint32_t ko = (uint32_t)kk * 2 * 128;
+        mma_ts(tG, tPl + kk * 8, smem_desc(aXh + ko, 128, 2048), idesc2, 1);
+      }
+      tc_commit(bar);
+    }
+    // the X block and R are free again only when GEMM2 has read them
+    mbar_wait(bar, parity);
+    parity ^= 1;
+    tc_fence_after();
+    first = false;
+  }
+
+  // ---- write this slab's partial gradient: G' = G * 2^(r_scale + x_scale)
+  const float gscale = ldexpf(1.0f, -(kRScaleLog2 + a.x_scale_log2));
+  float* gout = a.Gpart + ((size_t)slab * a.n_chains + (live ? chain : 0)) * kD;
+#pragma unroll 1
+  for (int ch = 0; ch < 4; ++ch) {
+    uint32_t gr[32];
+    if (!first) {
+      tmem_ld32(tG + lane_base + ch * 32, gr);
+      tmem_ld_wait();
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) gr[j] = 0u;
+    }
+    if (live) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) {
+        float4 o;
+        o.x = __uint_as_float(gr[j]) * gscale; o.y = __uint_as_float(gr[j + 1]) * gscale;
+        o.z = __uint_as_float(gr[j + 2]) * gscale; o.w = __uint_as_float(gr[j + 3]) * gscale;
+        *reinterpret_cast<float4*>(gout + ch * 32 + j) = o;
+      }
+    }
+  }
+  if (WANT_V && live && a.Vpart) a.Vpart[(size_t)slab * a.n_chains + chain] = vsum;
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+// X (fp32 [n_rows][d]) -> Xh, Xl (fp16 [n_rows_pad][kD]) with x' = x * 2^x_scale_log2
+__global__ void k_logreg_prep(const float* __restrict__ X, int n_rows, int d, int n_rows_pad, int x_scale_log2,
+                              __half* __restrict__ Xh, __half* __restrict__ Xl) {
+  const float s = ldexpf(1.0f, x_scale_log2);
+  const size_t n = (size_t)n_rows_pad * kD;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / kD), k = (int)(i % kD);
+    const float v = (r < n_rows && k < d) ? X[(size_t)r * d + k] * s : 0.f;
+    const __half h = __float2half_rn(v);
+    Xh[i] = h;
+    Xl[i] = __float2half_rn(v - __half2float(h));
+  }
+}
+
+}  // namespace lr
+}  // namespace hmcb
