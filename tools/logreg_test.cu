@@ -60,6 +60,39 @@ int main(int argc, char** argv) {
     float ms; cudaEventElapsedTime(&ms, e0, e1); if (ms < best) best = ms;
   }
   CK(cudaGetLastError());
+  // ---- pipelined kernel (v1): pre-tiled X
+  {
+    const int nblk = Npad / kTileR;
+    __half *dXhb, *dXlb;
+    CK(cudaMalloc(&dXhb, (size_t)nblk * kTileR * kD * 2)); CK(cudaMalloc(&dXlb, (size_t)nblk * kTileR * kD * 2));
+    k_logreg_prep_blk<<<256, 256>>>(dX, N, d, nblk, xs, dXhb, dXlb);
+    CK(cudaGetLastError());
+    GradArgsV1 b{};
+    b.Xh_blk = dXhb; b.Xl_blk = dXlb; b.y = dy; b.theta = dth; b.Gpart = dG; b.Vpart = dV; b.n_chains = C; b.d = d; b.n_rows = N;
+    b.n_blocks = nblk; b.blocks_per_slab = (nblk + slabs - 1) / slabs; b.n_slabs = slabs; b.x_scale_log2 = xs;
+    const size_t smem1 = 6 * 32768 + 2 * 512 + 512 + 512 + 16 * 8 + 64;
+    const int mode = argc > 6 ? atoi(argv[6]) : 0;   // 0: V + 3 products, 1: no V + 3 products, 2: no V + 1 product
+    auto launch = [&] {
+      if (mode == 0) k_logreg_grad_v1<true, 3><<<grid, kThreadsV1, smem1>>>(b);
+      else if (mode == 1) k_logreg_grad_v1<false, 3><<<grid, kThreadsV1, smem1>>>(b);
+      else k_logreg_grad_v1<false, 1><<<grid, kThreadsV1, smem1>>>(b);
+    };
+    CK(cudaFuncSetAttribute(k_logreg_grad_v1<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+    CK(cudaFuncSetAttribute(k_logreg_grad_v1<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+    CK(cudaFuncSetAttribute(k_logreg_grad_v1<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+    CK(cudaMemset(dG, 0, (size_t)slabs * C * kD * 4));
+    float b1 = 1e30f;
+    for (int r = 0; r < reps; ++r) {
+      cudaEventRecord(e0);
+      launch();
+      cudaEventRecord(e1);
+      CK(cudaEventSynchronize(e1));
+      float ms; cudaEventElapsedTime(&ms, e0, e1); if (ms < b1) b1 = ms;
+    }
+    CK(cudaGetLastError());
+    printf("v1 mode %d: %.3f ms  (v0 %.3f ms)\n", mode, b1, best);
+    best = b1;
+  }
   std::vector<float> G((size_t)slabs * C * kD), V((size_t)slabs * C);
   CK(cudaMemcpy(G.data(), dG, G.size() * 4, cudaMemcpyDeviceToHost));
   CK(cudaMemcpy(V.data(), dV, V.size() * 4, cudaMemcpyDeviceToHost));
