@@ -74,6 +74,13 @@ SIGNATURES = {
     "hmcb_adhmc_eps0_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32,
                                        C.POINTER(C.c_double), C.c_int32, C.c_int32, C.POINTER(AdhmcOut), C.c_void_p,
                                        C.c_size_t, C.c_void_p]),
+    "hmcb_logreg_prepared_bytes": (C.c_size_t, [C.POINTER(Model)]),
+    "hmcb_logreg_prepare": (C.c_int, [C.POINTER(Model), C.c_void_p, C.c_size_t, C.c_void_p]),
+    "hmcb_logreg_workspace_bytes": (C.c_size_t, [C.POINTER(Model), C.c_int64]),
+    "hmcb_logreg_hmc_step": (C.c_int, [C.POINTER(Model), C.c_void_p, C.POINTER(Chains), C.POINTER(Rng), C.c_int32,
+                                       C.c_double, C.c_int32, C.POINTER(StepOut), C.c_void_p, C.c_size_t, C.c_void_p]),
+    "hmcb_logreg_logp_grad": (C.c_int, [C.POINTER(Model), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
+                                        C.c_void_p, C.c_size_t, C.c_void_p]),
     "hmcb_probe_fma": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.POINTER(C.c_double),
                                  C.c_void_p]),
 }

@@ -136,225 +136,8 @@ __host__ __device__ __forceinline__ uint32_t cm_offset(int row, int col) {
   return (uint32_t)(((col >> 3) * 16 + (row >> 3)) * 128 + (row & 7) * 16 + (col & 7) * 2);
 }
 
-struct GradArgs {
-  const __half* Xh;      // [n_rows_pad][kD] pre-split, pre-scaled by 2^x_scale_log2
-  const __half* Xl;
-  const float* y;        // [n_rows_pad]
-  const float* theta;    // [n_chains][d] fp32
-  float* Gpart;          // [n_slabs][n_chains][kD]
-  float* Vpart;          // [n_slabs][n_chains] or nullptr
-  int64_t n_chains;
-  int32_t d;             // true feature count (<= kD)
-  int32_t n_rows;        // true row count
-  int32_t rows_per_slab; // multiple of kTileR
-  int32_t n_slabs;
-  int32_t x_scale_log2;
-};
-
-// One CTA = (chain tile, slab).  128 threads: thread t <-> chain t of the tile <-> TMEM lane t.
-template <bool WANT_V>
-__global__ void __launch_bounds__(128, 1) k_logreg_grad(const GradArgs a) {
-  extern __shared__ __align__(1024) unsigned char smem[];
-  __half* sTh = reinterpret_cast<__half*>(smem);             // 32 KB Theta hi
-  __half* sTl = sTh + kTileC * kD;                            // 32 KB Theta lo
-  __half* sXh = sTl + kTileC * kD;                            // 32 KB X block hi
-  __half* sXl = sXh + kTileR * kD;                            // 32 KB X block lo
-  float* sY = reinterpret_cast<float*>(sXl + kTileR * kD);    // 512 B
-  uint64_t* bar = reinterpret_cast<uint64_t*>(sY + kTileR);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 2);
-
-  const int t = threadIdx.x, warp = t >> 5;
-  const int tile = blockIdx.x, slab = blockIdx.y;
-  const int64_t chain = (int64_t)tile * kTileC + t;
-  const bool live = chain < a.n_chains;
-
-  if (warp == 0) tmem_alloc(tmem_slot, 512);
-  if (t == 0) {
-    mbar_init(bar, 1);
-    fence_barrier_init();
-  }
-  // Theta tile: thread = chain; per-chain power-of-two scale so that max |theta'| ~ 2^9
-  float tmax = 0.f;
-  const float* th = a.theta + (live ? chain : 0) * a.d;
-  for (int k = 0; k < a.d; ++k) tmax = fmaxf(tmax, fabsf(th[k]));
-  int te = 0;
-  if (tmax > 0.f) {
-    int ex;
-    frexpf(tmax, &ex);      // tmax = m * 2^ex, m in [0.5,1)
-    te = 10 - ex;
-  }
-  const float tscale = ldexpf(1.0f, te);
-  for (int k = 0; k < kD; ++k) {
-    const float v = (live && k < a.d) ? th[k] * tscale : 0.f;
-    const __half h = __float2half_rn(v);
-    const __half l = __float2half_rn(v - __half2float(h));
-    const uint32_t off = cm_offset(t, k);
-    *reinterpret_cast<__half*>(reinterpret_cast<unsigned char*>(sTh) + off) = h;
-    *reinterpret_cast<__half*>(reinterpret_cast<unsigned char*>(sTl) + off) = l;
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
-  const uint32_t tZ = tmem;            // 128 columns: Z^T accumulator
-  const uint32_t tPh = tmem + 128;     // 64 columns: R^T hi (fp16 pairs)
-  const uint32_t tPl = tmem + 192;     // 64 columns: R^T lo
-  const uint32_t tG = tmem + 256;      // 128 columns: G accumulator
-  const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
-
-  const float zscale = ldexpf(1.0f, -(a.x_scale_log2 + te));
-  const float rscale = ldexpf(1.0f, kRScaleLog2);
-  constexpr uint32_t idesc1 = instr_desc(kTileC, kTileR, 0, 0);   // Theta (K-major) x X_blk (K-major)
-  constexpr uint32_t idesc2 = instr_desc(kTileC, kD, 0, 1);       // R^T (TMEM) x X_blk (MN-major)
-
-  const int row0 = slab * a.rows_per_slab;
-  const int row1 = min(row0 + a.rows_per_slab, (a.n_rows + kTileR - 1) / kTileR * kTileR);
-  float vsum = 0.f;
-  uint32_t parity = 0;
-  bool first = true;
-  for (int rb = row0; rb < row1; rb += kTileR) {
-    // ---- stage the X block (hi and lo) in the core-matrix tiling: 16-byte chunks = 8 dims of one row
-    for (int c = t; c < kTileR * (kD / 8); c += 128) {
-      const int r = c >> 4, db = c & 15;             // row in block, dim block
-      const uint4 vh = *reinterpret_cast<const uint4*>(a.Xh + (size_t)(rb + r) * kD + db * 8);
-      const uint4 vl = *reinterpret_cast<const uint4*>(a.Xl + (size_t)(rb + r) * kD + db * 8);
-      const uint32_t off = (uint32_t)((db * 16 + (r >> 3)) * 128 + (r & 7) * 16);
-      *reinterpret_cast<uint4*>(reinterpret_cast<unsigned char*>(sXh) + off) = vh;
-      *reinterpret_cast<uint4*>(reinterpret_cast<unsigned char*>(sXl) + off) = vl;
-    }
-    if (t < kTileR) sY[t] = a.y[rb + t];
-    fence_proxy_async();
-    __syncthreads();
-
-    // ---- GEMM1: Z^T = Theta_hi X_hi^T + Theta_hi X_lo^T + Theta_lo X_hi^T
-    if (t == 0) {
-      tc_fence_after();
-      const uint32_t aTh = smem_u32(sTh), aTl = smem_u32(sTl), aXh = smem_u32(sXh), aXl = smem_u32(sXl);
-#pragma unroll
-      for (int kk = 0; kk < kD / 16; ++kk) {
-        const uint32_t ko = (uint32_t)kk * 2 * 2048;     // two core matrices along K per MMA
-        mma_ss(tZ, smem_desc(aTh + ko, 2048, 128), smem_desc(aXh + ko, 2048, 128), idesc1, kk > 0);
-      }
-#pragma unroll
-      for (int kk = 0; kk < kD / 16; ++kk) {
-        const uint32_t ko = (uint32_t)kk * 2 * 2048;
-        mma_ss(tZ, smem_desc(aTh + ko, 2048, 128), smem_desc(aXl + ko, 2048, 128), idesc1, 1);
-      }
-#pragma unroll
-      for (int kk = 0; kk < kD / 16; ++kk) {
-        const uint32_t ko = (uint32_t)kk * 2 * 2048;
-        mma_ss(tZ, smem_desc(aTl + ko, 2048, 128), smem_desc(aXh + ko, 2048, 128), idesc1, 1);
-      }
-      tc_commit(bar);
-    }
-    mbar_wait(bar, parity);
-    parity ^= 1;
-    tc_fence_after();
-
-    // ---- epilogue: thread = chain; 128 data rows in 4 chunks of 32 columns
-#pragma unroll 1
-    for (int ch = 0; ch < 4; ++ch) {
-      uint32_t zr[32];
-      tmem_ld32(tZ + lane_base + ch * 32, zr);
-      tmem_ld_wait();
-      uint32_t ph[16], pl[16];
-#pragma unroll
-      for (int j = 0; j < 32; j += 2) {
-        float rr[2];
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-          const int row = rb + ch * 32 + j + e;
-          const float z = __uint_as_float(zr[j + e]) * zscale;
-          const float yv = sY[ch * 32 + j + e];
-          const float ez = __expf(-fabsf(z));                    // in (0,1]
-          const float sig_abs = 1.0f / (1.0f + ez);              // sigmoid(|z|)
-          const float sig = z >= 0.f ? sig_abs : 1.0f - sig_abs;
-          const bool ok = row < a.n_rows;
-          rr[e] = ok ? (sig - yv) * rscale : 0.f;
-          if (WANT_V && ok) vsum += (fmaxf(z, 0.f) + log1pf(ez)) - yv * z;   // softplus(z) - y z
-        }
-        const __half h0 = __float2half_rn(rr[0]), h1 = __float2half_rn(rr[1]);
-        const __half l0 = __float2half_rn(rr[0] - __half2float(h0)), l1 = __float2half_rn(rr[1] - __half2float(h1));
-        ph[j >> 1] = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
-        pl[j >> 1] = (uint32_t)__half_as_ushort(l0) | ((uint32_t)__half_as_ushort(l1) << 16);
-      }
-      // 32 data rows = 16 packed fp16x2 columns per chunk
-      asm volatile(
-          "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(
-              tPh + lane_base + ch * 16),
-          "r"(ph[0]), "r"(ph[1]), "r"(ph[2]), "r"(ph[3]), "r"(ph[4]), "r"(ph[5]), "r"(ph[6]), "r"(ph[7]), "r"(ph[8]),
-          "r"(ph[9]), "r"(ph[10]), "r"(ph[11]), "r"(ph[12]), "r"(ph[13]), "r"(ph[14]), "r"(ph[15])
-          : "memory");
-      asm volatile(
-          "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(
-              tPl + lane_base + ch * 16),
-          "r"(pl[0]), "r"(pl[1]), "r"(pl[2]), "r"(pl[3]), "r"(pl[4]), "r"(pl[5]), "r"(pl[6]), "r"(pl[7]), "r"(pl[8]),
-          "r"(pl[9]), "r"(pl[10]), "r"(pl[11]), "r"(pl[12]), "r"(pl[13]), "r"(pl[14]), "r"(pl[15])
-          : "memory");
-    }
-    tmem_st_wait();
-    tc_fence_before();
-    __syncthreads();
-
-    // ---- GEMM2: G += R_hi X_hi + R_hi X_lo + R_lo X_hi     (K = 128 rows, 16 per MMA = 8 TMEM columns)
-    if (t == 0) {
-      tc_fence_after();
-      const uint32_t aXh = smem_u32(sXh), aXl = smem_u32(sXl);
-#pragma unroll
-      for (int kk = 0; kk < kTileR / 16; ++kk) {
-        const uint32_t ko = (uint32_t)kk * 2 * 128;      // two core matrices along K (= rows) per MMA
-        mma_ts(tG, tPh + kk * 8, smem_desc(aXh + ko, 128, 2048), idesc2, (!first || kk > 0) ? 1 : 0);
-      }
-#pragma unroll
-      for (int kk = 0; kk < kTileR / 16; ++kk) {
-        const uint32_t ko = (uint32_t)kk * 2 * 128;
-        mma_ts(tG, tPh + kk * 8, smem_desc(aXl + ko, 128, 2048), idesc2, 1);
-      }
-#pragma unroll
-      for (int kk = 0; kk < kTileR / 16; ++kk) {
-        const uint32_t ko = (uint32_t)kk * 2 * 128;
-        mma_ts(tG, tPl + kk * 8, smem_desc(aXh + ko, 128, 2048), idesc2, 1);
-      }
-      tc_commit(bar);
-    }
-    // the X block and R are free again only when GEMM2 has read them
-    mbar_wait(bar, parity);
-    parity ^= 1;
-    tc_fence_after();
-    first = false;
-  }
-
-  // ---- write this slab's partial gradient: G' = G * 2^(r_scale + x_scale)
-  const float gscale = ldexpf(1.0f, -(kRScaleLog2 + a.x_scale_log2));
-  float* gout = a.Gpart + ((size_t)slab * a.n_chains + (live ? chain : 0)) * kD;
-#pragma unroll 1
-  for (int ch = 0; ch < 4; ++ch) {
-    uint32_t gr[32];
-    if (!first) {
-      tmem_ld32(tG + lane_base + ch * 32, gr);
-      tmem_ld_wait();
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j) gr[j] = 0u;
-    }
-    if (live) {
-#pragma unroll
-      for (int j = 0; j < 32; j += 4) {
-        float4 o;
-        o.x = __uint_as_float(gr[j]) * gscale; o.y = __uint_as_float(gr[j + 1]) * gscale;
-        o.z = __uint_as_float(gr[j + 2]) * gscale; o.w = __uint_as_float(gr[j + 3]) * gscale;
-        *reinterpret_cast<float4*>(gout + ch * 32 + j) = o;
-      }
-    }
-  }
-  if (WANT_V && live && a.Vpart) a.Vpart[(size_t)slab * a.n_chains + chain] = vsum;
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 512);
-}
-
 // ------------------------------------------------------------------ pipelined kernel
-// Warp-specialised version of the above: warp 0 streams X blocks (pre-tiled in global
+// Warp-specialised: warp 0 streams X blocks (pre-tiled in global
 // memory, one 32 KB bulk copy per matrix per block) into a 2-stage shared-memory ring,
 // warp 1 issues the MMAs, 16 epilogue warps (4 per TMEM lane quarter, one 32-row chunk
 // each) turn Z into R in place in TMEM.  Z/R is double-buffered in TMEM so that the
@@ -366,6 +149,8 @@ constexpr int kEpiWarps = 16;
 constexpr int kThreadsV1 = 32 * (2 + kEpiWarps);
 constexpr int kFlush = 8;
 constexpr uint32_t kBlkBytes = kTileR * kD * 2;   // one fp16 operand block
+// dynamic shared memory of k_logreg_grad_v1: Theta hi/lo, 2 X stages x hi/lo, y ring, V sums, scales, barriers
+constexpr size_t kSmemV1 = 6 * (size_t)kBlkBytes + 2 * kTileR * 4 + kTileC * 8 + kTileC * 4 + 16 * 8 + 64;
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -392,11 +177,12 @@ struct GradArgsV1 {
   const float* y;        // [n_blocks*kTileR]
   const float* theta;    // [n_chains][d] fp32
   float* Gpart;          // [n_slabs][n_chains][kD]
-  float* Vpart;          // [n_slabs][n_chains] or nullptr
+  double* Vpart;         // [n_slabs][n_chains] or nullptr (sum of softplus(z) - y z over the slab's rows)
   int64_t n_chains;
   int32_t d, n_rows;
   int32_t blocks_per_slab, n_blocks, n_slabs;
-  int32_t x_scale_log2;
+  int32_t x_scale_log2;  // used when x_scale_dev == nullptr
+  const int32_t* x_scale_dev;  // device copy of the scale exponent (written by the prepare step)
 };
 
 template <bool WANT_V, int NPROD>
@@ -406,7 +192,7 @@ __global__ void __launch_bounds__(kThreadsV1, 1) k_logreg_grad_v1(const GradArgs
   unsigned char* sTl = sTh + kBlkBytes;              // 32 KB
   unsigned char* sX = sTl + kBlkBytes;               // 2 stages x (hi 32 KB + lo 32 KB)
   float* sY = reinterpret_cast<float*>(sX + 4 * kBlkBytes);     // 2 x 128 floats
-  float* sV = sY + 2 * kTileR;                                    // 128 floats
+  double* sV = reinterpret_cast<double*>(sY + 2 * kTileR);        // 128 doubles
   int* sTe = reinterpret_cast<int*>(sV + kTileC);                 // 128 ints: per-chain scale exponent
   uint64_t* bars = reinterpret_cast<uint64_t*>(sTe + kTileC);
   uint64_t *x_full = bars, *x_empty = bars + 2, *z_full = bars + 4, *p_full = bars + 6, *zp_empty = bars + 8,
@@ -432,7 +218,8 @@ __global__ void __launch_bounds__(kThreadsV1, 1) k_logreg_grad_v1(const GradArgs
     mbar_init(g_empty, kEpiWarps);
     fence_barrier_init();
   }
-  if (t < kTileC) sV[t] = 0.f;
+  if (t < kTileC) sV[t] = 0.0;
+  const int xs_log2 = a.x_scale_dev ? *a.x_scale_dev : a.x_scale_log2;
   // Theta tile -> fp16 hi/lo in the core-matrix tiling; one warp per chain row, 8 rows per warp
   if (warp >= 2) {
     const int ew = warp - 2;
@@ -547,12 +334,12 @@ __global__ void __launch_bounds__(kThreadsV1, 1) k_logreg_grad_v1(const GradArgs
     const int q = warp & 3, cq = ew >> 2;
     const int r = q * 32 + lane;                       // chain row in the tile = TMEM lane
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
-    const float zscale = ldexpf(1.0f, -(a.x_scale_log2 + sTe[r]));
+    const float zscale = ldexpf(1.0f, -(xs_log2 + sTe[r]));
     const float rscale = ldexpf(1.0f, kRScaleLog2);
     float gacc[32];
 #pragma unroll
     for (int j = 0; j < 32; ++j) gacc[j] = 0.f;
-    float vsum = 0.f;
+    double vsum = 0.0;
     for (int i = 0; i < nb; ++i) {
       const int s = i & 1, u = i >> 1;
       mbar_wait(z_full + s, u & 1);
@@ -575,7 +362,11 @@ __global__ void __launch_bounds__(kThreadsV1, 1) k_logreg_grad_v1(const GradArgs
           const float sig = fast_sigmoid(z, ez);
           const bool ok = row_base + j + e < a.n_rows;
           rr[e] = ok ? (sig - yv) * rscale : 0.f;
-          if (WANT_V && ok) vsum += (fmaxf(z, 0.f) + log1pf(ez)) - yv * z;
+          if (WANT_V && ok) {
+            float l2;
+            asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l2) : "f"(1.0f + ez));
+            vsum += (double)(fmaf(0.6931471805599453f, l2, fmaxf(z, 0.f)) - yv * z);   // softplus(z) - y z
+          }
         }
         const __half2 h2 = __floats2half2_rn(rr[0], rr[1]);
         const float2 hf = __half22float2(h2);
@@ -614,7 +405,7 @@ __global__ void __launch_bounds__(kThreadsV1, 1) k_logreg_grad_v1(const GradArgs
     }
     const int64_t chain = (int64_t)tile * kTileC + r;
     if (chain < a.n_chains) {
-      const float gscale = ldexpf(1.0f, -(kRScaleLog2 + a.x_scale_log2));
+      const float gscale = ldexpf(1.0f, -(kRScaleLog2 + xs_log2));
       float* gout = a.Gpart + ((size_t)slab * a.n_chains + chain) * kD + cq * 32;
 #pragma unroll
       for (int j = 0; j < 32; j += 4)
@@ -634,8 +425,9 @@ __global__ void __launch_bounds__(kThreadsV1, 1) k_logreg_grad_v1(const GradArgs
 
 // X (fp32 [n_rows][d]) -> pre-tiled fp16 hi/lo blocks for the pipelined kernel
 __global__ void k_logreg_prep_blk(const float* __restrict__ X, int n_rows, int d, int n_blocks, int x_scale_log2,
-                                  __half* __restrict__ Xh, __half* __restrict__ Xl) {
-  const float s = ldexpf(1.0f, x_scale_log2);
+                                  const int32_t* __restrict__ x_scale_dev, __half* __restrict__ Xh,
+                                  __half* __restrict__ Xl) {
+  const float s = ldexpf(1.0f, x_scale_dev ? *x_scale_dev : x_scale_log2);
   const size_t n = (size_t)n_blocks * kTileR * kD;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     const size_t blk = i / (kTileR * kD);
@@ -647,20 +439,6 @@ __global__ void k_logreg_prep_blk(const float* __restrict__ X, int n_rows, int d
     const size_t o = blk * (kTileR * kD) + cm_offset(r, k) / 2;
     Xh[o] = h;
     Xl[o] = __float2half_rn(v - __half2float(h));
-  }
-}
-
-// X (fp32 [n_rows][d]) -> Xh, Xl (fp16 [n_rows_pad][kD]) with x' = x * 2^x_scale_log2
-__global__ void k_logreg_prep(const float* __restrict__ X, int n_rows, int d, int n_rows_pad, int x_scale_log2,
-                              __half* __restrict__ Xh, __half* __restrict__ Xl) {
-  const float s = ldexpf(1.0f, x_scale_log2);
-  const size_t n = (size_t)n_rows_pad * kD;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-    const int r = (int)(i / kD), k = (int)(i % kD);
-    const float v = (r < n_rows && k < d) ? X[(size_t)r * d + k] * s : 0.f;
-    const __half h = __float2half_rn(v);
-    Xh[i] = h;
-    Xl[i] = __float2half_rn(v - __half2float(h));
   }
 }
 

@@ -63,8 +63,13 @@ class Engine:
     scratch buffers, and wraps each C-ABI entry point."""
 
     def __init__(self, log_prob, grad_log_prob=None, log_prob_and_grad=None, invmetric_diag=None, device=None,
-                 dtype=torch.float64, seed=0, chain_offset=0, rng_f64=False):
+                 dtype=None, seed=0, chain_offset=0, rng_f64=False):
         self.model = as_model(log_prob, grad_log_prob, log_prob_and_grad)
+        self.is_logistic = self.model.kind == _lib.MODEL_LOGISTIC
+        if dtype is None:   # the reference computes in float64; the tensor-core logistic gradient is float32
+            dtype = torch.float32 if self.is_logistic else torch.float64
+        if self.is_logistic and dtype != torch.float32:
+            raise ValueError("LogisticRegression runs in float32 (tensor-core gradient): pass dtype=torch.float32")
         if dtype not in (torch.float64, torch.float32):
             raise ValueError("dtype must be torch.float64 or torch.float32")
         self.dtype = dtype
@@ -87,7 +92,28 @@ class Engine:
             self.device = _require_cuda(self._device_arg)
             self.lib = _lib.load()
             self._struct, self._keep = self.model.to_struct(self.device, self.dtype, self.invmetric_diag)
+            if self.is_logistic:
+                self._prepare_logistic()
         return self._struct
+
+    def _prepare_logistic(self):
+        """Build the fp16 operand blocks of X once (hmcb_logreg_prepare)."""
+        m = self._struct
+        with torch.cuda.device(self.device):
+            need = self.lib.hmcb_logreg_prepared_bytes(C.byref(m))
+            if need == 0:
+                _lib.check(_lib.E_ARG)
+            self._lr_prepared = torch.empty(need, dtype=torch.uint8, device=self.device)
+            _lib.check(self.lib.hmcb_logreg_prepare(C.byref(m), C.c_void_p(self._lr_prepared.data_ptr()), need,
+                                                    self._stream()))
+
+    def _lr_workspace(self, n_chains):
+        need = self.lib.hmcb_logreg_workspace_bytes(C.byref(self._struct), int(n_chains))
+        if need == 0:
+            _lib.check(_lib.E_ARG)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        return self._ws
 
     @property
     def dev(self):
@@ -144,8 +170,15 @@ class Engine:
             so.counts, so.accept_prob = _lib.ptr(out["counts"]), _lib.ptr(out["prob"])
             ch = self._chains(q, q_out)
             r, keep = self._rng(p, u, 1, C_)
-            _lib.check(self.lib.hmcb_hmc_step(C.byref(m), C.byref(ch), C.byref(r), int(n_leap), float(step_size),
-                                              int(rule), C.byref(so), self._stream()))
+            if self.is_logistic:
+                ws = self._lr_workspace(C_)
+                _lib.check(self.lib.hmcb_logreg_hmc_step(C.byref(m), C.c_void_p(self._lr_prepared.data_ptr()),
+                                                         C.byref(ch), C.byref(r), int(n_leap), float(step_size),
+                                                         int(rule), C.byref(so), C.c_void_p(ws.data_ptr()), ws.numel(),
+                                                         self._stream()))
+            else:
+                _lib.check(self.lib.hmcb_hmc_step(C.byref(m), C.byref(ch), C.byref(r), int(n_leap), float(step_size),
+                                                  int(rule), C.byref(so), self._stream()))
         self.iteration += 1
         out["_keep"] = keep
         return out
@@ -322,6 +355,15 @@ class Engine:
 
     def logp_grad(self, q):
         m = self._ensure()
+        if self.is_logistic:
+            with torch.cuda.device(self.device):
+                logp = torch.empty(q.shape[0], dtype=self.dtype, device=self.device)
+                grad = torch.empty_like(q)
+                ws = self._lr_workspace(q.shape[0])
+                _lib.check(self.lib.hmcb_logreg_logp_grad(C.byref(m), C.c_void_p(self._lr_prepared.data_ptr()),
+                                                          _lib.ptr(q), q.shape[0], _lib.ptr(logp), _lib.ptr(grad),
+                                                          C.c_void_p(ws.data_ptr()), ws.numel(), self._stream()))
+            return logp, grad
         with torch.cuda.device(self.device):
             logp = torch.empty(q.shape[0], dtype=self.dtype, device=self.device)
             grad = torch.empty_like(q)

@@ -205,6 +205,28 @@ int hmcb_adhmc_eps0_step(const hmcb_model* model, const hmcb_chains* chains, con
                          const double* steps, int32_t ntry, int32_t nsteps, const hmcb_adhmc_out* out,
                          void* workspace, size_t workspace_bytes, void* stream);
 
+/* Bayesian logistic regression, log p = sum_i [y_i z_i - softplus(z_i)] - |theta|^2/(2 tau^2),
+ * z = X theta (builder-defined model): float32 chains, the
+ * gradient X^T(sigmoid(X theta) - y) for all chains at once on the tcgen05 tensor cores
+ * (hmc_b200/csrc/logreg.cuh).  model: kind LOGISTIC, dtype F32, d <= 128, n_data rows,
+ * par[0] = tau, dev0 = X float32 [n_data, d] row-major, dev1 = y float32 [n_data].
+ *  - hmcb_logreg_prepare: once per data set, builds the fp16 hi/lo operand blocks of X in a
+ *    caller-owned buffer of hmcb_logreg_prepared_bytes().
+ *  - hmcb_logreg_hmc_step: one HMC transition per chain, same semantics and outputs as
+ *    hmcb_hmc_step (replaces pyhmc.HMC.step / algorithms.HMC.step, src/pyhmc.py:64-69,
+ *    src/algorithms.py:192-198); chain state must be contiguous row-major [C, d] float32;
+ *    energies are accumulated in float64 and returned as float32.
+ *  - hmcb_logreg_logp_grad: log_prob [C] and grad_log_prob [C, d] (the model plug-in pair,
+ *    src/algorithms.py:81-89). */
+size_t hmcb_logreg_prepared_bytes(const hmcb_model* model);
+int hmcb_logreg_prepare(const hmcb_model* model, void* prepared, size_t prepared_bytes, void* stream);
+size_t hmcb_logreg_workspace_bytes(const hmcb_model* model, int64_t n_chains);
+int hmcb_logreg_hmc_step(const hmcb_model* model, const void* prepared, const hmcb_chains* chains,
+                         const hmcb_rng* rng, int32_t n_leap, double step_size, int32_t rule,
+                         const hmcb_step_out* out, void* workspace, size_t workspace_bytes, void* stream);
+int hmcb_logreg_logp_grad(const hmcb_model* model, const void* prepared, const void* theta, int64_t n_chains,
+                          void* logp, void* grad, void* workspace, size_t workspace_bytes, void* stream);
+
 /* Measurement probe: a register-resident dependent-FMA loop (FP64 or FP32) used
  * to measure the pipe peak that roofline fractions are quoted against.
  * Launches `blocks` x `threads`, each thread doing iters*ilp*unroll FMAs; writes

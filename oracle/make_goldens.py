@@ -150,6 +150,35 @@ def run_adhmc(case):
     return code
 
 
+def run_logistic():
+    """pyhmc.HMC.step on the Bayesian logistic-regression model (float64 reference arithmetic on
+    float32-representable data); the GPU path runs in float32 and is held to 1e-5."""
+    pyhmc = ref_loader.load("pyhmc")
+    rng = np.random.default_rng(401)
+    N, d, C, T = 3000, 24, 12, 3
+    X = (rng.standard_normal((N, d)) / np.sqrt(d)).astype(np.float32)
+    theta_star = rng.standard_normal(d)
+    y = (rng.random(N) < 1.0 / (1.0 + np.exp(-(X.astype(np.float64) @ theta_star)))).astype(np.float32)
+    model = models.LogisticRegression(X.astype(np.float64), y.astype(np.float64), 1.0)
+    ref = pyhmc.HMC(model.log_prob, model.grad_log_prob)
+    P, U = replay.make_draws(402, T, C, d, 1)
+    P = P.astype(np.float32).astype(np.float64)       # momenta exactly representable in float32
+    q0 = (0.1 * rng.standard_normal((C, d))).astype(np.float32).astype(np.float64)
+    args = dict(N=10, step_size=0.01)
+    q = np.zeros((T, C, d)); p = np.zeros((T, C, d)); code = np.zeros((T, C)); Hs = np.zeros((T, C, 2))
+    counts = np.zeros((T, C, 3), dtype=np.int64)
+    for c in range(C):
+        qc = q0[c]
+        for t in range(T):
+            with replay.patched_numpy_random(replay.Draws([P[t, c]], U[t, c])):
+                out = ref.step(qc, args["N"], args["step_size"])
+            qc = out[0]
+            q[t, c], p[t, c], code[t, c], Hs[t, c], counts[t, c] = out
+    np.savez_compressed(os.path.join(OUT, "logit_hmc.npz"), spec=json.dumps(dict(args=args, tau=1.0)), X=X, y=y, q0=q0, P=P,
+                        U=U, q=q, p=p, code=code, Hs=Hs, counts=counts)
+    return code
+
+
 def main():
     assert ref_loader.available(), "the reference tree is needed to make goldens"
     os.makedirs(OUT, exist_ok=True)
@@ -157,6 +186,8 @@ def main():
         code = run_case(case)
         vals, n = np.unique(code, return_counts=True)
         print("%-24s codes %s" % (case["name"], dict(zip(vals.tolist(), n.tolist()))))
+    vals, n = np.unique(run_logistic(), return_counts=True)
+    print("%-24s codes %s" % ("logit_hmc", dict(zip(vals.tolist(), n.tolist()))))
     for cases, fn in ((MALA_CASES, run_mala), (ADHMC_CASES, run_adhmc)):
         for case in cases:
             vals, n = np.unique(fn(case), return_counts=True)
