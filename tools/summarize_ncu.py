@@ -17,6 +17,7 @@ def short(name):
     if m:
         mode = {"0": "HMC", "1": "DR stage 0", "2": "DR stage>=1"}[m.group(6)]
         return "hmcb::k_transition<%s,%s,EPL=%s,LPC=%s> [%s]" % (m.group(1), m.group(2), m.group(3), m.group(4), mode)
+    name = name.replace("hmcb::lr::", "hmcb::lr::").replace("(bool)", "").replace("(int)", "")
     return re.sub(r"\(.*", "", name)[:100]
 
 
@@ -52,7 +53,14 @@ WANT = ["gpu__time_duration.sum", "launch__registers_per_thread", "launch__grid_
         "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio",
         "smsp__sass_inst_executed_op_local_ld.sum", "smsp__sass_inst_executed_op_local_st.sum",
-        "sm__sass_inst_executed_op_local_ld.sum", "sm__sass_inst_executed_op_local_st.sum"]
+        "sm__sass_inst_executed_op_local_ld.sum", "sm__sass_inst_executed_op_local_st.sum",
+        "TPC.TriageCompute.sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed",
+        "TPC.TriageCompute.sm__pipe_tensor_subpipe_hmma_cycles_active_realtime.avg",
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_tensor_subpipe_hmma.avg.pct_of_peak_sustained_active",
+        "sm__issue_active.avg.pct_of_peak_sustained_elapsed", "sm__cycles_active.avg",
+        "smsp__inst_executed_pipe_xu.sum", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
+        "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "lts__t_bytes.sum"]
 
 
 def full(src, dst):
