@@ -10,6 +10,7 @@ OK, E_ARG, E_UNSUPPORTED, E_CUDA, E_WORKSPACE = 0, -1, -2, -3, -4
 F64, F32 = 0, 1
 MODEL_FUNNEL, MODEL_GAUSSIAN, MODEL_ROSENBROCK, MODEL_LOGISTIC = 0, 1, 2, 3
 RULE_PYHMC, RULE_ALG = 0, 1
+DR_ALGORITHMS, DR_MULTISTEP = 0, 1
 RNG_NORMAL_F64 = 1
 MAX_PROPS = 6
 STATIC_SCRATCH_BYTES = 32 << 20
@@ -27,7 +28,13 @@ class Chains(C.Structure):
 
 class Rng(C.Structure):
     _fields_ = [("seed", C.c_uint64), ("iteration", C.c_uint64), ("p_inject", C.c_void_p), ("u_inject", C.c_void_p),
-                ("u_stride", C.c_int32), ("flags", C.c_int32)]
+                ("u_stride", C.c_int32), ("flags", C.c_int32), ("p_prev", C.c_void_p), ("alpha", C.c_double)]
+
+
+class GhmcIO(C.Structure):
+    _fields_ = [("p_out", C.c_void_p), ("V_in", C.c_void_p), ("Vg_in", C.c_void_p), ("V_out", C.c_void_p),
+                ("Vg_out", C.c_void_p), ("u_in", C.c_void_p), ("u_out", C.c_void_p), ("delta", C.c_double),
+                ("code", C.c_void_p), ("energies", C.c_void_p), ("counts", C.c_void_p)]
 
 
 class Profile(C.Structure):
@@ -60,16 +67,18 @@ SIGNATURES = {
     "hmcb_logp_grad": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.c_void_p, C.c_void_p, C.c_void_p]),
     "hmcb_drhmc_workspace_bytes": (C.c_size_t, [C.POINTER(Model), C.c_int64, C.c_int32]),
     "hmcb_drhmc_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
-                                  C.c_int32, C.c_double, C.POINTER(StepOut), C.c_void_p, C.c_size_t,
+                                  C.c_int32, C.c_double, C.c_int32, C.POINTER(StepOut), C.c_void_p, C.c_size_t,
                                   C.POINTER(Profile), C.c_void_p]),
     "hmcb_drhmc_step_static": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
-                                         C.c_int32, C.c_double, C.POINTER(StepOut), C.c_void_p]),
+                                         C.c_int32, C.c_double, C.c_int32, C.POINTER(StepOut), C.c_void_p]),
     "hmcb_moments_accumulate": (C.c_int, [C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_int64, C.c_int64,
                                           C.c_void_p, C.c_void_p, C.c_void_p]),
     "hmcb_moments_reduce": (C.c_int, [C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_double,
                                       C.c_void_p, C.c_void_p, C.c_void_p]),
     "hmcb_mala_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_double, C.c_int32,
                                  C.POINTER(MalaIO), C.c_void_p]),
+    "hmcb_ghmc_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
+                                 C.POINTER(GhmcIO), C.c_void_p]),
     "hmcb_adhmc_eps0_workspace_bytes": (C.c_size_t, [C.POINTER(Model), C.c_int64]),
     "hmcb_adhmc_eps0_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32,
                                        C.POINTER(C.c_double), C.c_int32, C.c_int32, C.POINTER(AdhmcOut), C.c_void_p,

@@ -220,13 +220,159 @@ class DRHMC(HMC):
         return state
 
 
+class GHMC(HMC):
+    """Generalised HMC, algorithms.GHMC (src/algorithms.py:259-303): the momentum is only partly
+    refreshed, p <- alpha p + sqrt(1-alpha^2) pn, and comes back flipped unless the proposal is
+    accepted; V(q) and grad V(q) are carried between transitions.  Work counters follow the
+    reference built as GHMC(log_prob, grad_log_prob, log_prob_and_grad)."""
+
+    def _as_dev(self, x, b):
+        if x is None:
+            return None
+        t = torch.as_tensor(np.asarray(x)) if not torch.is_tensor(x) else x
+        return t.reshape(b.C, -1).to(device=self.engine.device, dtype=self.engine.dtype).contiguous()
+
+    def step(self, q, p, nleap, step_size, alpha, V_q=None, V_gq=None, pn=None, u=None):
+        """Returns (q, p, V_q, V_gq, accepted, Hs, counts) (src/algorithms.py:265-281)."""
+        e = self.engine
+        b = self._device_q(q)
+        V = None if V_q is None else torch.as_tensor(np.asarray(V_q) if not torch.is_tensor(V_q) else V_q).reshape(-1).to(
+            device=e.device, dtype=e.dtype).contiguous()
+        out = e.ghmc_step(b.q, self._as_dev(p, b), nleap, step_size, alpha, V=V, Vg=self._as_dev(V_gq, b), pn=pn, u=u)
+        code = out["code"].to(torch.float64)
+        if b.unbatched:
+            cnt = out["counts"][0].tolist()
+            self.Hcount, self.Vgcount, self.leapcount = cnt
+            return (b.out(out["q"]), b.out(out["p"]), float(out["V"][0]), b.out(out["Vg"]), float(code[0]),
+                    out["Hs"][0].tolist(), cnt)
+        self.Hcount, self.Vgcount, self.leapcount = out["counts"][:, 0], out["counts"][:, 1], out["counts"][:, 2]
+        return (b.out(out["q"]), b.out(out["p"]), b.out(out["V"]), b.out(out["Vg"]), b.out(code), b.out(out["Hs"]),
+                b.out(out["counts"]))
+
+    def sample(self, q, p=None, callback=None, **kwargs):
+        """src/algorithms.py:284-303: every iteration is stored; p starts as a fresh normal draw."""
+        self._parse_kwargs_sample(**kwargs)
+        state = Sampler()
+        b = self._device_q(q)
+        qd = b.q
+        pd = torch.randn(qd.shape, dtype=qd.dtype, device=qd.device) if p is None else self._as_dev(p, b)
+        V, Vg = None, None
+        for i in range(self.nsamples + self.burnin):
+            out = self.engine.ghmc_step(qd, pd, self.nleap, self.step_size, kwargs["alpha"], V=V, Vg=Vg)
+            qd, pd, V, Vg = out["q"], out["p"], out["V"], out["Vg"]
+            state.i += 1
+            state.samples.append(b.out(qd))
+            state.accepts.append(b.out(out["code"].to(torch.float64)))
+            state.Hs.append(b.out(out["Hs"]))
+            state.counts.append(b.out(out["counts"]))
+            if callback is not None:
+                callback(state)
+        state.to_array()
+        return state
+
+
+class Persistent_GHMC(GHMC):
+    """algorithms.Persistent_GHMC (src/algorithms.py:307-357): GHMC whose Metropolis uniform u is a
+    persistent variable, u <- (u + 1 + delta) % 2 - 1 each transition, divided by exp(H0-H1) on
+    acceptance.  (As in the reference, u itself -- not |u| -- is compared with min(1, prob).)"""
+
+    def step(self, q, p, u, nleap, step_size, alpha, delta, V_q=None, V_gq=None, pn=None):
+        """Returns (q, p, u, V_q, V_gq, accepted, Hs, counts) (src/algorithms.py:314-333)."""
+        e = self.engine
+        b = self._device_q(q)
+        V = None if V_q is None else torch.as_tensor(np.asarray(V_q) if not torch.is_tensor(V_q) else V_q).reshape(-1).to(
+            device=e.device, dtype=e.dtype).contiguous()
+        ut = torch.as_tensor(np.asarray(u, dtype=np.float64) if not torch.is_tensor(u) else u, dtype=torch.float64)
+        ut = ut.reshape(-1).to(e.device).contiguous()
+        if ut.numel() == 1 and b.C > 1:
+            ut = ut.expand(b.C).contiguous()
+        out = e.ghmc_step(b.q, self._as_dev(p, b), nleap, step_size, alpha, V=V, Vg=self._as_dev(V_gq, b), pn=pn, pu=ut,
+                          delta=delta)
+        code = out["code"].to(torch.float64)
+        if b.unbatched:
+            cnt = out["counts"][0].tolist()
+            self.Hcount, self.Vgcount, self.leapcount = cnt
+            return (b.out(out["q"]), b.out(out["p"]), float(out["u"][0]), float(out["V"][0]), b.out(out["Vg"]),
+                    float(code[0]), out["Hs"][0].tolist(), cnt)
+        self.Hcount, self.Vgcount, self.leapcount = out["counts"][:, 0], out["counts"][:, 1], out["counts"][:, 2]
+        return (b.out(out["q"]), b.out(out["p"]), b.out(out["u"]), b.out(out["V"]), b.out(out["Vg"]), b.out(code),
+                b.out(out["Hs"]), b.out(out["counts"]))
+
+    def sample(self, q, p=None, callback=None, **kwargs):
+        """src/algorithms.py:336-357."""
+        self._parse_kwargs_sample(**kwargs)
+        state = Sampler()
+        state.u = []
+        b = self._device_q(q)
+        qd = b.q
+        pd = torch.randn(qd.shape, dtype=qd.dtype, device=qd.device) if p is None else self._as_dev(p, b)
+        ud = torch.randn(qd.shape[0], dtype=torch.float64, device=qd.device)
+        V, Vg = None, None
+        for i in range(self.nsamples + self.burnin):
+            out = self.engine.ghmc_step(qd, pd, self.nleap, self.step_size, kwargs["alpha"], V=V, Vg=Vg, pu=ud,
+                                        delta=kwargs["delta"])
+            qd, pd, ud, V, Vg = out["q"], out["p"], out["u"], out["V"], out["Vg"]
+            state.i += 1
+            state.samples.append(b.out(qd))
+            state.accepts.append(b.out(out["code"].to(torch.float64)))
+            state.Hs.append(b.out(out["Hs"]))
+            state.counts.append(b.out(out["counts"]))
+            state.u.append(b.out(ud))
+            if callback is not None:
+                callback(state)
+        state.to_array()
+        return state
+
+
+class DRGHMC(DRHMC):
+    """algorithms.DRGHMC (src/algorithms.py:561-646): delayed rejection started from the partially
+    refreshed momentum p0 = alpha p + sqrt(1-alpha^2) pn; p0 itself is returned on rejection."""
+
+    def step(self, q, p, nleap, step_size, alpha, nprops, stepfactor, pn=None, u=None):
+        """Returns (q, p, code, avec, counts) (src/algorithms.py:596-625)."""
+        e = self.engine
+        b = self._device_q(q)
+        pv = torch.as_tensor(np.asarray(p)) if not torch.is_tensor(p) else p
+        pv = pv.reshape(b.C, -1).to(device=e.device, dtype=e.dtype).contiguous()
+        out = e.drhmc_step(b.q, nleap, step_size, nprops, stepfactor, p=pn, u=u, p_prev=pv, alpha=alpha)
+        if b.unbatched:
+            cnt = out["counts"][0].tolist()
+            self.Hcount, self.Vgcount, self.leapcount = cnt
+            return b.out(out["q"]), b.out(out["p"]), int(out["code"][0]), b.out(out["avec"]), cnt
+        self.Hcount, self.Vgcount, self.leapcount = out["counts"][:, 0], out["counts"][:, 1], out["counts"][:, 2]
+        return b.out(out["q"]), b.out(out["p"]), b.out(out["code"]), b.out(out["avec"]), b.out(out["counts"])
+
+    def sample(self, q, p=None, callback=None, **kwargs):
+        """src/algorithms.py:629-646."""
+        self._parse_kwargs_sample(**kwargs)
+        state = Sampler()
+        state.avecs = []
+        b = self._device_q(q)
+        qd = b.q
+        pd = torch.randn(qd.shape, dtype=qd.dtype, device=qd.device) if p is None else torch.as_tensor(p).reshape(
+            qd.shape).to(device=qd.device, dtype=qd.dtype)
+        for i in range(self.nsamples + self.burnin):
+            out = self.engine.drhmc_step(qd, self.nleap, self.step_size, kwargs["nprops"], kwargs["stepfactor"],
+                                         p_prev=pd, alpha=kwargs["alpha"])
+            qd, pd = out["q"], out["p"]
+            state.i += 1
+            state.samples.append(b.out(qd))
+            state.accepts.append(b.out(out["code"]))
+            state.avecs.append(b.out(out["avec"]))
+            state.counts.append(b.out(out["counts"]))
+            if callback is not None:
+                callback(state)
+        state.to_array()
+        return state
+
+
 def dr_stage_lengths(nleap, nprops, stepfactor):
     """(L_j, eps scale 1/f^j) per stage as the reference computes them
     (src/algorithms.py:510-511): int() truncation of nleap*f^j with a float f."""
     return [int(nleap * stepfactor ** j) for j in range(nprops)], [1.0 / stepfactor ** j for j in range(nprops)]
 
 
-# name -> class registry (src/algorithms.py:823-832); the other keys of the reference
-# ('ghmc', 'pghmc', 'drghmc', 'pdrhmc_metrop', 'pdrhmc_hasting') are later rows of SURVEY.md section 8f
-alg_dict = {"hmc": HMC, "drhmc": DRHMC}
+# name -> class registry (src/algorithms.py:823-832); the probabilistic-DR keys of the reference
+# ('pdrhmc_metrop', 'pdrhmc_hasting') are a later row of SURVEY.md section 8f
+alg_dict = {"hmc": HMC, "ghmc": GHMC, "pghmc": Persistent_GHMC, "drhmc": DRHMC, "drghmc": DRGHMC}
 

@@ -133,6 +133,9 @@ static void fill_args(TransArgs<T>& a, const hmcb_model* m, const hmcb_chains* c
   a.p_inject = (const T*)r->p_inject;
   a.u_inject = r->u_inject;
   a.u_stride = r->u_stride;
+  a.p_prev = (const T*)r->p_prev;
+  a.alpha = (T)(r->p_prev ? r->alpha : 0.0);
+  a.beta = (T)(r->p_prev ? sqrt(1.0 - r->alpha * r->alpha) : 1.0);
   if (o) {
     a.p_out = (T*)o->p_out;
     a.code = o->code;
@@ -196,11 +199,12 @@ static int dr_layout(const Entry* e, const hmcb_model* m, int64_t n_chains, int 
 
 template <typename T>
 static int drhmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r, int n_leap,
-                        double eps, int nprops, double stepfactor, const hmcb_step_out* o, void* ws,
+                        double eps, int nprops, double stepfactor, int conv, const hmcb_step_out* o, void* ws,
                         const DrLayout& L, const hmcb_profile* prof, cudaStream_t st) {
   TransArgs<T> a;
   fill_args(a, m, c, r, o);
   a.nprops = nprops;
+  a.dr_conv = conv;
   for (int j = 0; j < nprops; ++j) {
     // fac = stepfactor**j; nleapf = int(nleap*fac); step_sizef = step_size/fac (src/algorithms.py:510-511)
     const double fac = pow(stepfactor, (double)j);
@@ -243,6 +247,21 @@ static int mala_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c
     a.code = io->code; a.n_accept = io->n_accept; a.counts = io->counts;
   }
   return e->fn(*m, OP_MALA, &a, st);
+}
+
+template <typename T>
+static int ghmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r, int n_leap,
+                       double eps, const hmcb_ghmc_io* io, cudaStream_t st) {
+  GhmcArgs<T> g;
+  memset(&g, 0, sizeof(g));
+  fill_args(g.t, m, c, r, nullptr);
+  g.t.nprops = 1;
+  g.t.L[0] = n_leap;
+  g.t.eps[0] = (T)eps;
+  g.t.p_out = (T*)io->p_out; g.t.code = io->code; g.t.energies = (T*)io->energies; g.t.counts = io->counts;
+  g.V_in = (const T*)io->V_in; g.Vg_in = (const T*)io->Vg_in; g.V_out = (T*)io->V_out; g.Vg_out = (T*)io->Vg_out;
+  g.pu_in = io->u_in; g.pu_out = io->u_out; g.delta = io->delta;
+  return e->fn(*m, OP_GHMC, &g, st);
 }
 
 static int ad_frame_threads(const Entry* e, const hmcb_model* m, int64_t n_chains, int64_t& ft, int& epl) {
@@ -397,14 +416,15 @@ size_t hmcb_drhmc_workspace_bytes(const hmcb_model* model, int64_t n_chains, int
 }
 
 int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
-                    double step_size, int32_t nprops, double stepfactor, const hmcb_step_out* out, void* workspace,
-                    size_t workspace_bytes, const hmcb_profile* profile, void* stream) {
+                    double step_size, int32_t nprops, double stepfactor, int32_t convention, const hmcb_step_out* out,
+                    void* workspace, size_t workspace_bytes, const hmcb_profile* profile, void* stream) {
   int rc;
   if ((rc = check_model(model))) return rc;
   if ((rc = check_chains(chains))) return rc;
   HMCB_CHECK_ARG(rng != nullptr, "rng is NULL");
   HMCB_CHECK_ARG(nprops >= 1 && nprops <= kMaxProps, "nprops=%d must be in 1..%d", nprops, kMaxProps);
   HMCB_CHECK_ARG(stepfactor > 0, "stepfactor must be > 0");
+  HMCB_CHECK_ARG(convention == HMCB_DR_ALGORITHMS || convention == HMCB_DR_MULTISTEP, "unknown DR convention %d", convention);
   HMCB_CHECK_ARG(n_leap >= 0, "n_leap must be >= 0");
   HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= nprops, "u_inject needs u_stride >= nprops");
   if (chains->n_chains == 0) return 0;
@@ -418,19 +438,20 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
   }
   cudaStream_t st = (cudaStream_t)stream;
   if (model->dtype == HMCB_F64)
-    return drhmc_step_t<double>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, out, workspace, L, profile, st);
-  return drhmc_step_t<float>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, out, workspace, L, profile, st);
+    return drhmc_step_t<double>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, convention, out, workspace, L, profile, st);
+  return drhmc_step_t<float>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, convention, out, workspace, L, profile, st);
 }
 
 int hmcb_drhmc_step_static(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
-                           double step_size, int32_t nprops, double stepfactor, const hmcb_step_out* out,
-                           void* stream) {
+                           double step_size, int32_t nprops, double stepfactor, int32_t convention,
+                           const hmcb_step_out* out, void* stream) {
   int rc;
   if ((rc = check_model(model))) return rc;
   if ((rc = check_chains(chains))) return rc;
   HMCB_CHECK_ARG(rng != nullptr, "rng is NULL");
   HMCB_CHECK_ARG(nprops >= 1 && nprops <= kMaxProps, "nprops=%d must be in 1..%d", nprops, kMaxProps);
   HMCB_CHECK_ARG(stepfactor > 0, "stepfactor must be > 0");
+  HMCB_CHECK_ARG(convention == HMCB_DR_ALGORITHMS || convention == HMCB_DR_MULTISTEP, "unknown DR convention %d", convention);
   HMCB_CHECK_ARG(n_leap >= 0, "n_leap must be >= 0");
   HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= nprops, "u_inject needs u_stride >= nprops");
   if (chains->n_chains == 0) return 0;
@@ -452,10 +473,10 @@ int hmcb_drhmc_step_static(const hmcb_model* model, const hmcb_chains* chains, c
   k_static_scratch_clear_counters<<<1, 64, 0, st>>>();
   HMCB_CUDA(cudaPeekAtLastError());
   if (model->dtype == HMCB_F64)
-    return drhmc_step_t<double>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, out, scratch, L,
-                                nullptr, st);
-  return drhmc_step_t<float>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, out, scratch, L, nullptr,
-                             st);
+    return drhmc_step_t<double>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, convention, out, scratch,
+                                L, nullptr, st);
+  return drhmc_step_t<float>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, convention, out, scratch, L,
+                             nullptr, st);
 }
 
 int hmcb_mala_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, double eps,
@@ -476,6 +497,22 @@ int hmcb_mala_step(const hmcb_model* model, const hmcb_chains* chains, const hmc
   cudaStream_t st = (cudaStream_t)stream;
   if (model->dtype == HMCB_F64) return mala_step_t<double>(e, &mm, chains, rng, eps, n_steps, io, st);
   return mala_step_t<float>(e, &mm, chains, rng, eps, n_steps, io, st);
+}
+
+int hmcb_ghmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
+                   double step_size, const hmcb_ghmc_io* io, void* stream) {
+  int rc;
+  if ((rc = check_model(model))) return rc;
+  if ((rc = check_chains(chains))) return rc;
+  HMCB_CHECK_ARG(rng != nullptr && io != nullptr, "rng/io is NULL");
+  HMCB_CHECK_ARG(n_leap >= 0, "n_leap must be >= 0");
+  HMCB_CHECK_ARG(!rng->p_prev || (rng->alpha >= -1.0 && rng->alpha <= 1.0), "alpha must be in [-1, 1]");
+  if (chains->n_chains == 0) return 0;
+  const Entry* e = choose_entry(*model, kGhmcMaxEpl);
+  if (!e) return HMCB_E_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (model->dtype == HMCB_F64) return ghmc_step_t<double>(e, model, chains, rng, n_leap, step_size, io, st);
+  return ghmc_step_t<float>(e, model, chains, rng, n_leap, step_size, io, st);
 }
 
 size_t hmcb_adhmc_eps0_workspace_bytes(const hmcb_model* model, int64_t n_chains) {

@@ -140,6 +140,152 @@ __global__ void __launch_bounds__(THREADS, MINB) k_mala(const Model model, const
   }
 }
 
+// ------------------------------------------------------------------ GHMC / Persistent GHMC
+// algorithms.GHMC.step and Persistent_GHMC.step (src/algorithms.py:265-281, 314-333): partial
+// momentum refresh, V and grad V cached between transitions (leapfrog_Vgq, :150-172: the first
+// half kick reuses the cached gradient, the last gradient comes with the potential), momentum
+// flipped unless accepted; the persistent variant carries its Metropolis uniform.
+template <typename T>
+struct GhmcArgs {
+  TransArgs<T> t;          // chains, rng, p_prev/alpha/beta, minv, L[0], eps[0], code, energies, counts, p_out
+  const T* V_in;           // [C] cached V(q) or nullptr
+  const T* Vg_in;          // layout of q, cached grad V(q), or nullptr
+  T* V_out;
+  T* Vg_out;
+  const double* pu_in;     // [C] persistent uniform, or nullptr (plain GHMC)
+  double* pu_out;
+  double delta;
+};
+
+template <class Model, typename T, int EPL, int LPC, bool UNITM, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) k_ghmc(const Model model, const GhmcArgs<T> ga) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  using Lay = Layout<EPL, LPC>;
+  constexpr int GPB = THREADS / LPC;
+  const TransArgs<T>& a = ga.t;
+  const int d = a.d;
+  model.block_init(smem_raw, THREADS);
+  GroupCtx<T> c;
+  c.lane = threadIdx.x & (LPC - 1);
+  c.d = d;
+  const int group_in_warp = (threadIdx.x & 31) / LPC;
+  c.mask = (LPC == 32) ? 0xffffffffu : (((1u << LPC) - 1u) << (group_in_warp * LPC));
+  c.smem_q = nullptr;
+  if (Model::kNeedsSmem) c.smem_q = (T*)smem_raw + model.p_smem_elems() + (size_t)(threadIdx.x / LPC) * d;
+  T minv[UNITM ? 1 : EPL];
+  if (!UNITM) {
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) {
+      const int i = Lay::elem(c.lane, s);
+      minv[UNITM ? 0 : s] = (i < d) ? a.minv[i] : T(1);
+    }
+  } else {
+    minv[0] = T(1);
+  }
+  const int64_t total_groups = (int64_t)gridDim.x * GPB;
+  const bool cached = ga.Vg_in != nullptr;
+  const int N = a.L[0] > 1 ? a.L[0] : 1;
+  const T eps = a.eps[0], heps = T(0.5) * a.eps[0];
+  for (int64_t chain = ((int64_t)blockIdx.x * THREADS + threadIdx.x) / LPC; chain < a.n_chains; chain += total_groups) {
+    const int64_t off = chain * a.sc;
+    T q[EPL], p[EPL], g[EPL];
+    load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
+    draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);     // includes the alpha-mix with p_prev
+    const T K0 = kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+    int cH = 0, cVg = 0;
+    // Per-chain cache state.  The reference keeps V_q = V_gq = None until a proposal is accepted
+    // (src/algorithms.py:275-276); in a batch that is a NaN in V for exactly those chains.
+    T V0 = T(0);
+    bool has = cached;
+    if (cached && ga.V_in) {
+      V0 = ga.V_in[chain];
+      if (isnan(V0)) has = false;
+    }
+    const bool had_cache = has;
+    if (has) {
+      load_vec<T, EPL, LPC>(g, ga.Vg_in, off, a.sd, c.lane, d, T(1));
+    }
+    if (!has || !ga.V_in) {
+      T tmp[EPL];
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) tmp[s] = T(0);
+      const T V = model.template kick<EPL, LPC, true>(q, tmp, T(-1), c);
+      if (!has) {
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) g[s] = tmp[s];
+        cVg += 1;
+      }
+      if (!has || !ga.V_in) { V0 = V; cH += 1; }
+    }
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) p[s] = fma(-heps, g[s], p[s]);
+#pragma unroll 1
+    for (int i = 1; i < N; ++i) {
+      drift<T, EPL, UNITM>(q, p, minv, eps);
+      model.template kick<EPL, LPC, false>(q, p, eps, c);
+    }
+    cVg += N - 1;
+    drift<T, EPL, UNITM>(q, p, minv, eps);
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) g[s] = T(0);
+    const T V1 = model.template kick<EPL, LPC, true>(q, g, T(-1), c);      // g = grad V(q1), V1 = V(q1)
+    cVg += 1;
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) p[s] = fma(-heps, g[s], p[s]);
+    const T H0 = V0 + K0, H1 = V1 + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+    T dq = diff_sum<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d);
+    dq = group_sum_masked<LPC, T>(dq, c.mask);
+    const T prob = t_exp<T>(H0 - H1);
+    const bool bad = t_bad(prob) || dq == T(0);
+    double u;
+    if (ga.pu_in) {
+      const double w = ga.pu_in[chain] + 1.0 + ga.delta;      // u = (u + 1 + delta) % 2 - 1, Python's sign convention
+      double r = fmod(w, 2.0);
+      if (r < 0.0) r += 2.0;
+      u = r - 1.0;
+    } else {
+      u = draw_uniform<T>(a, chain, 0);
+    }
+    const T pm = prob < T(1) ? prob : T(1);
+    const bool accept = !bad && !(u > (double)pm);
+    if (c.lane == 0) {
+      if (a.code) a.code[chain] = bad ? -1 : (accept ? 1 : 0);
+      if (a.energies) { a.energies[2 * chain] = H0; a.energies[2 * chain + 1] = H1; }
+      if (a.counts) { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = 1; }
+      if (ga.V_out) ga.V_out[chain] = accept ? V1 : (had_cache ? V0 : (T)NAN);
+      if (ga.pu_out) ga.pu_out[chain] = accept ? u / (double)prob : u;
+    }
+    if (accept) {
+      store_vec<T, EPL, LPC>(q, a.q_out, off, a.sd, c.lane, d);
+      if (a.p_out) store_vec<T, EPL, LPC>(p, a.p_out, off, a.sd, c.lane, d);
+      if (ga.Vg_out) store_vec<T, EPL, LPC>(g, ga.Vg_out, off, a.sd, c.lane, d);
+    } else {
+      if (a.q_out != a.q_in) {
+        load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
+        store_vec<T, EPL, LPC>(q, a.q_out, off, a.sd, c.lane, d);
+      }
+      if (a.p_out) {
+        draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);   // the refreshed momentum, flipped
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) p[s] = -p[s];
+        store_vec<T, EPL, LPC>(p, a.p_out, off, a.sd, c.lane, d);
+      }
+      if (ga.Vg_out) {
+        if (had_cache) {
+          if (ga.Vg_out != ga.Vg_in) {
+            load_vec<T, EPL, LPC>(g, ga.Vg_in, off, a.sd, c.lane, d, T(1));
+            store_vec<T, EPL, LPC>(g, ga.Vg_out, off, a.sd, c.lane, d);
+          }
+        } else {
+#pragma unroll
+          for (int s = 0; s < EPL; ++s) g[s] = (T)NAN;      // still "None" for this chain
+          store_vec<T, EPL, LPC>(g, ga.Vg_out, off, a.sd, c.lane, d);
+        }
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------ AdHMC_eps0
 // Per-transition random step size (src/adaptivehmc.py:111-192): ntry log-spaced trial
 // step sizes, nsteps leapfrog steps each from (q0,p0); weights exp(H0-H_i) sqrt(eps_i)
@@ -225,7 +371,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_adhmc_eps0(const Model model,
     {
       TransArgs<T> ta;
       ta.chain_offset = a.chain_offset; ta.sc = a.sc; ta.sd = a.sd; ta.seed = a.seed; ta.iteration = a.iteration;
-      ta.rng_flags = a.rng_flags; ta.p_inject = a.p_inject;
+      ta.rng_flags = a.rng_flags; ta.p_inject = a.p_inject; ta.p_prev = nullptr;
       draw_momentum<T, EPL, LPC, UNITM>(p, ta, minv, chain, c.lane, d);
     }
 #pragma unroll

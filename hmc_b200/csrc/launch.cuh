@@ -12,7 +12,8 @@
 namespace hmcb {
 
 enum Op { OP_HMC = 0, OP_DR0 = 1, OP_DRN = 2, OP_LEAPFROG = 3, OP_LOGPGRAD = 4, OP_QUERY = 5, OP_MALA = 6, OP_ADHMC = 7,
-          OP_QUERY_AD = 8 };
+          OP_QUERY_AD = 8, OP_GHMC = 9 };
+constexpr int kGhmcMaxEpl = 32;  // GHMC keeps q, p and the gradient: 3*EPL values per lane
 constexpr int kMalaMaxEpl = 28;  // MALA keeps q, grad, q1, grad1 in registers: 4*EPL values per lane
 
 struct LaunchInfo {
@@ -188,6 +189,19 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
         break;
       } else {
         set_error("internal: MALA is not compiled for EPL=%d", EPL);
+        return HMCB_E_UNSUPPORTED;
+      }
+    }
+    case OP_GHMC: {
+      if constexpr (EPL <= kGhmcMaxEpl) {
+        constexpr int MB = min_blocks_for<T, (3 * EPL + 1) / 2, UNITM, GAUSS>();
+        auto k = k_ghmc<Model, T, EPL, LPC, UNITM, THREADS, MB>;
+        if ((rc = prep(k, max_blocks))) return rc;
+        GhmcArgs<T>& a = *(GhmcArgs<T>*)args;
+        k<<<grid_for(a.t.n_chains, max_blocks), THREADS, smem, st>>>(model, a);
+        break;
+      } else {
+        set_error("internal: GHMC is not compiled for EPL=%d", EPL);
         return HMCB_E_UNSUPPORTED;
       }
     }

@@ -45,6 +45,8 @@ struct TransArgs {
   const T* p_inject;
   const double* u_inject;
   int32_t u_stride;
+  const T* p_prev;   // partial momentum refresh (GHMC family): p = alpha*p_prev + sqrt(1-alpha^2)*draw; nullptr = full refresh
+  T alpha, beta;     // beta = sqrt(1 - alpha^2)
   T* p_out;
   int32_t* code;
   T* energies;
@@ -53,6 +55,7 @@ struct TransArgs {
   T* accept_prob;
   const T* minv;     // inverse metric diagonal or nullptr
   int32_t rule;      // HMCB_RULE_*
+  int32_t dr_conv;   // HMCB_DR_*: 0 algorithms.DRHMC, 1 pyhmc.PyHMC_multistep
   int32_t nprops, stage;
   int32_t L[kMaxProps];
   T eps[kMaxProps];
@@ -187,6 +190,13 @@ __device__ __forceinline__ void draw_momentum(T (&p)[EPL], const TransArgs<T>& a
 #pragma unroll
     for (int s = 0; s < EPL; ++s) p[s] *= t_rsqrt<T>(minv[UNITM ? 0 : s]);
   }
+  if (a.p_prev) {
+    // p = alpha*p + sqrt(1 - alpha**2)*pn (src/algorithms.py:269,603)
+    T pv[EPL];
+    load_vec<T, EPL, LPC>(pv, a.p_prev, chain * a.sc, a.sd, lane, d, T(1));
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) p[s] = a.alpha * pv[s] + a.beta * p[s];
+  }
 }
 
 template <typename T>
@@ -314,8 +324,10 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
         if (t_bad(prob)) prob = T(0);
         const T a0 = prob < T(1) ? prob : T(1);
         const double u = draw_uniform<T>(a, chain, 0);
-        accept = u < (double)a0;
-        code = accept ? 1 : 0;
+        // algorithms.DRHMC: acc < avec[0] (src/algorithms.py:528); PyHMC_multistep's first stage: acc <= avec[0]
+        // (src/pyhmc.py:580) and codes j / -1 instead of j+1 / 0
+        accept = a.dr_conv ? (u <= (double)a0) : (u < (double)a0);
+        code = a.dr_conv ? (accept ? 0 : -1) : (accept ? 1 : 0);
         finished = accept || a.nprops == 1;
         if (c.lane == 0) {
           if (finished) {
@@ -406,6 +418,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
           for (int s = 0; s < EPL; ++s) { fq[(int64_t)s * FT] = q[s]; fq[(int64_t)(EPL + s) * FT] = p[s]; }
           lpf[lvl] = pf;
           ++lvl;
+          if (a.dr_conv) cH += 1;   // PyHMC_multistep.get_num re-evaluates H at its base (src/pyhmc.py:541)
           lm[lvl] = j; lj[lvl] = 0; lHb[lvl] = Hn;
 #pragma unroll
           for (int i = 0; i < kMaxProps; ++i) lav[lvl][i] = T(0);
@@ -449,7 +462,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
             for (int i = 0; i < a.nprops; ++i)
               a.avec_out[chain * a.nprops + i] = (i < J) ? lav[0][i] : (i == J ? aJ : T(0));
           }
-          if (a.code) a.code[chain] = accept ? J + 1 : 0;
+          if (a.code) a.code[chain] = a.dr_conv ? (accept ? J : -1) : (accept ? J + 1 : 0);
           if (a.counts) { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = cLeap; }
         } else {
           a.ws.avec[chain * kMaxProps + J] = aJ;

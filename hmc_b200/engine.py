@@ -130,10 +130,14 @@ class Engine:
         c.stride_chain, c.stride_dim = q_in.stride(0), q_in.stride(1)
         return c
 
-    def _rng(self, p, u, nu, C_):
+    def _rng(self, p, u, nu, C_, p_prev=None, alpha=0.0):
         r = _lib.Rng()
         r.seed, r.iteration, r.flags = self.seed, self.iteration, self.rng_flags
         keep = []
+        if p_prev is not None:
+            pv = p_prev.reshape(C_, -1).to(device=self.device, dtype=self.dtype).contiguous()
+            keep.append(pv)
+            r.p_prev, r.alpha = pv.data_ptr(), float(alpha)
         if p is not None:
             pt = torch.as_tensor(np.asarray(p)) if not torch.is_tensor(p) else p
             pt = pt.reshape(C_, -1).to(device=self.device, dtype=self.dtype).contiguous()
@@ -185,7 +189,7 @@ class Engine:
 
     def drhmc_step(self, q, n_leap, step_size, nprops, stepfactor, p=None, u=None, want_p=True, q_out=None,
                    stage_events=None, want_avec=True, code_out=None, counts_out=None, extra_offset=0, ws_slot=0,
-                   advance=True):
+                   advance=True, convention=0, p_prev=None, alpha=0.0):
         """hmcb_drhmc_step on device tensor q [C,d].  q_out / code_out / counts_out let a
         caller reuse its own output buffers (no allocation inside a timed loop)."""
         m = self._ensure()
@@ -208,9 +212,9 @@ class Engine:
             so.p_out, so.code, so.avec = _lib.ptr(out["p"]), _lib.ptr(out["code"]), _lib.ptr(out["avec"])
             so.counts = _lib.ptr(out["counts"])
             ch = self._chains(q, q_out, extra_offset)
-            r, keep = self._rng(p, u, nprops, C_)
+            r, keep = self._rng(p, u, nprops, C_, p_prev, alpha)
             _lib.check(self.lib.hmcb_drhmc_step(C.byref(m), C.byref(ch), C.byref(r), int(n_leap), float(step_size),
-                                                int(nprops), float(stepfactor), C.byref(so),
+                                                int(nprops), float(stepfactor), int(convention), C.byref(so),
                                                 C.c_void_p(ws.data_ptr()), ws.numel(),
                                                 self._profile(stage_events), self._stream()))
         if advance:
@@ -258,6 +262,31 @@ class Engine:
             st.synchronize()
         self.iteration += 1
         return host
+
+    def ghmc_step(self, q, p_prev, n_leap, step_size, alpha, V=None, Vg=None, pn=None, u=None, pu=None, delta=0.0):
+        """hmcb_ghmc_step on device tensors: q, p_prev [C,d]; cached V [C], Vg [C,d] or None;
+        pu [C] float64 = the persistent uniform (Persistent_GHMC) or None."""
+        m = self._ensure()
+        C_ = q.shape[0]
+        with torch.cuda.device(self.device):
+            out = {"q": torch.empty_like(q), "p": torch.empty_like(q),
+                   "V": torch.empty(C_, dtype=self.dtype, device=self.device), "Vg": torch.empty_like(q),
+                   "u": torch.empty(C_, dtype=torch.float64, device=self.device) if pu is not None else None,
+                   "code": torch.empty(C_, dtype=torch.int32, device=self.device),
+                   "Hs": torch.empty((C_, 2), dtype=self.dtype, device=self.device),
+                   "counts": torch.empty((C_, 3), dtype=torch.int32, device=self.device)}
+            io = _lib.GhmcIO()
+            io.p_out, io.V_in, io.Vg_in = _lib.ptr(out["p"]), _lib.ptr(V), _lib.ptr(Vg)
+            io.V_out, io.Vg_out = _lib.ptr(out["V"]), _lib.ptr(out["Vg"])
+            io.u_in, io.u_out, io.delta = _lib.ptr(pu), _lib.ptr(out["u"]), float(delta)
+            io.code, io.energies, io.counts = _lib.ptr(out["code"]), _lib.ptr(out["Hs"]), _lib.ptr(out["counts"])
+            ch = self._chains(q, out["q"])
+            r, keep = self._rng(pn, u, 1, C_, p_prev, alpha)
+            _lib.check(self.lib.hmcb_ghmc_step(C.byref(m), C.byref(ch), C.byref(r), int(n_leap), float(step_size),
+                                               C.byref(io), self._stream()))
+        self.iteration += 1
+        out["_keep"] = keep
+        return out
 
     def mala_step(self, q, eps, n_steps=1, V=None, Vg=None, z=None, u=None, q_out=None):
         """hmcb_mala_step on device tensor q [C,d]; V [C] / Vg [C,d] are the cached

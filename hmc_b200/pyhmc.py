@@ -132,3 +132,25 @@ class PyHMC(HMC):
 
     def hmc_step(self, q, N, step_size, p=None, u=None):
         return self._step(q, N, step_size, p=p, u=u)
+
+
+class PyHMC_multistep(HMC):
+    """pyhmc.PyHMC_multistep (src/pyhmc.py:489-598), the delayed-rejection sampler the
+    reference's funnel experiments run (scripts_old/tests/test_drhmc_funnel.py:157-159).
+    Same proposals and acceptance probabilities as algorithms.DRHMC, with this class's own
+    bookkeeping: the first stage accepts iff u <= alpha_0 (:580), codes are the accepting
+    stage j >= 0 or -1, and Hcount counts the energy that get_num re-evaluates at its base
+    (:541)."""
+
+    def multi_step(self, m, q0, N, ss, fsub, p=None, u=None):
+        """Returns (q, p, code, avec[m], [Hcount, Vgcount, leapcount])."""
+        e = self.engine
+        b = Batch(q0, e.dev, e.dtype)
+        e.check_dim(b)
+        out = e.drhmc_step(b.q, N, ss, m, fsub, p=p, u=u, convention=_lib.DR_MULTISTEP)
+        if b.unbatched:
+            cnt = out["counts"][0].tolist()
+            self.Hcount, self.Vgcount, self.leapcount = cnt
+            return b.out(out["q"]), b.out(out["p"]), int(out["code"][0]), b.out(out["avec"]), cnt
+        self.Hcount, self.Vgcount, self.leapcount = out["counts"][:, 0], out["counts"][:, 1], out["counts"][:, 2]
+        return b.out(out["q"]), b.out(out["p"]), b.out(out["code"]), b.out(out["avec"]), b.out(out["counts"])

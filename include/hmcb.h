@@ -72,6 +72,10 @@ typedef struct hmcb_rng {
   const double* u_inject;     /* uniforms [n_chains, u_stride] or NULL */
   int32_t u_stride;
   int32_t flags;
+  /* Partial momentum refresh of the generalised-HMC family (src/algorithms.py:269,603):
+   * momentum = alpha * p_prev + sqrt(1 - alpha^2) * draw.  p_prev NULL = full refresh. */
+  const void* p_prev;         /* previous momentum, layout of q, or NULL */
+  double alpha;
 } hmcb_rng;
 
 /* Per-chain outputs of one transition.  Any pointer may be NULL (not written). */
@@ -119,6 +123,12 @@ int hmcb_logp_grad(const hmcb_model* model, const hmcb_chains* chains, void* log
  * owned scratch of at least hmcb_drhmc_workspace_bytes(); contents need not be
  * preserved between calls. */
 #define HMCB_MAX_PROPS 6
+/* Which reference class's bookkeeping a DR step follows (same proposals and probabilities):
+ *  HMCB_DR_ALGORITHMS  algorithms.DRHMC.step: accept iff u < alpha_j, code j+1 / 0 (src/algorithms.py:500-530)
+ *  HMCB_DR_MULTISTEP   pyhmc.PyHMC_multistep.multi_step (src/pyhmc.py:564-598): first stage accepts iff
+ *                      u <= alpha_0, code j / -1, and get_num re-evaluates H at its base (:541) so
+ *                      Hcount is larger by one per ghost frame */
+enum { HMCB_DR_ALGORITHMS = 0, HMCB_DR_MULTISTEP = 1 };
 /* Optional per-stage timing: cudaEvent_t handles (as void*) recorded on `stream`
  * before stage 0, between stages and after the last one (nprops+1 events).  The
  * reference's only timing is time.time() around its sample loop
@@ -128,7 +138,7 @@ typedef struct hmcb_profile {
 } hmcb_profile;
 size_t hmcb_drhmc_workspace_bytes(const hmcb_model* model, int64_t n_chains, int32_t nprops);
 int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng,
-                    int32_t n_leap, double step_size, int32_t nprops, double stepfactor,
+                    int32_t n_leap, double step_size, int32_t nprops, double stepfactor, int32_t convention,
                     const hmcb_step_out* out, void* workspace, size_t workspace_bytes,
                     const hmcb_profile* profile /* may be NULL */, void* stream);
 
@@ -154,7 +164,7 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
  * Same arguments, outputs and results as hmcb_drhmc_step. */
 #define HMCB_STATIC_SCRATCH_BYTES (32u << 20)
 int hmcb_drhmc_step_static(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng,
-                           int32_t n_leap, double step_size, int32_t nprops, double stepfactor,
+                           int32_t n_leap, double step_size, int32_t nprops, double stepfactor, int32_t convention,
                            const hmcb_step_out* out, void* stream);
 
 /* Streamed sample moments (the reference stores samples[T,C,d] and post-processes,
@@ -186,6 +196,30 @@ typedef struct hmcb_mala_io {
 } hmcb_mala_io;
 int hmcb_mala_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, double eps,
                    int32_t n_steps, const hmcb_mala_io* io, void* stream);
+
+/* Generalised HMC, algorithms.GHMC.step (src/algorithms.py:265-281), and its persistent-uniform
+ * variant Persistent_GHMC.step (:314-333): momentum partially refreshed from rng->p_prev with
+ * rng->alpha, potential and gradient cached between transitions as leapfrog_Vgq does (:150-172),
+ * momentum returned flipped unless the proposal is accepted.  Codes 1/0/-1.  Counts follow the
+ * reference built with both grad_log_prob and log_prob_and_grad: Vgcount = n_leap (n_leap+1
+ * without a cached gradient), Hcount = 0 (1 without a cached potential).  u_in non-NULL selects
+ * the persistent variant: u <- (u_in + 1 + delta) mod 2 - 1 is the Metropolis variable and
+ * u_out = u / exp(H0-H1) on acceptance, else u. */
+typedef struct hmcb_ghmc_io {
+  void* p_out;         /* layout of q */
+  const void* V_in;    /* [C] or NULL */
+  const void* Vg_in;   /* layout of q, or NULL */
+  void* V_out;         /* [C] */
+  void* Vg_out;        /* layout of q */
+  const double* u_in;  /* [C] or NULL */
+  double* u_out;       /* [C] */
+  double delta;
+  int32_t* code;       /* [C] */
+  void* energies;      /* [C,2] */
+  int32_t* counts;     /* [C,3] */
+} hmcb_ghmc_io;
+int hmcb_ghmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
+                   double step_size, const hmcb_ghmc_io* io, void* stream);
 
 /* AdHMC_eps0.hmc_step with Tint = 0 (src/adaptivehmc.py:138-192) and its step-size
  * draw get_stepsize (:111-134).  `steps` is a HOST array of the ntry trial step sizes

@@ -364,3 +364,172 @@ def split_rhat(x):
     W = s2.mean(axis=0)
     B = T * m.var(axis=0, ddof=1)
     return np.sqrt(((T - 1) / T * W + B / T) / W)
+
+
+# ----------------------------------------------------------------------------- PyHMC_multistep
+
+def _ms_ghost(model, kin, m, q, p, N, ss, fsub, cnt):
+    """PyHMC_multistep.get_num, src/pyhmc.py:538-561: as DRHMC.get_num but it evaluates the
+    energy at its base itself (one more Hcount per call)."""
+    avec = np.zeros(m)
+    H0 = _H(model, kin, q, p, cnt)
+    for j in range(m):
+        fac = fsub ** j
+        qj, pj = leapfrog(model, kin, q, p, int(N * fac), ss / fac, cnt)
+        Hj = _H(model, kin, qj, pj, cnt)
+        pfac = np.exp(H0 - Hj)
+        if (q - qj).sum() == 0:
+            pfac = 0.0
+        if j:
+            den = np.prod(1 - avec[:j])
+            num = _ms_ghost(model, kin, j, qj, -pj, N, ss, fsub, cnt)
+            prob = pfac * num / den
+        else:
+            prob = pfac
+        if _bad(prob):
+            return 0.0
+        avec[j] = min(1.0, prob)
+        if not np.prod(1 - avec):
+            return np.prod(1 - avec)
+    return np.prod(1 - avec)
+
+
+def multistep_step(model, m, q0, N, ss, fsub, rng, invmetric_diag=None):
+    """pyhmc.PyHMC_multistep.multi_step, src/pyhmc.py:564-598: first stage accepts iff
+    u <= alpha_0; later stages iff u < alpha_j; code = accepting stage j, or -1."""
+    kin, cnt = Kinetics(invmetric_diag), Counters()
+    with np.errstate(all="ignore"):
+        p0 = rng.normal(size=q0.size).reshape(q0.shape) * kin.metricstd
+        avec = np.zeros(m)
+        H0 = _H(model, kin, q0, p0, cnt)
+        q1, p1 = leapfrog(model, kin, q0, p0, N, ss, cnt)
+        H1 = _H(model, kin, q1, p1, cnt)
+        prob = np.exp(H0 - H1)
+        if _bad(prob) or (q0 - q1).sum() == 0:
+            prob = 0.0
+        avec[0] = min(1.0, prob)
+        if rng.uniform() <= avec[0]:
+            return q1, p1, 0, avec, cnt.as_list()
+        for j in range(1, m):
+            fac = fsub ** j
+            qj, pj = leapfrog(model, kin, q0, p0, int(N * fac), ss / fac, cnt)
+            Hj = _H(model, kin, qj, pj, cnt)
+            pfac = np.exp(H0 - Hj)
+            if (q0 - qj).sum() == 0:
+                pfac = 0.0
+            den = np.prod(1 - avec[:j])
+            num = _ms_ghost(model, kin, j, qj, -pj, N, ss, fsub, cnt)
+            prob = pfac * num / den
+            if _bad(prob):
+                prob = 0.0
+            avec[j] = min(1.0, prob)
+            if rng.uniform() < avec[j]:
+                return qj, pj, j, avec, cnt.as_list()
+    return q0, p0, -1, avec, cnt.as_list()
+
+
+# ----------------------------------------------------------------------------- generalised HMC family
+# These classes are built as Cls(log_prob, grad_log_prob, log_prob_and_grad): V_g then uses
+# grad_log_prob (src/algorithms.py:100-106) and the last gradient of a trajectory comes from
+# log_prob_and_grad through V_vandg (:109-115,163-164), which also yields the cached V_q1.
+
+def _leapfrog_Vgq(model, kin, q, p, N, step_size, cnt, V_q=None, V_gq=None):
+    """algorithms.HMC.leapfrog_Vgq, src/algorithms.py:150-172: the first half kick reuses a cached
+    gradient; the last gradient evaluation also returns the potential."""
+    cnt.leap += 1
+    if V_gq is None:
+        p = p - 0.5 * step_size * _V_g(model, q, cnt)
+    else:
+        p = p - 0.5 * step_size * V_gq
+    for _ in range(N - 1):
+        q = q + step_size * kin.KE_g(p)
+        p = p - step_size * _V_g(model, q, cnt)
+    q = q + step_size * kin.KE_g(p)
+    cnt.Vg += 1
+    v, v_g = model.log_prob_and_grad(q)
+    V_q1, V_gq1 = v * -1.0, v_g * -1
+    p = p - 0.5 * step_size * V_gq1
+    return q, p, V_q1, V_gq1
+
+
+def _metropolis_alg(model, kin, q0, p0, q1, p1, cnt, V_q0, V_q1, u):
+    """algorithms.HMC.metropolis with cached potentials and a given uniform, src/algorithms.py:175-189."""
+    if V_q0 is None:
+        cnt.H += 1
+        V_q0 = _V(model, q0)
+    H0 = V_q0 + kin.KE(p0)
+    if V_q1 is None:
+        cnt.H += 1
+        V_q1 = _V(model, q1)
+    H1 = V_q1 + kin.KE(p1)
+    prob = np.exp(H0 - H1)
+    if _bad(prob) or (q0 - q1).sum() == 0:
+        return q0, p0, -1, [H0, H1]
+    if u > min(1.0, prob):
+        return q0, p0, 0.0, [H0, H1]
+    return q1, p1, 1.0, [H0, H1]
+
+
+def ghmc_step(model, q, p, nleap, step_size, alpha, rng, V_q=None, V_gq=None, invmetric_diag=None):
+    """algorithms.GHMC.step, src/algorithms.py:265-281: partial momentum refresh
+    p <- alpha p + sqrt(1-alpha^2) pn, cached V / grad V, momentum flipped unless accepted.
+    Returns (q, p, V_q, V_gq, accepted, Hs, counts)."""
+    kin, cnt = Kinetics(invmetric_diag), Counters()
+    with np.errstate(all="ignore"):
+        pn = rng.normal(size=q.size).reshape(q.shape) * kin.metricstd
+        p = alpha * p + np.sqrt(1 - alpha ** 2) * pn
+        q1, p1, V_q1, V_gq1 = _leapfrog_Vgq(model, kin, q, p, nleap, step_size, cnt, V_q, V_gq)
+        u = rng.uniform(0.0, 1.0, size=1)
+        q, p, accepted, Hs = _metropolis_alg(model, kin, q, p, q1, p1, cnt, V_q, V_q1, u)
+        if accepted == 1:
+            V_q, V_gq = V_q1, V_gq1
+        else:
+            p = -p
+    return q, p, V_q, V_gq, accepted, Hs, cnt.as_list()
+
+
+def pghmc_step(model, q, p, u, nleap, step_size, alpha, delta, rng, V_q=None, V_gq=None, invmetric_diag=None):
+    """algorithms.Persistent_GHMC.step, src/algorithms.py:314-333: GHMC whose Metropolis uniform
+    is itself a persistent variable, u <- (u + 1 + delta) % 2 - 1, rescaled by 1/exp(H0-H1) on
+    acceptance.  Returns (q, p, u, V_q, V_gq, accepted, Hs, counts)."""
+    kin, cnt = Kinetics(invmetric_diag), Counters()
+    with np.errstate(all="ignore"):
+        pn = rng.normal(size=q.size).reshape(q.shape) * kin.metricstd
+        p = alpha * p + np.sqrt(1 - alpha ** 2) * pn
+        u = (u + 1 + delta) % 2 - 1
+        q1, p1, V_q1, V_gq1 = _leapfrog_Vgq(model, kin, q, p, nleap, step_size, cnt, V_q, V_gq)
+        q, p, accepted, Hs = _metropolis_alg(model, kin, q, p, q1, p1, cnt, V_q, V_q1, u)
+        if accepted == 1:
+            V_q, V_gq = V_q1, V_gq1
+            u = u / np.exp(Hs[0] - Hs[1])
+        else:
+            p = -p
+    return q, p, u, V_q, V_gq, accepted, Hs, cnt.as_list()
+
+
+def drghmc_step(model, q, p, nleap, step_size, alpha, nprops, stepfactor, rng, invmetric_diag=None):
+    """algorithms.DRGHMC.step, src/algorithms.py:596-625: DRHMC.step started from the partially
+    refreshed momentum p0 = alpha p + sqrt(1-alpha^2) pn; p0 is returned (not flipped) on rejection."""
+    kin, cnt = Kinetics(invmetric_diag), Counters()
+    avec = np.zeros(nprops)
+    with np.errstate(all="ignore"):
+        q0 = q
+        pn = rng.normal(size=q.size).reshape(q.shape) * kin.metricstd
+        p0 = alpha * p + np.sqrt(1 - alpha ** 2) * pn
+        H0 = _H(model, kin, q0, p0, cnt)
+        for j in range(nprops):
+            fac = stepfactor ** j
+            qj, pj = leapfrog(model, kin, q0, p0, int(nleap * fac), step_size / fac, cnt)
+            Hj = _H(model, kin, qj, pj, cnt)
+            pfac = np.exp(H0 - Hj)
+            if (q0 - qj).sum() == 0:
+                pfac = 0.0
+            den = np.prod(1 - avec[:j])
+            num = _dr_ghost(model, kin, j, qj, -pj, nleap, step_size, stepfactor, Hj, cnt)
+            prob = pfac * num / den
+            if _bad(prob):
+                prob = 0.0
+            avec[j] = min(1.0, prob)
+            if rng.uniform() < avec[j]:
+                return qj, pj, j + 1, avec, cnt.as_list()
+    return q0, p0, 0, avec, cnt.as_list()

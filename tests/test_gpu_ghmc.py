@@ -1,0 +1,118 @@
+"""GPU parity for the generalised-HMC family: algorithms.GHMC,
+Persistent_GHMC (src/algorithms.py:259-357) and DRGHMC (:561-646) against the oracle, which is
+pinned bit-for-bit to the reference classes (tests/test_oracle_vs_reference.py)."""
+import numpy as np
+import pytest
+import torch
+
+from hmc_b200 import algorithms, models
+from oracle import models as omodels
+from oracle import replay, samplers
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    assert torch.cuda.is_available()
+    return torch.device("cuda:0")
+
+
+def _models(kind, d):
+    if kind == "funnel":
+        return models.Funnel(d), omodels.Funnel(d)
+    if kind == "rosenbrock":
+        return models.Rosenbrock(d), omodels.Rosenbrock(d)
+    return models.CorrGaussian.ar1(d), omodels.CorrGaussian.ar1(d)
+
+
+def _close(a, b, rtol=1e-10, atol=1e-11):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    ok = np.isclose(a, b, rtol=rtol, atol=atol, equal_nan=True)
+    assert ok.all(), "max rel err %.3e" % np.nanmax(np.abs(a - b) / (np.abs(b) + atol / rtol))
+
+
+@pytest.mark.parametrize("kind,d,eps", [("funnel", 10, 0.1), ("funnel", 50, 0.06), ("rosenbrock", 20, 0.03),
+                                        ("gaussian", 12, 0.15)])
+@pytest.mark.parametrize("alpha", [0.0, 0.8])
+def test_ghmc_three_transitions_with_caches(kind, d, eps, alpha):
+    pm, om = _models(kind, d)
+    C, N, T = 29, 5, 3
+    rng = np.random.default_rng(d)
+    q = rng.uniform(-1, 1, (C, d))
+    if kind == "rosenbrock":
+        q = 1.0 + 0.1 * q
+    p = rng.standard_normal((C, d))
+    P, U = replay.make_draws(300 + d, T, C, d, 1)
+    s = algorithms.GHMC(pm, device=_dev())
+    gq, gp, gV, gVg = q, p, None, None
+    ref = [(q[c], p[c], None, None) for c in range(C)]
+    for t in range(T):
+        gq, gp, gV, gVg, acc, Hs, counts = s.step(gq, gp, N, eps, alpha, V_q=gV, V_gq=gVg, pn=P[t], u=U[t])
+        out = [samplers.ghmc_step(om, ref[c][0], ref[c][1], N, eps, alpha, replay.Draws([P[t, c]], U[t, c]), ref[c][2], ref[c][3])
+               for c in range(C)]
+        assert np.array_equal(acc, [o[4] for o in out])
+        assert np.array_equal(counts, [o[6] for o in out])        # [1, N+1, 1] first, then [0, N, 1]
+        _close(gq, np.array([o[0] for o in out]))
+        _close(gp, np.array([o[1] for o in out]))                 # flipped on rejection
+        # chains whose first proposal was rejected still have V_q = V_gq = None in the reference: NaN here
+        rV = np.array([np.nan if o[2] is None else o[2] for o in out], dtype=np.float64)
+        rVg = np.array([np.full(d, np.nan) if o[3] is None else o[3] for o in out], dtype=np.float64)
+        _close(gV, rV, rtol=1e-10, atol=1e-10)
+        _close(gVg, rVg, rtol=1e-10, atol=1e-10)
+        _close(Hs, np.array([o[5] for o in out]), rtol=1e-9, atol=1e-10)
+        ref = [o[:4] for o in out]
+    assert [0, N, 1] in counts.tolist()
+
+
+def test_persistent_ghmc_carries_its_uniform():
+    pm, om = _models("funnel", 10)
+    C, N, T = 31, 4, 4
+    rng = np.random.default_rng(4)
+    q, p = rng.uniform(-1, 1, (C, 10)), rng.standard_normal((C, 10))
+    u = rng.uniform(-1, 1, C)
+    P, _ = replay.make_draws(41, T, C, 10, 1)
+    s = algorithms.Persistent_GHMC(pm, device=_dev())
+    g = (q, p, u, None, None)
+    ref = [(q[c], p[c], u[c], None, None) for c in range(C)]
+    for t in range(T):
+        out_g = s.step(g[0], g[1], g[2], N, 0.1, 0.5, 0.37, V_q=g[3], V_gq=g[4], pn=P[t])
+        out = [samplers.pghmc_step(om, *ref[c][:3], N, 0.1, 0.5, 0.37, replay.Draws([P[t, c]], []), ref[c][3], ref[c][4])
+               for c in range(C)]
+        assert np.array_equal(out_g[5], [o[5] for o in out])
+        _close(out_g[0], np.array([o[0] for o in out]))
+        _close(out_g[2], np.array([o[2] for o in out]), rtol=1e-9, atol=1e-12)
+        g, ref = out_g[:5], [o[:5] for o in out]
+
+
+@pytest.mark.parametrize("kind,d,nleap,eps", [("funnel", 10, 6, 0.6), ("funnel", 50, 8, 0.35), ("rosenbrock", 10, 8, 0.1)])
+def test_drghmc_vs_oracle(kind, d, nleap, eps):
+    pm, om = _models(kind, d)
+    C = 47
+    rng = np.random.default_rng(d + 1)
+    q, p = rng.uniform(-1, 1, (C, d)), rng.standard_normal((C, d))
+    if kind == "rosenbrock":
+        q = 1.0 + 0.1 * q
+    P, U = replay.make_draws(500 + d, 1, C, d, 3)
+    s = algorithms.DRGHMC(pm, device=_dev())
+    gq, gp, code, avec, counts = s.step(q, p, nleap, eps, 0.6, 3, 2.0, pn=P[0], u=U[0])
+    ref = [samplers.drghmc_step(om, q[c], p[c], nleap, eps, 0.6, 3, 2.0, replay.Draws([P[0, c]], U[0, c])) for c in range(C)]
+    assert np.array_equal(code, [r[2] for r in ref])
+    assert np.array_equal(counts, [r[4] for r in ref])
+    _close(gq, np.array([r[0] for r in ref]), rtol=1e-9, atol=1e-10)
+    _close(gp, np.array([r[1] for r in ref]), rtol=1e-9, atol=1e-10)   # p0 (unflipped) on rejection
+    _close(avec, np.array([r[3] for r in ref]), rtol=1e-8, atol=1e-12)
+
+
+def test_ghmc_sample_keeps_the_gaussian_invariant():
+    dev = _dev()
+    d, C = 20, 1 << 14
+    pm = models.CorrGaussian.ar1(d)
+    Lc = np.linalg.cholesky(pm.Sigma)
+    g = torch.Generator().manual_seed(0)
+    q0 = (torch.randn(C, d, generator=g, dtype=torch.float64) @ torch.as_tensor(Lc).T).to(dev)
+    for name, kw in (("ghmc", dict(alpha=0.7)), ("pghmc", dict(alpha=0.7, delta=0.3)), ("drghmc", dict(alpha=0.7, nprops=2, stepfactor=2.0))):
+        s = algorithms.alg_dict[name](pm, device=dev, seed=3)
+        st = s.sample(q0, nsamples=12, burnin=0, step_size=0.25, nleap=3, **kw)
+        q = st.samples[-1]
+        assert abs(q.mean().item()) < 0.03, name
+        assert abs(q.std(dim=0).mean().item() - 1.0) < 0.03, name

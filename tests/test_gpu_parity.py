@@ -245,3 +245,25 @@ def test_nan_and_no_move_codes():
         rq, rp, rcode, rHs, rcounts = _run_oracle_hmc(om, q0, P, U, 5, 0.1, rule)
         assert np.array_equal(code, rcode) and code[0] == bad
         _close(q, rq)
+
+
+@pytest.mark.parametrize("kind,d,N,eps", [("funnel", 10, 6, 0.6), ("funnel", 50, 10, 0.35), ("rosenbrock", 10, 8, 0.1)])
+@pytest.mark.parametrize("m,fsub", [(1, 2.0), (2, 2.0), (3, 2.0), (4, 1.5)])
+def test_pyhmc_multistep_vs_oracle(kind, d, N, eps, m, fsub):
+    """pyhmc.PyHMC_multistep.multi_step: codes j/-1, first-stage <=, Hcount incl. ghost base energies."""
+    spec = dict(kind=kind, d=d)
+    om, pmodel = _oracle_model(spec), _product_model(spec)
+    C = 53
+    q0 = np.random.default_rng(m * 17 + d).uniform(-1, 1, (C, d))
+    if kind == "rosenbrock":
+        q0 = 1.0 + 0.1 * q0
+    P, U = replay.make_draws(2000 + d + m, 1, C, d, m)
+    U[0, 0, 0] = 0.0          # u == 0 with alpha_0 == 0 would split "<" from "<="; here it must accept unless alpha_0 < 0
+    s = pyhmc.PyHMC_multistep(pmodel, device=_dev())
+    q, p, code, avec, counts = s.multi_step(m, q0, N, eps, fsub, p=P[0], u=U[0])
+    ref = [samplers.multistep_step(om, m, q0[c], N, eps, fsub, replay.Draws([P[0, c]], U[0, c])) for c in range(C)]
+    assert np.array_equal(code, [r[2] for r in ref])
+    assert np.array_equal(counts, [r[4] for r in ref])
+    _close(avec, np.array([r[3] for r in ref]), rtol=1e-8, atol=1e-12)
+    _close(q, np.array([r[0] for r in ref]), rtol=1e-9, atol=1e-10)
+    assert code[0] == 0       # the u = 0 chain accepted at the first stage (<=)

@@ -162,3 +162,80 @@ def test_utils_ess_rcc_bit_exact():
         assert _same(a, b)
     (r1, t1), (r2, t2) = utils.get_rcc(x), samplers.get_rcc(x)
     assert _same(r1, r2) and _same(t1, t2)
+
+
+@pytest.mark.parametrize("mi", [0, 1, 3])
+@pytest.mark.parametrize("m,fsub", [(1, 2), (2, 2), (3, 2), (4, 1.5)])
+def test_pyhmc_multistep_bit_exact(mi, m, fsub):
+    pyhmc = ref_loader.load("pyhmc")
+    model = _models()[mi]
+    ref = pyhmc.PyHMC_multistep(model.log_prob, model.grad_log_prob)
+    T = 25
+    P, U = replay.make_draws(71 + mi, T, 1, model.d, m)
+    q_r = q_o = _q0(model, mi)
+    eps, N = (0.35, 7) if model.name == "funnel" else (0.08, 7)
+    codes = []
+    for t in range(T):
+        with replay.patched_numpy_random(replay.Draws([P[t, 0]], U[t, 0])):
+            out_r = ref.multi_step(m, q_r, N, eps, fsub)
+        out_o = samplers.multistep_step(model, m, q_o, N, eps, fsub, replay.Draws([P[t, 0]], U[t, 0]))
+        for a, b in zip(out_r, out_o):
+            assert _same(a, b)
+        q_r, q_o = out_r[0], out_o[0]
+        codes.append(out_r[2])
+    if m >= 2 and model.name == "funnel":
+        assert len(set(codes)) >= 2
+
+
+@pytest.mark.parametrize("mi", [0, 1, 2, 3])
+@pytest.mark.parametrize("alpha", [0.0, 0.7])
+def test_ghmc_and_pghmc_bit_exact(mi, alpha):
+    alg = ref_loader.load("algorithms")
+    model = _models()[mi]
+    g_ref = alg.GHMC(model.log_prob, model.grad_log_prob, model.log_prob_and_grad)
+    pg_ref = alg.Persistent_GHMC(model.log_prob, model.grad_log_prob, model.log_prob_and_grad)
+    T = 20
+    P, U = replay.make_draws(81 + mi, T, 1, model.d, 1)
+    q0 = _q0(model, mi)
+    p0 = np.random.default_rng(5).standard_normal(model.d)
+    eps, N = (0.12, 4) if model.name != "rosenbrock" else (0.03, 4)
+    # GHMC
+    sr = (q0, p0, None, None)
+    so = (q0, p0, None, None)
+    for t in range(T):
+        with replay.patched_numpy_random(replay.Draws([P[t, 0]], U[t, 0])):
+            out_r = g_ref.step(sr[0], sr[1], N, eps, alpha, V_q=sr[2], V_gq=sr[3])
+        out_o = samplers.ghmc_step(model, so[0], so[1], N, eps, alpha, replay.Draws([P[t, 0]], U[t, 0]), so[2], so[3])
+        for a, b in zip(out_r, out_o):
+            assert _same(a, b)
+        sr, so = out_r[:4], out_o[:4]
+    # persistent GHMC (uniform carried)
+    sr = (q0, p0, 0.3, None, None)
+    so = (q0, p0, 0.3, None, None)
+    for t in range(T):
+        with replay.patched_numpy_random(replay.Draws([P[t, 0]], [])):
+            out_r = pg_ref.step(sr[0], sr[1], sr[2], N, eps, alpha, 0.37, V_q=sr[3], V_gq=sr[4])
+        out_o = samplers.pghmc_step(model, so[0], so[1], so[2], N, eps, alpha, 0.37, replay.Draws([P[t, 0]], []), so[3], so[4])
+        for a, b in zip(out_r, out_o):
+            assert _same(a, b)
+        sr, so = out_r[:5], out_o[:5]
+
+
+@pytest.mark.parametrize("mi", [0, 3])
+def test_drghmc_bit_exact(mi, capsys):
+    alg = ref_loader.load("algorithms")
+    model = _models()[mi]
+    ref = alg.DRGHMC(model.log_prob, model.grad_log_prob)
+    T = 20
+    P, U = replay.make_draws(91 + mi, T, 1, model.d, 3)
+    q_r = q_o = _q0(model, mi)
+    p_r = p_o = np.random.default_rng(6).standard_normal(model.d)
+    eps, nleap = (0.35, 7) if model.name == "funnel" else (0.08, 7)
+    for t in range(T):
+        with replay.patched_numpy_random(replay.Draws([P[t, 0]], U[t, 0])):
+            out_r = ref.step(q_r, p_r, nleap, eps, 0.6, 3, 2)
+        out_o = samplers.drghmc_step(model, q_o, p_o, nleap, eps, 0.6, 3, 2, replay.Draws([P[t, 0]], U[t, 0]))
+        for a, b in zip(out_r, out_o):
+            assert _same(a, b)
+        q_r, p_r, q_o, p_o = out_r[0], out_r[1], out_o[0], out_o[1]
+    capsys.readouterr()

@@ -49,13 +49,13 @@ def _call(lib, static, q, iteration, dev):
                                              out["counts"].data_ptr())
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
     if static:
-        rc = lib.hmcb_drhmc_step_static(C.byref(m), C.byref(ch), C.byref(r), NLEAP, EPS, NPROPS, FACTOR, C.byref(so),
+        rc = lib.hmcb_drhmc_step_static(C.byref(m), C.byref(ch), C.byref(r), NLEAP, EPS, NPROPS, FACTOR, 0, C.byref(so),
                                         stream)
     else:
         need = lib.hmcb_drhmc_workspace_bytes(C.byref(m), n, NPROPS)
         assert 0 < need
         ws = torch.empty(need, dtype=torch.uint8, device=dev)
-        rc = lib.hmcb_drhmc_step(C.byref(m), C.byref(ch), C.byref(r), NLEAP, EPS, NPROPS, FACTOR, C.byref(so),
+        rc = lib.hmcb_drhmc_step(C.byref(m), C.byref(ch), C.byref(r), NLEAP, EPS, NPROPS, FACTOR, 0, C.byref(so),
                                  C.c_void_p(ws.data_ptr()), need, None, stream)
     assert rc == 0, lib.hmcb_last_error()
     torch.cuda.synchronize(dev)
@@ -102,7 +102,7 @@ def test_static_scratch_refuses_oversized_batches():
         assert need > _lib.STATIC_SCRATCH_BYTES
         ch = _lib.Chains(n, 0, q.data_ptr(), qo.data_ptr(), q.stride(0), q.stride(1))
         r, so = _lib.Rng(), _lib.StepOut()
-        rc = lib.hmcb_drhmc_step_static(C.byref(m), C.byref(ch), C.byref(r), NLEAP, EPS, NPROPS, FACTOR, C.byref(so),
+        rc = lib.hmcb_drhmc_step_static(C.byref(m), C.byref(ch), C.byref(r), NLEAP, EPS, NPROPS, FACTOR, 0, C.byref(so),
                                         None)
     assert rc == _lib.E_WORKSPACE
     msg = lib.hmcb_last_error().decode()
