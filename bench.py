@@ -1,8 +1,11 @@
 #!/usr/bin/env python
 """Benchmark of the sampler hot path on the BASELINE.json headline workload:
 Neal's funnel d=50, delayed-rejection HMC (nleap=150, step 0.2 -> lpath 30 as
-scripts_old/jobscripts/run_funnel2.sh:21-22; nprops=3, stepfactor=2), 2^20 chains
-sharded over N GPUs (strong scaling: the chain count is fixed by the config).
+scripts_old/jobscripts/run_funnel2.sh:21-22; nprops=3, stepfactor=2), 2^20 chains.
+Chains are independent, so N GPUs shard them by global chain id with no data-path
+collective.  Default: weak scaling -- every GPU runs the N=1 workload (2^20 chains per
+GPU, N*2^20 in total); `--scaling strong` keeps 2^20 chains in total, as the BASELINE
+config words it.
 
 A "step" is one DRHMC transition of every chain.  Prints ONE JSON line.
   value  : gradient evaluations/s (the reference's Vgcount counter, src/pyhmc.py:21-23),
@@ -37,7 +40,8 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="hmcb", choices=["hmcb", "reference"])
-    ap.add_argument("--chains", type=int, default=1 << 20)
+    ap.add_argument("--chains", type=int, default=1 << 20, help="chains per GPU (weak) / in total (strong)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--ndim", type=int, default=50)
     ap.add_argument("--nleap", type=int, default=150)
     ap.add_argument("--step_size", type=float, default=0.2)
@@ -141,7 +145,7 @@ def run_reference(a):
     val = grads / dt
     line = {"impl": "reference", "metric": "grad_evals_per_sec", "value": val, "unit": "grad_evals/s",
             "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * dt / a.steps,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "higher_is_better": True, "scaling": a.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(a, sample="each step = %d chains x %d processes x 1 transition" % (m, arm.P)),
             "cpu_baseline": {"value": val, "unit": "grad_evals/s", "cores": arm.P, "kind": "port",
                              "sample": "%d steps of %d chain-transitions on %d processes" % (a.steps, m * arm.P, arm.P)},
@@ -150,12 +154,19 @@ def run_reference(a):
     print(json.dumps(line), flush=True)
 
 
+def total_chains(a):
+    n = int(os.environ.get("WORLD_SIZE", "1"))
+    return a.chains * n if a.scaling == "weak" else a.chains
+
+
 def workload_config(a, **extra):
-    cfg = {"workload": "funnel d=%d sigma=3, DRHMC nleap=%d step_size=%g nprops=%d stepfactor=%g, %d chains total, "
-                       "q0~U(-1,1), %d burn-in transitions before timing" %
-                       (a.ndim, a.nleap, a.step_size, a.nprops, a.stepfactor, a.chains, a.burnin),
-           "chains": a.chains, "d": a.ndim, "cache": "inputs larger than L2 (q is %.0f MB per rank at N=1)" %
-                                                    (a.chains * a.ndim * 8 / 1e6)}
+    n = int(os.environ.get("WORLD_SIZE", "1"))
+    tot = total_chains(a)
+    cfg = {"workload": "funnel d=%d sigma=3, DRHMC nleap=%d step_size=%g nprops=%d stepfactor=%g, %d chains total "
+                       "(%d per GPU, %s scaling), q0~U(-1,1), %d burn-in transitions before timing" %
+                       (a.ndim, a.nleap, a.step_size, a.nprops, a.stepfactor, tot, tot // n, a.scaling, a.burnin),
+           "chains": tot, "chains_per_gpu": tot // n, "d": a.ndim,
+           "cache": "inputs larger than L2 (q is %.0f MB per rank)" % (tot // n * a.ndim * 8 / 1e6)}
     cfg.update(extra)
     return cfg
 
@@ -213,7 +224,8 @@ def run_hmcb(a):
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    lo, hi = dist.shard_range(a.chains)
+    n_total = total_chains(a)
+    lo, hi = dist.shard_range(n_total)
     C, d = hi - lo, a.ndim
 
     model = models.Funnel(d)
@@ -221,7 +233,11 @@ def run_hmcb(a):
     eng = dr.engine
     eng._ensure()
     g = torch.Generator().manual_seed(a.seed)
-    q = (torch.rand(a.chains, d, generator=g, dtype=torch.float64) * 2 - 1)[lo:hi].to(dev).contiguous()
+    if a.scaling == "strong":   # one global array, sliced: chain statistics do not depend on N
+        q = (torch.rand(n_total, d, generator=g, dtype=torch.float64) * 2 - 1)[lo:hi].to(dev).contiguous()
+    else:                       # per-shard stream (no N*2^20 x d host array); shard 0 is the N=1 workload
+        g.manual_seed(a.seed + 7919 * rank)
+        q = (torch.rand(C, d, generator=g, dtype=torch.float64) * 2 - 1).to(dev).contiguous()
     nxt = torch.empty_like(q)
 
     K = a.steps
@@ -358,13 +374,13 @@ def run_hmcb(a):
     if not a.no_cpu_baseline and world == 1:
         cpu = cpu_baseline(a, a.cpu_seconds)
     line = {"metric": "grad_evals_per_sec", "value": value, "unit": "grad_evals/s", "n_gpus": world, "steps": K,
-            "warmup": a.warmup, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "strong",
+            "warmup": a.warmup, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": a.scaling,
             "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(a),
             "leapfrog_steps_per_sec": (grads - leaps) / sec,
             "ess_per_sec": ess_min / sec, "ess_min": ess_min, "ess_note": "min over dims of utils.get_ess_true over the "
             "%d timed transitions of all chains (analytic funnel mean/std); chains started at U(-1,1), so it includes "
             "remaining burn-in bias" % K,
-            "grad_evals_per_transition": grads / (K * a.chains), "accept_rate": float(stats[-1]) / a.chains,
+            "grad_evals_per_transition": grads / (K * n_total), "accept_rate": float(stats[-1]) / n_total,
             "rhat_max": float(rhat.max()), "v_mean": float(mean[0]), "v_std": float(std[0]),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks.summary(t_wall0, t_wall1),
             "device_busy_frac": (sum(st_ms) + 0.35) / (ms_total / K),
