@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "extra_kernels.cuh"
+#include "transition_ws.cuh"
 
 namespace hmcb {
 
@@ -147,6 +148,29 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
   };
 
   int max_blocks = 0, rc;
+  // thread-per-chain float64 shapes with a long RNG prologue: warp-specialised kernel (transition_ws.cuh)
+  if constexpr (LPC == 1 && UNITM && sizeof(T) == 8 && EPL >= 20 && !GAUSS) {
+    if ((op == OP_HMC || op == OP_DR0) && !getenv("HMCB_NO_WS")) {
+      TransArgs<T>& a = *(TransArgs<T>*)args;
+      if (!a.p_inject && !a.p_prev && a.n_chains >= 4096) {
+        const size_t ws_smem = 2 * (size_t)EPL * kWsComputeThreads * sizeof(float) + 64;
+        const int grid = (int)((a.n_chains + kWsComputeThreads - 1) / kWsComputeThreads < sm_count()
+                                   ? (a.n_chains + kWsComputeThreads - 1) / kWsComputeThreads
+                                   : sm_count());
+        if (op == OP_HMC) {
+          auto k = k_transition_ws<Model, T, EPL, MODE_HMC>;
+          HMCB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws_smem));
+          k<<<grid, kWsThreads, ws_smem, st>>>(model, a);
+        } else {
+          auto k = k_transition_ws<Model, T, EPL, MODE_DR0>;
+          HMCB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws_smem));
+          k<<<grid, kWsThreads, ws_smem, st>>>(model, a);
+        }
+        HMCB_CUDA(cudaPeekAtLastError());
+        return 0;
+      }
+    }
+  }
   switch (op) {
     case OP_HMC: {
       auto k = k_transition<Model, T, EPL, LPC, UNITM, MODE_HMC, THREADS, MINB>;

@@ -241,6 +241,92 @@ __device__ __forceinline__ void leapfrog(const Model& model, T (&q)[EPL], T (&p)
   V_end = model.template kick<EPL, LPC, true>(q, p, T(0.5) * eps, c);
 }
 
+// Everything of a single-trajectory transition (vanilla HMC step, or DR stage 0) after the
+// chain's position q and refreshed momentum p are in registers: energies, trajectory, no-move
+// test, accept rule, outputs, and for DR the hand-over of rejected chains to stage 1.  Shared by
+// the plain kernel below and the warp-specialised one (k_transition_ws).
+template <class Model, typename T, int EPL, int LPC, bool UNITM, int MODE>
+__device__ __forceinline__ void finish_single(const Model& model, const TransArgs<T>& a, const GroupCtx<T>& c,
+                                              const T (&minv)[UNITM ? 1 : EPL], int64_t chain, int64_t qoff,
+                                              T (&q)[EPL], T (&p)[EPL]) {
+  using Lay = Layout<EPL, LPC>;
+  const int d = a.d;
+  int cH, cVg, cLeap;
+    const T K0 = kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+    T V0, V1;
+    const int N = a.L[0] > 1 ? a.L[0] : 1;
+    leapfrog<Model, T, EPL, LPC, UNITM>(model, q, p, minv, N, a.eps[0], c, V0, V1);
+    const T H0 = V0 + K0;
+    const T H1 = V1 + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+    cH = 2; cVg = N + 1; cLeap = 1;
+    // sum(q0 - q1) == 0 is the reference's "did not move" test (src/pyhmc.py:57)
+    T dq = diff_sum<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d);
+    dq = group_sum_masked<LPC, T>(dq, c.mask);
+    T prob = t_exp<T>(H0 - H1);
+
+    bool accept;
+    int code;
+    bool finished = true;
+    if (MODE == MODE_HMC) {
+      const bool bad = t_bad(prob) || dq == T(0);
+      const double u = draw_uniform<T>(a, chain, 0);
+      const T pm = prob < T(1) ? prob : T(1);
+      accept = !bad && !(u > (double)pm);
+      code = bad ? (a.rule == HMCB_RULE_PYHMC ? 2 : -1) : (accept ? 1 : 0);
+      if (c.lane == 0) {
+        if (a.energies) { a.energies[2 * chain] = H0; a.energies[2 * chain + 1] = H1; }
+        if (a.accept_prob) a.accept_prob[chain] = (accept && !t_bad(prob)) ? pm : T(0);
+      }
+    } else {
+      if (dq == T(0)) prob = T(0);
+      if (t_bad(prob)) prob = T(0);
+      const T a0 = prob < T(1) ? prob : T(1);
+      const double u = draw_uniform<T>(a, chain, 0);
+      // algorithms.DRHMC: acc < avec[0] (src/algorithms.py:528); PyHMC_multistep's first stage: acc <= avec[0]
+      // (src/pyhmc.py:580) and codes j / -1 instead of j+1 / 0
+      accept = a.dr_conv ? (u <= (double)a0) : (u < (double)a0);
+      code = a.dr_conv ? (accept ? 0 : -1) : (accept ? 1 : 0);
+      finished = accept || a.nprops == 1;
+      if (c.lane == 0) {
+        if (finished) {
+          if (a.avec_out) {
+            a.avec_out[chain * a.nprops] = a0;
+            for (int i = 1; i < a.nprops; ++i) a.avec_out[chain * a.nprops + i] = T(0);
+          }
+        } else {
+          a.ws.H0[chain] = H0;
+          a.ws.avec[chain * kMaxProps] = a0;
+          a.ws.counts[3 * chain] = cH; a.ws.counts[3 * chain + 1] = cVg; a.ws.counts[3 * chain + 2] = cLeap;
+          // plain atomicAdd (the compiler aggregates it per warp): a cooperative-groups coalesced_threads()
+          // here cost the trajectory loop its register allocation in the warp-specialised kernel
+          // (3 spills + 25 moves per leapfrog step at EPL = 50)
+          const int slot = atomicAdd(a.ws.count + 1, 1);
+          a.ws.list[(int64_t)1 * a.n_chains + slot] = (int32_t)chain;
+        }
+      }
+    }
+    if (finished && c.lane == 0) {
+      if (a.code) a.code[chain] = code;
+      if (a.counts) { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = cLeap; }
+    }
+    if (accept) {
+      store_vec<T, EPL, LPC>(q, a.q_out, qoff, a.sd, c.lane, d);
+      if (a.p_out) store_vec<T, EPL, LPC>(p, a.p_out, qoff, a.sd, c.lane, d);
+    } else if (finished) {
+      if (a.q_out != a.q_in) {
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) {
+          const int i = Lay::elem(c.lane, s);
+          if (i < d) a.q_out[qoff + i * a.sd] = a.q_in[qoff + i * a.sd];
+        }
+      }
+      if (a.p_out) {
+        draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);
+        store_vec<T, EPL, LPC>(p, a.p_out, qoff, a.sd, c.lane, d);
+      }
+    }
+}
+
 // ------------------------------------------------------------------ the kernel
 // Threads are grouped LPC lanes per chain; a warp carries 32/LPC chains.  Work
 // items (chains, or entries of the stage list) are walked grid-stride so a
@@ -294,81 +380,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
       // ---------------- single trajectory from (q0, p0): HMC step or DR stage 0
       load_vec<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d, T(1));    // loads in flight under the RNG
       draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);
-      const T K0 = kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
-      T V0, V1;
-      const int N = a.L[0] > 1 ? a.L[0] : 1;
-      leapfrog<Model, T, EPL, LPC, UNITM>(model, q, p, minv, N, a.eps[0], c, V0, V1);
-      const T H0 = V0 + K0;
-      const T H1 = V1 + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
-      cH = 2; cVg = N + 1; cLeap = 1;
-      // sum(q0 - q1) == 0 is the reference's "did not move" test (src/pyhmc.py:57)
-      T dq = diff_sum<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d);
-      dq = group_sum_masked<LPC, T>(dq, c.mask);
-      T prob = t_exp<T>(H0 - H1);
-
-      bool accept;
-      int code;
-      bool finished = true;
-      if (MODE == MODE_HMC) {
-        const bool bad = t_bad(prob) || dq == T(0);
-        const double u = draw_uniform<T>(a, chain, 0);
-        const T pm = prob < T(1) ? prob : T(1);
-        accept = !bad && !(u > (double)pm);
-        code = bad ? (a.rule == HMCB_RULE_PYHMC ? 2 : -1) : (accept ? 1 : 0);
-        if (c.lane == 0) {
-          if (a.energies) { a.energies[2 * chain] = H0; a.energies[2 * chain + 1] = H1; }
-          if (a.accept_prob) a.accept_prob[chain] = (accept && !t_bad(prob)) ? pm : T(0);
-        }
-      } else {
-        if (dq == T(0)) prob = T(0);
-        if (t_bad(prob)) prob = T(0);
-        const T a0 = prob < T(1) ? prob : T(1);
-        const double u = draw_uniform<T>(a, chain, 0);
-        // algorithms.DRHMC: acc < avec[0] (src/algorithms.py:528); PyHMC_multistep's first stage: acc <= avec[0]
-        // (src/pyhmc.py:580) and codes j / -1 instead of j+1 / 0
-        accept = a.dr_conv ? (u <= (double)a0) : (u < (double)a0);
-        code = a.dr_conv ? (accept ? 0 : -1) : (accept ? 1 : 0);
-        finished = accept || a.nprops == 1;
-        if (c.lane == 0) {
-          if (finished) {
-            if (a.avec_out) {
-              a.avec_out[chain * a.nprops] = a0;
-              for (int i = 1; i < a.nprops; ++i) a.avec_out[chain * a.nprops + i] = T(0);
-            }
-          } else {
-            a.ws.H0[chain] = H0;
-            a.ws.avec[chain * kMaxProps] = a0;
-            a.ws.counts[3 * chain] = cH; a.ws.counts[3 * chain + 1] = cVg; a.ws.counts[3 * chain + 2] = cLeap;
-            cg::coalesced_group g = cg::coalesced_threads();
-            int base = 0;
-            if (g.thread_rank() == 0) base = atomicAdd(a.ws.count + 1, (int)g.size());
-            base = g.shfl(base, 0);
-            a.ws.list[(int64_t)1 * a.n_chains + base + g.thread_rank()] = (int32_t)chain;
-          }
-        }
-      }
-      if (finished) {
-        if (c.lane == 0) {
-          if (a.code) a.code[chain] = code;
-          if (a.counts) { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = cLeap; }
-        }
-        if (accept) {
-          store_vec<T, EPL, LPC>(q, a.q_out, qoff, a.sd, c.lane, d);
-          if (a.p_out) store_vec<T, EPL, LPC>(p, a.p_out, qoff, a.sd, c.lane, d);
-        } else {
-          if (a.q_out != a.q_in) {
-#pragma unroll
-            for (int s = 0; s < EPL; ++s) {
-              const int i = Lay::elem(c.lane, s);
-              if (i < d) a.q_out[qoff + i * a.sd] = a.q_in[qoff + i * a.sd];
-            }
-          }
-          if (a.p_out) {
-            draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);
-            store_vec<T, EPL, LPC>(p, a.p_out, qoff, a.sd, c.lane, d);
-          }
-        }
-      }
+      finish_single<Model, T, EPL, LPC, UNITM, MODE>(model, a, c, minv, chain, qoff, q, p);
     } else {
       // ---------------- DR stage J >= 1: explicit-stack walk of step/get_num
       // level 0 is DRHMC.step's own loop at j = J; level l >= 1 is a get_num frame

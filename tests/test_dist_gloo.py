@@ -75,3 +75,34 @@ def test_world_size_2_moment_reductions_match_single_process():
         assert np.allclose(s, xm.reshape(-1, d).std(axis=0), rtol=1e-10)
         assert np.isclose(eps, eps_ref, rtol=1e-12)
     assert res[0][6] == res[1][6]
+
+
+def _gather_worker(rank, world, port, x, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    from hmc_b200 import results
+    dist.init_from_env(backend="gloo")
+    lo, hi = dist.shard_range(x.shape[1])
+    got = results.gather_to_rank0(x[:, lo:hi].contiguous())
+    q.put((rank, None if got is None else np.asarray(got)))
+    dist.barrier()
+    torch.distributed.destroy_process_group()
+
+
+@pytest.mark.timeout(120)
+def test_world_size_2_gather_restores_global_chain_order():
+    """results.gather_to_rank0 stands in for comm.gather + concatenate(axis=1)
+    (scripts_old/funnel/funnelmpi.py:193-201); ragged shards."""
+    x = torch.arange(6 * 7 * 3, dtype=torch.float64).reshape(6, 7, 3)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gather_worker, args=(r, 2, port, x, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=100) for _ in procs)
+    for p in procs:
+        p.join(timeout=30)
+        assert p.exitcode == 0
+    assert res[1] is None
+    assert np.array_equal(res[0], x.numpy())

@@ -1,0 +1,143 @@
+// kbench_ws.cu -- experiment: warp-specialised HMC transition kernel.  Two compute warpgroups
+// (256 threads, one chain each, state in registers, 240 registers after setmaxnreg.inc) and one
+// helper warpgroup (128 threads, 32 registers) that generates the NEXT round's momenta into a
+// double-buffered shared-memory tile while the compute warps integrate, so the compute warps'
+// per-transition prologue no longer contains the random-number generation.
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#include "../hmc_b200/csrc/launch.cuh"
+#include "../hmc_b200/csrc/sync_ptx.cuh"   // mbarrier helpers
+
+namespace hmcb {
+void set_error(const char*, ...) {}
+int cuda_fail(cudaError_t e, const char* what) { fprintf(stderr, "CUDA %s at %s\n", cudaGetErrorString(e), what); return -3; }
+int sm_count() { return 148; }
+int max_optin_smem() { return 232448; }
+std::vector<Entry>& registry() { static std::vector<Entry> r; return r; }
+
+template <int EPL>
+__global__ void __launch_bounds__(384, 1) k_hmc_ws(const FunnelModel<double> model, const TransArgs<double> a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float* sP = reinterpret_cast<float*>(smem_raw);                        // [2][EPL][256]
+  uint64_t* full = reinterpret_cast<uint64_t*>(sP + 2 * EPL * 256);
+  uint64_t* empty = full + 2;
+  const int tid = threadIdx.x, wg = tid >> 7;
+  if (tid == 0) {
+    for (int s = 0; s < 2; ++s) { lr::mbar_init(full + s, 128); lr::mbar_init(empty + s, 256); }
+    lr::fence_barrier_init();
+  }
+  __syncthreads();
+  const int d = a.d;
+  const int64_t per_round = (int64_t)gridDim.x * 256;
+  const int rounds = (int)((a.n_chains + per_round - 1) / per_round);
+  if (wg == 2) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+    const int ht = tid - 256;
+    for (int r = 0; r < rounds; ++r) {
+      const int s = r & 1;
+      lr::mbar_wait(empty + s, ((r >> 1) & 1) ^ 1);
+      float* dst = sP + (size_t)s * EPL * 256;
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h) {
+        const int c = ht + 128 * h;
+        const int64_t chain = ((int64_t)r * gridDim.x + blockIdx.x) * 256 + c;
+        if (chain < a.n_chains) {
+          const uint64_t gchain = (uint64_t)(a.chain_offset + chain);
+#pragma unroll 1
+          for (int b = 0; b < (EPL + 3) / 4; ++b) {
+            uint32_t w[4];
+            float z[4];
+            Philox::gen(a.seed, gchain, a.iteration, STREAM_MOMENTUM, (uint32_t)b, w);
+            normal4_f32(w, z);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              if (4 * b + k < EPL) dst[(4 * b + k) * 256 + c] = (4 * b + k < d) ? z[k] : 0.f;
+          }
+        }
+      }
+      lr::mbar_arrive(full + s);
+    }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 240;");
+    GroupCtx<double> c;
+    c.lane = 0; c.d = d; c.mask = 0xffffffffu; c.smem_q = nullptr;
+    double minv[1] = {1.0};
+    for (int r = 0; r < rounds; ++r) {
+      const int s = r & 1;
+      const int64_t chain = ((int64_t)r * gridDim.x + blockIdx.x) * 256 + tid;
+      const bool live = chain < a.n_chains;
+      const int64_t qoff = (live ? chain : 0) * a.sc;
+      double q[EPL], p[EPL];
+      load_vec<double, EPL, 1>(q, a.q_in, qoff, a.sd, 0, d, 1.0);
+      lr::mbar_wait(full + s, (r >> 1) & 1);
+      const float* src = sP + (size_t)s * EPL * 256 + tid;
+#pragma unroll
+      for (int k = 0; k < EPL; ++k) p[k] = (double)src[k * 256];
+      lr::mbar_arrive(empty + s);
+      if (!live) continue;
+      const double K0 = kinetic<double, EPL, 1, true>(p, minv, c.mask);
+      double V0, V1;
+      const int N = a.L[0] > 1 ? a.L[0] : 1;
+      leapfrog<FunnelModel<double>, double, EPL, 1, true>(model, q, p, minv, N, a.eps[0], c, V0, V1);
+      const double H0 = V0 + K0;
+      const double H1 = V1 + kinetic<double, EPL, 1, true>(p, minv, c.mask);
+      const double dq = diff_sum<double, EPL, 1>(q, a.q_in, qoff, a.sd, 0, d);
+      const double prob = exp(H0 - H1);
+      const bool bad = t_bad(prob) || dq == 0.0;
+      const double u = draw_uniform<double>(a, chain, 0);
+      const double pm = prob < 1.0 ? prob : 1.0;
+      const bool accept = !bad && !(u > pm);
+      if (a.code) a.code[chain] = bad ? 2 : (accept ? 1 : 0);
+      if (accept) {
+        store_vec<double, EPL, 1>(q, a.q_out, qoff, a.sd, 0, d);
+      } else if (a.q_out != a.q_in) {
+        load_vec<double, EPL, 1>(q, a.q_in, qoff, a.sd, 0, d, 1.0);
+        store_vec<double, EPL, 1>(q, a.q_out, qoff, a.sd, 0, d);
+      }
+    }
+  }
+}
+}  // namespace hmcb
+
+using namespace hmcb;
+
+int main(int argc, char** argv) {
+  const int64_t C = argc > 1 ? atoll(argv[1]) : (1 << 20);
+  const int L = argc > 2 ? atoi(argv[2]) : 150;
+  const int d = 50;
+  constexpr int EPL = 50;
+  double *q, *qo; int* code;
+  cudaMalloc(&q, C * d * 8); cudaMalloc(&qo, C * d * 8); cudaMalloc(&code, C * 4);
+  std::vector<double> h(C * d);
+  srand(1);
+  for (auto& x : h) x = 2.0 * rand() / RAND_MAX - 1.0;
+  cudaMemcpy(q, h.data(), C * d * 8, cudaMemcpyHostToDevice);
+  hmcb_model hm{}; hm.kind = HMCB_MODEL_FUNNEL; hm.d = d; hm.dtype = HMCB_F64; hm.par[0] = 3.0;
+  auto model = FunnelModel<double>::make(hm);
+  TransArgs<double> a{};
+  a.n_chains = C; a.d = d; a.q_in = q; a.q_out = qo; a.sc = d; a.sd = 1; a.seed = 1; a.nprops = 1; a.L[0] = L; a.eps[0] = 0.05; a.code = code;
+  const size_t smem = 2 * EPL * 256 * 4 + 64;
+  auto k = k_hmc_ws<EPL>;
+  cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaFuncAttributes fa; cudaFuncGetAttributes(&fa, k);
+  const int grid = (int)std::min<int64_t>((C + 255) / 256, 148);
+  cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+  float best = 1e30f;
+  for (int r = 0; r < 5; ++r) {
+    a.iteration = r;
+    cudaEventRecord(e0);
+    k<<<grid, 384, smem>>>(model, a);
+    cudaEventRecord(e1); cudaEventSynchronize(e1);
+    float ms; cudaEventElapsedTime(&ms, e0, e1); if (r && ms < best) best = ms;
+  }
+  cudaError_t err = cudaDeviceSynchronize();
+  std::vector<int> hc(C);
+  cudaMemcpy(hc.data(), code, C * 4, cudaMemcpyDeviceToHost);
+  long acc = 0; for (auto v : hc) acc += v == 1;
+  const double ach = (double)C * (L + 1) * 7.0 * d / (best * 1e-3) / 1e12;
+  printf("WS EPL=%d regs=%d stack=%zu grid=%d C=%lld L=%d: %.3f ms  %.2f TF/s algorithmic = %.3f of 36.7  accept %.3f (%s)\n", EPL,
+         fa.numRegs, fa.localSizeBytes, grid, (long long)C, L, best, ach, ach / 36.7, (double)acc / C, cudaGetErrorString(err));
+  return 0;
+}
