@@ -311,6 +311,7 @@ def run_hmcb(a):
                             dtype=torch.float64, device=dev)
     n_stage1 = (code_log[:K] != 1).sum(dim=1).double().mean()
     acc_rate = (code_log[:K] > 0).double().mean()
+    code_frac = (torch.bincount(code_log[:K].flatten().long(), minlength=a.nprops + 1).double() / (K * C)).tolist()
     stats = torch.cat([tot, stage_ms.mean(dim=0), n_stage1[None], acc_rate[None] * C])
     dist.all_reduce_sum(stats[:3])
     dist.all_reduce_sum(stats[-1:])
@@ -381,6 +382,8 @@ def run_hmcb(a):
             "%d timed transitions of all chains (analytic funnel mean/std); chains started at U(-1,1), so it includes "
             "remaining burn-in bias" % K,
             "grad_evals_per_transition": grads / (K * n_total), "accept_rate": float(stats[-1]) / n_total,
+            "code_fractions": {"note": "rank 0: fraction of chain-transitions by DRHMC code (0 = rejected at every "
+                               "stage, j+1 = accepted at stage j)", "by_code": code_frac},
             "rhat_max": float(rhat.max()), "v_mean": float(mean[0]), "v_std": float(std[0]),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks.summary(t_wall0, t_wall1),
             "device_busy_frac": (sum(st_ms) + 0.35) / (ms_total / K),

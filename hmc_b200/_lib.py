@@ -10,7 +10,7 @@ OK, E_ARG, E_UNSUPPORTED, E_CUDA, E_WORKSPACE = 0, -1, -2, -3, -4
 F64, F32 = 0, 1
 MODEL_FUNNEL, MODEL_GAUSSIAN, MODEL_ROSENBROCK, MODEL_LOGISTIC = 0, 1, 2, 3
 RULE_PYHMC, RULE_ALG = 0, 1
-DR_ALGORITHMS, DR_MULTISTEP = 0, 1
+DR_ALGORITHMS, DR_MULTISTEP, DR_PROB_METROP, DR_PROB_HASTINGS = 0, 1, 2, 3
 RNG_NORMAL_F64 = 1
 MAX_PROPS = 6
 STATIC_SCRATCH_BYTES = 32 << 20
@@ -43,7 +43,7 @@ class Profile(C.Structure):
 
 class StepOut(C.Structure):
     _fields_ = [("p_out", C.c_void_p), ("code", C.c_void_p), ("energies", C.c_void_p), ("avec", C.c_void_p),
-                ("counts", C.c_void_p), ("accept_prob", C.c_void_p)]
+                ("counts", C.c_void_p), ("accept_prob", C.c_void_p), ("ptries", C.c_void_p)]
 
 
 class MalaIO(C.Structure):

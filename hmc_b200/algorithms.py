@@ -374,5 +374,41 @@ def dr_stage_lengths(nleap, nprops, stepfactor):
 
 # name -> class registry (src/algorithms.py:823-832); the probabilistic-DR keys of the reference
 # ('pdrhmc_metrop', 'pdrhmc_hasting') are a later row of SURVEY.md section 8f
+class _ProbDRHMC(HMC):
+    """Probabilistic delayed rejection in src/algorithms.py: the classes add get_num and
+    multi_step to algorithms.HMC and inherit its step / sample unchanged."""
+    _convention = None
+
+    def multi_step(self, m, q0, N, ss, stepfactor, p=None, u=None):
+        """Returns (q, p, code, avec[m], [Hcount, Vgcount, leapcount], ptries[m]); code = accepting
+        stage j, -1 (rejected at every stage) or -2 (a stage was declined).  u, if given, holds
+        2m-1 uniforms per chain in consumption order: u_acc0, u_try1, u_acc1, ..."""
+        e = self.engine
+        b = self._device_q(q0)
+        out = e.drhmc_step(b.q, N, ss, m, stepfactor, p=p, u=u, convention=self._convention)
+        if b.unbatched:
+            cnt = out["counts"][0].tolist()
+            self.Hcount, self.Vgcount, self.leapcount = cnt
+            return (b.out(out["q"]), b.out(out["p"]), int(out["code"][0]), b.out(out["avec"]), cnt,
+                    b.out(out["ptries"]))
+        self.Hcount, self.Vgcount, self.leapcount = out["counts"][:, 0], out["counts"][:, 1], out["counts"][:, 2]
+        return (b.out(out["q"]), b.out(out["p"]), b.out(out["code"]), b.out(out["avec"]), b.out(out["counts"]),
+                b.out(out["ptries"]))
+
+
+class Prob_DRHMC_Metrop(_ProbDRHMC):
+    """algorithms.Prob_DRHMC_Metrop (src/algorithms.py:649-728): p_try_j = 1 - min(1, pi(prop_j)/pi(init))."""
+    _convention = _lib.DR_PROB_METROP
+
+
+class Prob_DRHMC_Hastings(_ProbDRHMC):
+    """algorithms.Prob_DRHMC_Hastings (src/algorithms.py:734-818): p_try_j = 1 - alpha_j.  The reference's
+    constructor takes (log_prob, grad_log_prob, invmetric_diag) only (:738-739)."""
+    _convention = _lib.DR_PROB_HASTINGS
+
+    def __init__(self, log_prob, grad_log_prob=None, invmetric_diag=None, **engine_kw):
+        super().__init__(log_prob, grad_log_prob, invmetric_diag=invmetric_diag, **engine_kw)
+
+
 alg_dict = {"hmc": HMC, "ghmc": GHMC, "pghmc": Persistent_GHMC, "drhmc": DRHMC, "drghmc": DRGHMC}
 

@@ -143,6 +143,7 @@ static void fill_args(TransArgs<T>& a, const hmcb_model* m, const hmcb_chains* c
     a.avec_out = (T*)o->avec;
     a.counts = o->counts;
     a.accept_prob = (T*)o->accept_prob;
+    a.ptries_out = (T*)o->ptries;
   }
   a.minv = (const T*)m->invmetric_diag;
 }
@@ -168,7 +169,7 @@ static int hmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c,
 
 // ------------------------------------------------------------------ DR workspace
 struct DrLayout {
-  size_t off_count, off_list, off_H0, off_avec, off_counts, off_frames, total;
+  size_t off_count, off_list, off_H0, off_avec, off_counts, off_ptries, off_frames, total;
   int64_t frame_threads;
 };
 
@@ -190,12 +191,17 @@ static int dr_layout(const Entry* e, const hmcb_model* m, int64_t n_chains, int 
   L.off_H0 = off;    off = align_up(off + (size_t)n_chains * ts, 256);
   L.off_avec = off;  off = align_up(off + (size_t)n_chains * kMaxProps * ts, 256);
   L.off_counts = off; off = align_up(off + (size_t)n_chains * 3 * sizeof(int32_t), 256);
+  L.off_ptries = off; off = align_up(off + (size_t)n_chains * kMaxProps * ts, 256);
   L.off_frames = off;
   const int nframes = nprops > 1 ? nprops - 1 : 0;
   off = align_up(off + (size_t)nframes * 2 * li.epl * L.frame_threads * ts, 256);
   L.total = off;
   return 0;
 }
+
+// uniforms one chain can consume in a DR transition: one per stage, plus one "try" draw before each later
+// stage under the probabilistic rules (consumption order u_acc0, u_try1, u_acc1, u_try2, ...)
+static int dr_uniforms(int nprops, int conv) { return conv >= HMCB_DR_PROB_METROP ? 2 * nprops - 1 : nprops; }
 
 template <typename T>
 static int drhmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r, int n_leap,
@@ -204,7 +210,9 @@ static int drhmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* 
   TransArgs<T> a;
   fill_args(a, m, c, r, o);
   a.nprops = nprops;
-  a.dr_conv = conv;
+  a.dr_conv = conv != HMCB_DR_ALGORITHMS;   // the probabilistic classes keep PyHMC_multistep's conventions
+  a.dr_prob = conv == HMCB_DR_PROB_METROP ? 1 : (conv == HMCB_DR_PROB_HASTINGS ? 2 : 0);
+  if (!a.dr_prob) a.ptries_out = nullptr;
   for (int j = 0; j < nprops; ++j) {
     // fac = stepfactor**j; nleapf = int(nleap*fac); step_sizef = step_size/fac (src/algorithms.py:510-511)
     const double fac = pow(stepfactor, (double)j);
@@ -217,6 +225,7 @@ static int drhmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* 
   a.ws.H0 = (T*)(w + L.off_H0);
   a.ws.avec = (T*)(w + L.off_avec);
   a.ws.counts = (int32_t*)(w + L.off_counts);
+  a.ws.ptries = (T*)(w + L.off_ptries);
   a.ws.frames = (T*)(w + L.off_frames);
   a.ws.frame_threads = L.frame_threads;
   if (nprops > 1) HMCB_CUDA(cudaMemsetAsync(a.ws.count, 0, (kMaxProps + 2) * sizeof(int32_t), st));
@@ -424,9 +433,10 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
   HMCB_CHECK_ARG(rng != nullptr, "rng is NULL");
   HMCB_CHECK_ARG(nprops >= 1 && nprops <= kMaxProps, "nprops=%d must be in 1..%d", nprops, kMaxProps);
   HMCB_CHECK_ARG(stepfactor > 0, "stepfactor must be > 0");
-  HMCB_CHECK_ARG(convention == HMCB_DR_ALGORITHMS || convention == HMCB_DR_MULTISTEP, "unknown DR convention %d", convention);
+  HMCB_CHECK_ARG(convention >= HMCB_DR_ALGORITHMS && convention <= HMCB_DR_PROB_HASTINGS, "unknown DR convention %d", convention);
   HMCB_CHECK_ARG(n_leap >= 0, "n_leap must be >= 0");
-  HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= nprops, "u_inject needs u_stride >= nprops");
+  HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= dr_uniforms(nprops, convention),
+                 "u_inject needs u_stride >= %d for nprops=%d under convention %d", dr_uniforms(nprops, convention), nprops, convention);
   if (chains->n_chains == 0) return 0;
   const Entry* e = choose_entry(*model);
   if (!e) return HMCB_E_UNSUPPORTED;
@@ -451,9 +461,10 @@ int hmcb_drhmc_step_static(const hmcb_model* model, const hmcb_chains* chains, c
   HMCB_CHECK_ARG(rng != nullptr, "rng is NULL");
   HMCB_CHECK_ARG(nprops >= 1 && nprops <= kMaxProps, "nprops=%d must be in 1..%d", nprops, kMaxProps);
   HMCB_CHECK_ARG(stepfactor > 0, "stepfactor must be > 0");
-  HMCB_CHECK_ARG(convention == HMCB_DR_ALGORITHMS || convention == HMCB_DR_MULTISTEP, "unknown DR convention %d", convention);
+  HMCB_CHECK_ARG(convention >= HMCB_DR_ALGORITHMS && convention <= HMCB_DR_PROB_HASTINGS, "unknown DR convention %d", convention);
   HMCB_CHECK_ARG(n_leap >= 0, "n_leap must be >= 0");
-  HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= nprops, "u_inject needs u_stride >= nprops");
+  HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= dr_uniforms(nprops, convention),
+                 "u_inject needs u_stride >= %d for nprops=%d under convention %d", dr_uniforms(nprops, convention), nprops, convention);
   if (chains->n_chains == 0) return 0;
   const Entry* e = choose_entry(*model);
   if (!e) return HMCB_E_UNSUPPORTED;

@@ -27,6 +27,7 @@ struct DrScratch {
   int32_t* list;     // [kMaxProps][n_chains] local chain ids queued for stage j
   T* H0;             // [n_chains] energy at (q0,p0)
   T* avec;           // [n_chains*kMaxProps] running stage acceptance probabilities
+  T* ptries;         // [n_chains*kMaxProps] running try probabilities (probabilistic DR only)
   int32_t* counts;   // [n_chains*3] running Hcount, Vgcount, leapcount
   T* frames;         // [(kMaxProps-1)*2*EPL*frame_threads] per-thread proposal frames
   int64_t frame_threads;
@@ -55,7 +56,9 @@ struct TransArgs {
   T* accept_prob;
   const T* minv;     // inverse metric diagonal or nullptr
   int32_t rule;      // HMCB_RULE_*
-  int32_t dr_conv;   // HMCB_DR_*: 0 algorithms.DRHMC, 1 pyhmc.PyHMC_multistep
+  int32_t dr_conv;   // 0 algorithms.DRHMC conventions, 1 pyhmc.PyHMC_multistep's (also the probabilistic classes')
+  int32_t dr_prob;   // probabilistic DR: 0 off, 1 p_try = 1 - min(1, e^{H0-Hj}), 2 p_try = 1 - alpha_j
+  T* ptries_out;     // [n_chains, nprops] or nullptr
   int32_t nprops, stage;
   int32_t L[kMaxProps];
   T eps[kMaxProps];
@@ -278,9 +281,13 @@ __device__ __forceinline__ void finish_single(const Model& model, const TransArg
         if (a.accept_prob) a.accept_prob[chain] = (accept && !t_bad(prob)) ? pm : T(0);
       }
     } else {
+      const T pf_raw = prob;
       if (dq == T(0)) prob = T(0);
       if (t_bad(prob)) prob = T(0);
       const T a0 = prob < T(1) ? prob : T(1);
+      // probabilistic DR, first stage (src/algorithms.py:702-703, :790-791): from the raw energy ratio
+      T pt0 = T(1);
+      if (a.dr_prob && !t_bad(pf_raw)) pt0 = T(1) - (a.dr_prob == 1 ? (pf_raw < T(1) ? pf_raw : T(1)) : a0);
       const double u = draw_uniform<T>(a, chain, 0);
       // algorithms.DRHMC: acc < avec[0] (src/algorithms.py:528); PyHMC_multistep's first stage: acc <= avec[0]
       // (src/pyhmc.py:580) and codes j / -1 instead of j+1 / 0
@@ -293,9 +300,14 @@ __device__ __forceinline__ void finish_single(const Model& model, const TransArg
             a.avec_out[chain * a.nprops] = a0;
             for (int i = 1; i < a.nprops; ++i) a.avec_out[chain * a.nprops + i] = T(0);
           }
+          if (a.ptries_out) {
+            a.ptries_out[chain * a.nprops] = pt0;
+            for (int i = 1; i < a.nprops; ++i) a.ptries_out[chain * a.nprops + i] = T(1);
+          }
         } else {
           a.ws.H0[chain] = H0;
           a.ws.avec[chain * kMaxProps] = a0;
+          if (a.dr_prob) a.ws.ptries[chain * kMaxProps] = pt0;
           a.ws.counts[3 * chain] = cH; a.ws.counts[3 * chain + 1] = cVg; a.ws.counts[3 * chain + 2] = cLeap;
           // plain atomicAdd (the compiler aggregates it per warp): a cooperative-groups coalesced_threads()
           // here cost the trajectory loop its register allocation in the warp-specialised kernel
@@ -387,11 +399,42 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
       // whose base state is the proposal stored in frame[l-1] with p flipped.
       int lm[kMaxProps], lj[kMaxProps];
       T lHb[kMaxProps], lpf[kMaxProps], lav[kMaxProps][kMaxProps];
+      T lpt[kMaxProps][kMaxProps];   // try probabilities per frame (probabilistic DR; all 1 otherwise)
+      const int prob_rule = a.dr_prob;
       int lvl = 0;
       lm[0] = J + 1; lj[0] = J; lHb[0] = a.ws.H0[chain];
 #pragma unroll
-      for (int i = 0; i < kMaxProps; ++i) lav[0][i] = (i < J) ? a.ws.avec[chain * kMaxProps + i] : T(0);
+      for (int i = 0; i < kMaxProps; ++i) {
+        lav[0][i] = (i < J) ? a.ws.avec[chain * kMaxProps + i] : T(0);
+        lpt[0][i] = (prob_rule && i < J) ? a.ws.ptries[chain * kMaxProps + i] : T(1);
+      }
       cH = a.ws.counts[3 * chain]; cVg = a.ws.counts[3 * chain + 1]; cLeap = a.ws.counts[3 * chain + 2];
+      if (prob_rule) {
+        // one more uniform decides whether stage J is attempted at all (src/algorithms.py:710-711): code -2 if not
+        const double u_try = draw_uniform<T>(a, chain, 2 * J - 1);
+        if (u_try > (double)lpt[0][J - 1]) {
+          if (c.lane == 0) {
+            for (int i = 0; i < a.nprops; ++i) {
+              if (a.avec_out) a.avec_out[chain * a.nprops + i] = lav[0][i];
+              if (a.ptries_out) a.ptries_out[chain * a.nprops + i] = lpt[0][i];
+            }
+            if (a.code) a.code[chain] = -2;
+            if (a.counts) { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = cLeap; }
+          }
+          if (a.q_out != a.q_in) {
+#pragma unroll
+            for (int s = 0; s < EPL; ++s) {
+              const int i = Lay::elem(c.lane, s);
+              if (i < d) a.q_out[qoff + i * a.sd] = a.q_in[qoff + i * a.sd];
+            }
+          }
+          if (a.p_out) {
+            draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);
+            store_vec<T, EPL, LPC>(p, a.p_out, qoff, a.sd, c.lane, d);
+          }
+          continue;
+        }
+      }
       const int64_t FT = a.ws.frame_threads;
       T* fr = a.ws.frames + gthread;  // frame f: q at (2f)*EPL*FT, p at (2f+1)*EPL*FT, slot stride FT
       T prob_top = T(0);
@@ -421,7 +464,11 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
         }
         dq = group_sum_masked<LPC, T>(dq, c.mask);
         T pf = t_exp<T>(lHb[lvl] - Hn);
+        // rule 1 inside a ghost frame takes p_try from the raw ratio (src/algorithms.py:668-669), at level 0
+        // from the ratio after the no-move test (:714-719)
+        if (prob_rule == 1 && lvl > 0) lpt[lvl][j] = t_bad(pf) ? T(1) : T(1) - (pf < T(1) ? pf : T(1));
         if (dq == T(0)) pf = T(0);
+        if (prob_rule == 1 && lvl == 0) lpt[0][j] = t_bad(pf) ? T(1) : T(1) - (pf < T(1) ? pf : T(1));
 
         if (j > 0) {
           // the ghost chain from the flipped proposal is needed: push a get_num frame
@@ -433,11 +480,12 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
           if (a.dr_conv) cH += 1;   // PyHMC_multistep.get_num re-evaluates H at its base (src/pyhmc.py:541)
           lm[lvl] = j; lj[lvl] = 0; lHb[lvl] = Hn;
 #pragma unroll
-          for (int i = 0; i < kMaxProps; ++i) lav[lvl][i] = T(0);
+          for (int i = 0; i < kMaxProps; ++i) { lav[lvl][i] = T(0); lpt[lvl][i] = T(1); }
           continue;
         }
         // j == 0 can only happen inside a ghost frame here (J >= 1)
         T prob = pf;
+        T pf_cur = pf;     // the energy ratio (after the no-move test) of the stage whose alpha is being set
         bool done = false;
         for (;;) {
           T ret;
@@ -446,17 +494,33 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
             ret = T(0);
             returning = true;
           } else {
-            lav[lvl][lj[lvl]] = prob < T(1) ? prob : T(1);
+            const T al = prob < T(1) ? prob : T(1);
+            lav[lvl][lj[lvl]] = al;
+            if (prob_rule == 2) lpt[lvl][lj[lvl]] = t_bad(pf_cur) ? T(1) : T(1) - al;   // src/algorithms.py:764-765
             T pr = T(1);
             for (int i = 0; i < lm[lvl]; ++i) pr *= (T(1) - lav[lvl][i]);
-            if (pr == T(0) || lj[lvl] + 1 == lm[lvl]) { ret = pr; returning = true; }
+            if (pr == T(0)) { ret = pr; returning = true; }
+            else if (lj[lvl] + 1 == lm[lvl]) {
+              if (prob_rule) {
+                T pt = T(1);
+                for (int i = 0; i < lm[lvl]; ++i) pt *= lpt[lvl][i];
+                pr *= pt;                                                              // prod(1-avec) * prod(ptries)
+              }
+              ret = pr; returning = true;
+            }
             else { lj[lvl] += 1; returning = false; }
           }
           if (!returning) break;
           --lvl;
           T den = T(1);
           for (int i = 0; i < lj[lvl]; ++i) den *= (T(1) - lav[lvl][i]);
+          if (prob_rule) {
+            T pt = T(1);
+            for (int i = 0; i < lj[lvl]; ++i) pt *= lpt[lvl][i];
+            den *= pt;
+          }
           prob = lpf[lvl] * ret / den;
+          pf_cur = lpf[lvl];
           if (lvl == 0) { prob_top = prob; done = true; break; }
         }
         if (done) break;
@@ -465,7 +529,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
       // ---------------- DRHMC.step's accept test for stage J (src/algorithms.py:523-529)
       if (t_bad(prob_top)) prob_top = T(0);
       const T aJ = prob_top < T(1) ? prob_top : T(1);
-      const double u = draw_uniform<T>(a, chain, J);
+      if (prob_rule == 2) lpt[0][J] = t_bad(lpf[0]) ? T(1) : T(1) - aJ;                 // src/algorithms.py:808-809
+      const double u = draw_uniform<T>(a, chain, prob_rule ? 2 * J : J);
       const bool accept = u < (double)aJ;
       const bool finished = accept || (J == a.nprops - 1);
       if (c.lane == 0) {
@@ -474,16 +539,17 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
             for (int i = 0; i < a.nprops; ++i)
               a.avec_out[chain * a.nprops + i] = (i < J) ? lav[0][i] : (i == J ? aJ : T(0));
           }
+          if (a.ptries_out) {
+            for (int i = 0; i < a.nprops; ++i) a.ptries_out[chain * a.nprops + i] = lpt[0][i];
+          }
           if (a.code) a.code[chain] = a.dr_conv ? (accept ? J : -1) : (accept ? J + 1 : 0);
           if (a.counts) { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = cLeap; }
         } else {
           a.ws.avec[chain * kMaxProps + J] = aJ;
+          if (prob_rule) a.ws.ptries[chain * kMaxProps + J] = lpt[0][J];
           a.ws.counts[3 * chain] = cH; a.ws.counts[3 * chain + 1] = cVg; a.ws.counts[3 * chain + 2] = cLeap;
-          cg::coalesced_group g = cg::coalesced_threads();
-          int base = 0;
-          if (g.thread_rank() == 0) base = atomicAdd(a.ws.count + J + 1, (int)g.size());
-          base = g.shfl(base, 0);
-          a.ws.list[(int64_t)(J + 1) * a.n_chains + base + g.thread_rank()] = (int32_t)chain;
+          const int slot = atomicAdd(a.ws.count + J + 1, 1);   // aggregated per warp by the compiler
+          a.ws.list[(int64_t)(J + 1) * a.n_chains + slot] = (int32_t)chain;
         }
       }
       if (finished) {

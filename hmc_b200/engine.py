@@ -208,11 +208,14 @@ class Engine:
                    "avec": torch.empty((C_, nprops), dtype=self.dtype, device=self.device) if want_avec else None,
                    "counts": torch.empty((C_, 3), dtype=torch.int32, device=self.device)
                    if counts_out is None else counts_out}
+            prob = convention in (_lib.DR_PROB_METROP, _lib.DR_PROB_HASTINGS)
+            if prob:   # the probabilistic classes also return their try probabilities
+                out["ptries"] = torch.empty((C_, nprops), dtype=self.dtype, device=self.device)
             so = _lib.StepOut()
             so.p_out, so.code, so.avec = _lib.ptr(out["p"]), _lib.ptr(out["code"]), _lib.ptr(out["avec"])
-            so.counts = _lib.ptr(out["counts"])
+            so.counts, so.ptries = _lib.ptr(out["counts"]), _lib.ptr(out.get("ptries"))
             ch = self._chains(q, q_out, extra_offset)
-            r, keep = self._rng(p, u, nprops, C_, p_prev, alpha)
+            r, keep = self._rng(p, u, 2 * nprops - 1 if prob else nprops, C_, p_prev, alpha)
             _lib.check(self.lib.hmcb_drhmc_step(C.byref(m), C.byref(ch), C.byref(r), int(n_leap), float(step_size),
                                                 int(nprops), float(stepfactor), int(convention), C.byref(so),
                                                 C.c_void_p(ws.data_ptr()), ws.numel(),

@@ -154,3 +154,39 @@ class PyHMC_multistep(HMC):
             return b.out(out["q"]), b.out(out["p"]), int(out["code"][0]), b.out(out["avec"]), cnt
         self.Hcount, self.Vgcount, self.leapcount = out["counts"][:, 0], out["counts"][:, 1], out["counts"][:, 2]
         return b.out(out["q"]), b.out(out["p"]), b.out(out["code"]), b.out(out["avec"]), b.out(out["counts"])
+
+
+class _ProbMultistep(HMC):
+    """Probabilistic delayed rejection: after a rejection the next, finer stage is only
+    attempted with probability ptries[j-1] (one more uniform per stage; code -2 when the
+    stage is declined), and the ghost products carry prod(ptries).  multi_step returns the
+    reference's six values (q, p, code, avec[m], [Hcount, Vgcount, leapcount], ptries[m])."""
+    _convention = None
+
+    def multi_step(self, m, q0, N, ss, fsub, p=None, u=None):
+        """u, if given, holds 2m-1 uniforms per chain in the order the reference consumes them:
+        u_acc0, u_try1, u_acc1, u_try2, ..."""
+        e = self.engine
+        b = Batch(q0, e.dev, e.dtype)
+        e.check_dim(b)
+        out = e.drhmc_step(b.q, N, ss, m, fsub, p=p, u=u, convention=self._convention)
+        if b.unbatched:
+            cnt = out["counts"][0].tolist()
+            self.Hcount, self.Vgcount, self.leapcount = cnt
+            return (b.out(out["q"]), b.out(out["p"]), int(out["code"][0]), b.out(out["avec"]), cnt,
+                    b.out(out["ptries"]))
+        self.Hcount, self.Vgcount, self.leapcount = out["counts"][:, 0], out["counts"][:, 1], out["counts"][:, 2]
+        return (b.out(out["q"]), b.out(out["p"]), b.out(out["code"]), b.out(out["avec"]), b.out(out["counts"]),
+                b.out(out["ptries"]))
+
+
+class PyHMC_multistep_tries(_ProbMultistep):
+    """pyhmc.PyHMC_multistep_tries (src/pyhmc.py:233-349): p_try_j = 1 - min(1, e^{H0-Hj}),
+    i.e. without the balancing Hastings factor of the delayed attempts."""
+    _convention = _lib.DR_PROB_METROP
+
+
+class PyHMC_multistep_tries3(_ProbMultistep):
+    """pyhmc.PyHMC_multistep_tries3 (src/pyhmc.py:362-483): p_try_j = 1 - alpha_j, the acceptance
+    probability of the stage that just failed."""
+    _convention = _lib.DR_PROB_HASTINGS

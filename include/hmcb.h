@@ -87,6 +87,8 @@ typedef struct hmcb_step_out {
   int32_t* counts;            /* [C,3] Hcount, Vgcount, leapcount (src/pyhmc.py:69) */
   void* accept_prob;          /* [C] min(1, exp(H0-H1)) with NaN->0, 0 if q did not move
                                  (what src/algorithms.py:218-224 feeds dual averaging) */
+  void* ptries;               /* [C,nprops] try probabilities, probabilistic DR conventions only
+                                 (6th return value of multi_step, src/algorithms.py:706) */
 } hmcb_step_out;
 
 /* Accept-rule conventions:
@@ -127,8 +129,17 @@ int hmcb_logp_grad(const hmcb_model* model, const hmcb_chains* chains, void* log
  *  HMCB_DR_ALGORITHMS  algorithms.DRHMC.step: accept iff u < alpha_j, code j+1 / 0 (src/algorithms.py:500-530)
  *  HMCB_DR_MULTISTEP   pyhmc.PyHMC_multistep.multi_step (src/pyhmc.py:564-598): first stage accepts iff
  *                      u <= alpha_0, code j / -1, and get_num re-evaluates H at its base (:541) so
- *                      Hcount is larger by one per ghost frame */
-enum { HMCB_DR_ALGORITHMS = 0, HMCB_DR_MULTISTEP = 1 };
+ *                      Hcount is larger by one per ghost frame
+ *  HMCB_DR_PROB_METROP   probabilistic DR, algorithms.Prob_DRHMC_Metrop.multi_step (src/algorithms.py:687-728;
+ *                      same body: pyhmc.PyHMC_multistep_tries, src/pyhmc.py:308-349): MULTISTEP's conventions, and
+ *                      stage j >= 1 is attempted only if a further uniform u_try <= ptries[j-1], with
+ *                      ptries[j] = 1 - min(1, e^{H0-Hj}); code -2 when a stage is declined; the ghost products
+ *                      carry prod(ptries) (get_num, :659-684)
+ *  HMCB_DR_PROB_HASTINGS the same with ptries[j] = 1 - alpha_j (algorithms.Prob_DRHMC_Hastings, :744-818;
+ *                      pyhmc.PyHMC_multistep_tries3)
+ * Injected uniforms are read in the order the reference consumes them: [C, nprops] = u_acc per stage for the first
+ * two conventions, [C, 2*nprops-1] = u_acc0, u_try1, u_acc1, u_try2, ... for the probabilistic ones. */
+enum { HMCB_DR_ALGORITHMS = 0, HMCB_DR_MULTISTEP = 1, HMCB_DR_PROB_METROP = 2, HMCB_DR_PROB_HASTINGS = 3 };
 /* Optional per-stage timing: cudaEvent_t handles (as void*) recorded on `stream`
  * before stage 0, between stages and after the last one (nprops+1 events).  The
  * reference's only timing is time.time() around its sample loop

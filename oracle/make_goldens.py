@@ -150,6 +150,41 @@ def run_adhmc(case):
     return code
 
 
+PROBDR_CASES = [
+    dict(name="probdr_metrop_funnel10", cls="algorithms.Prob_DRHMC_Metrop", model=dict(kind="funnel", d=10), C=16, T=5,
+         seed=401, args=dict(m=3, N=6, ss=0.6, fsub=2.0)),
+    dict(name="probdr_hastings_funnel10", cls="algorithms.Prob_DRHMC_Hastings", model=dict(kind="funnel", d=10), C=16,
+         T=5, seed=402, args=dict(m=3, N=6, ss=0.6, fsub=2.0)),
+    dict(name="probdr_tries_funnel50", cls="pyhmc.PyHMC_multistep_tries", model=dict(kind="funnel", d=50), C=12, T=4,
+         seed=403, args=dict(m=4, N=10, ss=0.4, fsub=1.5)),
+    dict(name="probdr_tries3_rosen8", cls="pyhmc.PyHMC_multistep_tries3", model=dict(kind="rosenbrock", d=8), C=12, T=4,
+         seed=404, args=dict(m=3, N=8, ss=0.12, fsub=2.0)),
+]
+
+
+def run_probdr(case):
+    """multi_step of the probabilistic delayed-rejection classes, 2m-1 replayed uniforms per transition."""
+    modname, clsname = case["cls"].split(".")
+    model = build_model(case["model"])
+    d, C, T, a = model.d, case["C"], case["T"], case["args"]
+    m = a["m"]
+    P, U = replay.make_draws(case["seed"], T, C, d, 2 * m - 1)
+    q0 = _q0(case, model)
+    ref = getattr(ref_loader.load(modname), clsname)(model.log_prob, model.grad_log_prob)
+    q = np.zeros((T, C, d)); p = np.zeros((T, C, d)); code = np.zeros((T, C)); avec = np.zeros((T, C, m))
+    ptries = np.zeros((T, C, m)); counts = np.zeros((T, C, 3))
+    with np.errstate(all="ignore"), contextlib.redirect_stdout(io.StringIO()):
+        for c in range(C):
+            qc = q0[c]
+            for t in range(T):
+                with replay.patched_numpy_random(replay.Draws([P[t, c]], U[t, c])):
+                    qc, pc, acc, av, cnt, pt = ref.multi_step(m, qc, a["N"], a["ss"], a["fsub"])
+                q[t, c], p[t, c], code[t, c], avec[t, c], counts[t, c], ptries[t, c] = qc, pc, acc, av, cnt, pt
+    np.savez_compressed(os.path.join(OUT, case["name"] + ".npz"), spec=json.dumps(case), q0=q0, P=P, U=U, q=q, p=p,
+                        code=code, avec=avec, counts=counts, ptries=ptries)
+    return code
+
+
 def run_logistic():
     """pyhmc.HMC.step on the Bayesian logistic-regression model (float64 reference arithmetic on
     float32-representable data); the GPU path runs in float32 and is held to 1e-5."""
@@ -188,7 +223,7 @@ def main():
         print("%-24s codes %s" % (case["name"], dict(zip(vals.tolist(), n.tolist()))))
     vals, n = np.unique(run_logistic(), return_counts=True)
     print("%-24s codes %s" % ("logit_hmc", dict(zip(vals.tolist(), n.tolist()))))
-    for cases, fn in ((MALA_CASES, run_mala), (ADHMC_CASES, run_adhmc)):
+    for cases, fn in ((MALA_CASES, run_mala), (ADHMC_CASES, run_adhmc), (PROBDR_CASES, run_probdr)):
         for case in cases:
             vals, n = np.unique(fn(case), return_counts=True)
             print("%-24s codes %s" % (case["name"], dict(zip(vals.tolist(), n.tolist()))))

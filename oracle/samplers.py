@@ -428,6 +428,91 @@ def multistep_step(model, m, q0, N, ss, fsub, rng, invmetric_diag=None):
     return q0, p0, -1, avec, cnt.as_list()
 
 
+# ----------------------------------------------------------------------------- probabilistic delayed rejection
+# Two rules for the probability of attempting the next stage after a rejection:
+#   "metrop"   p_try_j = 1 - min(1, e^{H0-Hj})   (algorithms.Prob_DRHMC_Metrop, pyhmc.PyHMC_multistep_tries)
+#   "hastings" p_try_j = 1 - alpha_j             (algorithms.Prob_DRHMC_Hastings, pyhmc.PyHMC_multistep_tries3)
+# They differ from each other only in where ptries[j] is set, which the two functions keep.
+
+def _prob_ghost(model, kin, rule, m, q, p, N, ss, fsub, cnt):
+    """get_num of the probabilistic classes, src/algorithms.py:659-684 (metrop) and :744-771
+    (hastings); src/pyhmc.py:280-305 and :409-436 are the same bodies."""
+    avec = np.zeros(m)
+    ptries = np.ones(m)
+    H0 = _H(model, kin, q, p, cnt)
+    for j in range(m):
+        fac = fsub ** j
+        qj, pj = leapfrog(model, kin, q, p, int(N * fac), ss / fac, cnt)
+        Hj = _H(model, kin, qj, pj, cnt)
+        pfac = np.exp(H0 - Hj)
+        if rule == "metrop":
+            ptries[j] = 1 if _bad(pfac) else 1 - min(1.0, pfac)      # before the no-move test
+        if (q - qj).sum() == 0:
+            pfac = 0.0
+        if j:
+            den = np.prod(1 - avec[:j]) * np.prod(ptries[:j])
+            num = _prob_ghost(model, kin, rule, j, qj, -pj, N, ss, fsub, cnt)
+            prob = pfac * num / den
+        else:
+            prob = pfac
+        if _bad(prob):
+            return 0.0
+        avec[j] = min(1.0, prob)
+        if rule == "hastings":
+            ptries[j] = 1 if _bad(pfac) else 1 - avec[j]
+        if not np.prod(1 - avec):
+            return np.prod(1 - avec)
+    return np.prod(1 - avec) * np.prod(ptries)
+
+
+def prob_multistep_step(model, rule, m, q0, N, ss, fsub, rng, invmetric_diag=None):
+    """multi_step of the probabilistic classes, src/algorithms.py:687-728 (metrop) and :774-818
+    (hastings): before stage j >= 1 one more uniform decides whether the stage is attempted at
+    all (code -2 when it is not); codes otherwise as PyHMC_multistep.  Returns the reference's
+    six values (q, p, code, avec, counts, ptries)."""
+    kin, cnt = Kinetics(invmetric_diag), Counters()
+    with np.errstate(all="ignore"):
+        p0 = rng.normal(size=q0.size).reshape(q0.shape) * kin.metricstd
+        avec = np.zeros(m)
+        ptries = np.ones(m)
+        H0 = _H(model, kin, q0, p0, cnt)
+        q1, p1 = leapfrog(model, kin, q0, p0, N, ss, cnt)
+        H1 = _H(model, kin, q1, p1, cnt)
+        pfac = np.exp(H0 - H1)
+        prob = pfac
+        if _bad(prob) or (q0 - q1).sum() == 0:
+            prob = 0.0
+        avec[0] = min(1.0, prob)
+        if _bad(pfac):
+            ptries[0] = 1
+        else:
+            ptries[0] = 1 - min(1.0, pfac) if rule == "metrop" else 1 - avec[0]
+        if rng.uniform() <= avec[0]:
+            return q1, p1, 0, avec, cnt.as_list(), ptries
+        for j in range(1, m):
+            if rng.uniform() > ptries[j - 1]:
+                return q0, p0, -2, avec, cnt.as_list(), ptries
+            fac = fsub ** j
+            qj, pj = leapfrog(model, kin, q0, p0, int(N * fac), ss / fac, cnt)
+            Hj = _H(model, kin, qj, pj, cnt)
+            pfac = np.exp(H0 - Hj)
+            if (q0 - qj).sum() == 0:
+                pfac = 0.0
+            den = np.prod(1 - avec[:j]) * np.prod(ptries[:j])
+            num = _prob_ghost(model, kin, rule, j, qj, -pj, N, ss, fsub, cnt)
+            if rule == "metrop":
+                ptries[j] = 1 if _bad(pfac) else 1 - min(1.0, pfac)  # here after the no-move test
+            prob = pfac * num / den
+            if _bad(prob):
+                prob = 0.0
+            avec[j] = min(1.0, prob)
+            if rule == "hastings":
+                ptries[j] = 1 if _bad(pfac) else 1 - avec[j]
+            if rng.uniform() < avec[j]:
+                return qj, pj, j, avec, cnt.as_list(), ptries
+    return q0, p0, -1, avec, cnt.as_list(), ptries
+
+
 # ----------------------------------------------------------------------------- generalised HMC family
 # These classes are built as Cls(log_prob, grad_log_prob, log_prob_and_grad): V_g then uses
 # grad_log_prob (src/algorithms.py:100-106) and the last gradient of a trajectory comes from

@@ -187,6 +187,32 @@ def test_pyhmc_multistep_bit_exact(mi, m, fsub):
         assert len(set(codes)) >= 2
 
 
+@pytest.mark.parametrize("mi", [0, 1, 3])
+@pytest.mark.parametrize("m,fsub", [(1, 2), (2, 2), (3, 2), (4, 1.5)])
+@pytest.mark.parametrize("cls,rule", [("algorithms.Prob_DRHMC_Metrop", "metrop"), ("algorithms.Prob_DRHMC_Hastings", "hastings"),
+                                      ("pyhmc.PyHMC_multistep_tries", "metrop"), ("pyhmc.PyHMC_multistep_tries3", "hastings")])
+def test_probabilistic_dr_bit_exact(mi, m, fsub, cls, rule):
+    mod, name = cls.split(".")
+    model = _models()[mi]
+    ref = getattr(ref_loader.load(mod), name)(model.log_prob, model.grad_log_prob)
+    T = 30
+    P, U = replay.make_draws(171 + mi, T, 1, model.d, 2 * m - 1)
+    q_r = q_o = _q0(model, mi)
+    eps, N = (0.45, 6) if model.name == "funnel" else (0.1, 6)
+    codes = []
+    for t in range(T):
+        with replay.patched_numpy_random(replay.Draws([P[t, 0]], U[t, 0])):
+            out_r = ref.multi_step(m, q_r, N, eps, fsub)
+        out_o = samplers.prob_multistep_step(model, rule, m, q_o, N, eps, fsub, replay.Draws([P[t, 0]], U[t, 0]))
+        assert len(out_r) == len(out_o) == 6
+        for a, b in zip(out_r, out_o):
+            assert _same(a, b)
+        q_r, q_o = out_r[0], out_o[0]
+        codes.append(out_r[2])
+    if m >= 3 and model.name == "funnel":
+        assert -2 in codes and len(set(codes)) >= 3          # declined-to-try really happens
+
+
 @pytest.mark.parametrize("mi", [0, 1, 2, 3])
 @pytest.mark.parametrize("alpha", [0.0, 0.7])
 def test_ghmc_and_pghmc_bit_exact(mi, alpha):
