@@ -51,6 +51,17 @@ class MalaIO(C.Structure):
                 ("code", C.c_void_p), ("n_accept", C.c_void_p), ("counts", C.c_void_p)]
 
 
+class WalkPar(C.Structure):
+    _fields_ = [("n_segments", C.c_int32), ("n_leap_segment", C.c_int32), ("tint", C.c_double), ("n_ratios", C.c_int32),
+                ("ntry", C.c_int32), ("nsteps", C.c_int32), ("ratios", C.c_double * 4), ("pwts0", C.c_double * 4),
+                ("smin", C.c_double), ("smax", C.c_double), ("steps", C.POINTER(C.c_double))]
+
+
+class WalkOut(C.Structure):
+    _fields_ = [("p_out", C.c_void_p), ("code", C.c_void_p), ("probs", C.c_void_p), ("checks", C.c_void_p),
+                ("counts", C.c_void_p)]
+
+
 class AdhmcOut(C.Structure):
     _fields_ = [("p_out", C.c_void_p), ("code", C.c_void_p), ("probs", C.c_void_p), ("aux", C.c_void_p),
                 ("counts", C.c_void_p)]
@@ -80,9 +91,12 @@ SIGNATURES = {
     "hmcb_ghmc_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
                                  C.POINTER(GhmcIO), C.c_void_p]),
     "hmcb_adhmc_eps0_workspace_bytes": (C.c_size_t, [C.POINTER(Model), C.c_int64]),
-    "hmcb_adhmc_eps0_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32,
+    "hmcb_adhmc_eps0_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
                                        C.POINTER(C.c_double), C.c_int32, C.c_int32, C.POINTER(AdhmcOut), C.c_void_p,
                                        C.c_size_t, C.c_void_p]),
+    "hmcb_adhmc_walk_workspace_bytes": (C.c_size_t, [C.POINTER(Model), C.c_int64, C.c_int32]),
+    "hmcb_adhmc_walk_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.POINTER(WalkPar),
+                                       C.POINTER(WalkOut), C.c_void_p, C.c_size_t, C.c_void_p]),
     "hmcb_logreg_prepared_bytes": (C.c_size_t, [C.POINTER(Model)]),
     "hmcb_logreg_prepare": (C.c_int, [C.POINTER(Model), C.c_void_p, C.c_size_t, C.c_void_p]),
     "hmcb_logreg_workspace_bytes": (C.c_size_t, [C.POINTER(Model), C.c_int64]),

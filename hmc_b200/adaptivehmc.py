@@ -1,14 +1,17 @@
-"""Batched drop-in for the hot-path part of the reference's ``src/adaptivehmc.py``:
-``HMC`` (:5-99, the third copy of vanilla HMC, entry point ``hmc_step``) and
-``AdHMC_eps0`` (:105-192), HMC whose step size is drawn per transition from a
-distribution built by trial trajectories, with the matching Hastings correction.
+"""Batched drop-in for the reference's ``src/adaptivehmc.py``:
 
-``AdHMC_eps0.hmc_step(q0, Nleap, smin, smax, Tint, ntry, nsteps)`` returns the
-reference's 6-tuple ``(q, p, accepted, [prob, prob/hastings, hastings],
-stack([pf_den, pb_num, eps]), [Hcount, Vgcount, leapcount])``; batched inputs give
-``probs[C,3]``, ``aux[C,3]``, ``counts[C,3]``.  Only ``Tint == 0`` (fixed number of
-leapfrog steps) runs on the GPU: with ``Tint != 0`` the reference makes the number
-of steps a function of the drawn step size, which is a later row.
+``HMC`` (:5-99)           the third copy of vanilla HMC, entry point ``hmc_step``
+``AdHMC_eps0`` (:105-192) step size drawn per transition from a distribution built by trial
+                          trajectories, with the matching Hastings correction; ``Nleap`` steps, or
+                          with ``Tint`` given int(Tint/eps)+1 steps of the drawn step size
+``AdHMC`` (:196-354)      the step size walks inside the trajectory: after every ``nleap`` steps it
+                          is multiplied by one of ``ratios``, chosen by the energy error of the
+                          candidate segments, with the reverse-walk Hastings factor
+``AdHMC_tint`` (:362-519) the same with segments of fixed integration time Tint/ntimes
+
+``hmc_step`` returns the reference's 6-tuple ``(q, p, accepted, [prob, prob/hastings, hastings],
+checks, [Hcount, Vgcount, leapcount])`` with ``checks = stack([pf_den, pb_num, eps])``; batched
+inputs give ``probs[C,3]``, ``checks[C,3]`` (eps0) or ``[C,3,N]`` (walks), ``counts[C,3]``.
 """
 import numpy as np
 import torch
@@ -40,13 +43,10 @@ class AdHMC_eps0(HMC):
             raise ValueError("Tint and Nleap cannot be both zeros")
         if (Tint != 0) and (Nleap != 0):
             raise ValueError("Tint and Nleap both given and are inconsistent")
-        if Tint != 0:
-            raise NotImplementedError("AdHMC_eps0 with Tint != 0 (step count depends on the drawn step size) "
-                                      "is not on the GPU path yet")
         e = self.engine
         b = Batch(q0, e.dev, e.dtype)
         e.check_dim(b)
-        out = e.adhmc_eps0_step(b.q, Nleap, self.get_steps(smin, smax, ntry), nsteps, p=p, u=u)
+        out = e.adhmc_eps0_step(b.q, Nleap, self.get_steps(smin, smax, ntry), nsteps, p=p, u=u, tint=float(Tint))
         code = out["code"].to(torch.float64)
         if b.unbatched:
             cnt = out["counts"][0].tolist()
@@ -55,3 +55,43 @@ class AdHMC_eps0(HMC):
         self.Hcount, self.Vgcount, self.leapcount = out["counts"][:, 0], out["counts"][:, 1], out["counts"][:, 2]
         return (b.out(out["q"]), b.out(out["p"]), b.out(code), b.out(out["probs"]), b.out(out["aux"]),
                 b.out(out["counts"]))
+
+
+class AdHMC(AdHMC_eps0):
+    """adaptivehmc.AdHMC (src/adaptivehmc.py:196-354).  ``u``, if given, holds N+2 uniforms per chain
+    (N = Nleap // nleap) in the order the reference consumes them: bin draw, within-bin draw, one per
+    step-size choice (np.random.choice), accept test."""
+
+    _tint = False
+
+    def _walk(self, q0, N, nleap, tint, ratios, pwts0, smin, smax, ntry_eps0, nsteps_eps0, logeps, p, u):
+        if N < 2:
+            raise ValueError("need at least two segments (the reference leaves its step-size walk undefined for one)")
+        e = self.engine
+        b = Batch(q0, e.dev, e.dtype)
+        e.check_dim(b)
+        out = e.adhmc_walk_step(b.q, N, nleap, tint, list(ratios), list(pwts0), smin, smax,
+                                self.get_steps(smin, smax, ntry_eps0, logeps), nsteps_eps0, p=p, u=u)
+        code = out["code"].to(torch.float64)
+        if b.unbatched:
+            cnt = out["counts"][0].tolist()
+            self.Hcount, self.Vgcount, self.leapcount = cnt
+            return (b.out(out["q"]), b.out(out["p"]), float(code[0]), out["probs"][0].tolist(), b.out(out["checks"]), cnt)
+        self.Hcount, self.Vgcount, self.leapcount = out["counts"][:, 0], out["counts"][:, 1], out["counts"][:, 2]
+        return (b.out(out["q"]), b.out(out["p"]), b.out(code), b.out(out["probs"]), b.out(out["checks"]),
+                b.out(out["counts"]))
+
+    def hmc_step(self, q0, Nleap=100, nleap=10, ratios=(1 / np.sqrt(2), np.sqrt(2)), pwts0=(1.0, 1.0), smin=0.01,
+                 smax=1.0, ntry_eps0=10, nsteps_eps0=1, logeps=True, getstepfunc=None, verbose=False, p=None, u=None):
+        return self._walk(q0, int(Nleap // nleap), nleap, 0.0, ratios, pwts0, smin, smax, ntry_eps0, nsteps_eps0, logeps,
+                          p, u)
+
+
+class AdHMC_tint(AdHMC):
+    """adaptivehmc.AdHMC_tint (src/adaptivehmc.py:362-519): ``ntimes`` segments, each of integration
+    time Tint/ntimes, i.e. max(1, int(tint/eps)) steps at the segment's step size."""
+
+    def hmc_step(self, q0, Tint=10, ntimes=10, ratios=(1 / np.sqrt(2), np.sqrt(2)), pwts0=(1.0, 1.0), smin=0.01,
+                 smax=1.0, ntry_eps0=10, nsteps_eps0=1, logeps=True, verbose=False, p=None, u=None):
+        return self._walk(q0, int(ntimes), 0, Tint / ntimes, ratios, pwts0, smin, smax, ntry_eps0, nsteps_eps0, logeps,
+                          p, u)

@@ -273,9 +273,10 @@ static int ghmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c
   return e->fn(*m, OP_GHMC, &g, st);
 }
 
-static int ad_frame_threads(const Entry* e, const hmcb_model* m, int64_t n_chains, int64_t& ft, int& epl) {
+static int ad_frame_threads(const Entry* e, const hmcb_model* m, int64_t n_chains, int64_t& ft, int& epl,
+                            int query_op = OP_QUERY_AD) {
   LaunchInfo li;
-  int rc = e->fn(*m, OP_QUERY_AD, &li, nullptr);
+  int rc = e->fn(*m, query_op, &li, nullptr);
   if (rc) return rc;
   const int64_t gpb = li.threads / li.lpc;
   int64_t blocks = (n_chains + gpb - 1) / gpb;
@@ -288,7 +289,7 @@ static int ad_frame_threads(const Entry* e, const hmcb_model* m, int64_t n_chain
 
 template <typename T>
 static int adhmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r, int n_leap,
-                        const double* steps, int ntry, int nsteps, const hmcb_adhmc_out* o, void* ws, int64_t ft,
+                        double tint, const double* steps, int ntry, int nsteps, const hmcb_adhmc_out* o, void* ws, int64_t ft,
                         cudaStream_t st) {
   AdArgs<T> a;
   memset(&a, 0, sizeof(a));
@@ -297,12 +298,36 @@ static int adhmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* 
   a.seed = r->seed; a.iteration = (uint32_t)r->iteration; a.rng_flags = r->flags;
   a.p_inject = (const T*)r->p_inject; a.u_inject = r->u_inject; a.u_stride = r->u_stride;
   a.minv = (const T*)m->invmetric_diag;
-  a.n_leap = n_leap; a.ntry = ntry; a.nsteps = nsteps;
+  a.n_leap = n_leap; a.tint = tint; a.ntry = ntry; a.nsteps = nsteps;
   for (int i = 0; i < ntry; ++i) { a.steps[i] = steps[i]; a.pwts[i] = pow(steps[i], 0.5); }
   if (o) { a.p_out = (T*)o->p_out; a.code = o->code; a.probs = (T*)o->probs; a.aux = (T*)o->aux; a.counts = o->counts; }
   a.frames = (T*)ws;
   a.frame_threads = ft;
   return e->fn(*m, OP_ADHMC, &a, st);
+}
+
+template <typename T>
+static int adwalk_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r,
+                         const hmcb_adhmc_walk_par* par, const hmcb_adhmc_walk_out* o, void* ws, int64_t ft,
+                         cudaStream_t st) {
+  WalkArgs<T> a;
+  memset(&a, 0, sizeof(a));
+  a.n_chains = c->n_chains; a.chain_offset = c->chain_offset; a.d = m->d;
+  a.q_in = (const T*)c->q_in; a.q_out = (T*)c->q_out; a.sc = c->stride_chain; a.sd = c->stride_dim;
+  a.seed = r->seed; a.iteration = (uint32_t)r->iteration; a.rng_flags = r->flags;
+  a.p_inject = (const T*)r->p_inject; a.u_inject = r->u_inject; a.u_stride = r->u_stride;
+  a.minv = (const T*)m->invmetric_diag;
+  a.nseg = par->n_segments; a.nleap = par->n_leap_segment;
+  a.tint_mode = par->tint > 0 ? 1 : 0; a.tint = par->tint;
+  a.nr = par->n_ratios;
+  for (int j = 0; j < par->n_ratios; ++j) { a.ratios[j] = par->ratios[j]; a.pwts0[j] = par->pwts0[j]; }
+  a.smin = par->smin; a.smax = par->smax;
+  a.ntry = par->ntry; a.nsteps = par->nsteps;
+  for (int i = 0; i < par->ntry; ++i) { a.steps[i] = par->steps[i]; a.pwts[i] = pow(par->steps[i], 0.5); }
+  if (o) { a.p_out = (T*)o->p_out; a.code = o->code; a.probs = (T*)o->probs; a.checks = (T*)o->checks; a.counts = o->counts; }
+  a.frames = (T*)ws;
+  a.frame_threads = ft;
+  return e->fn(*m, OP_ADWALK, &a, st);
 }
 
 // ------------------------------------------------------------------ built-in scratch (hmcb_drhmc_step_static)
@@ -537,14 +562,15 @@ size_t hmcb_adhmc_eps0_workspace_bytes(const hmcb_model* model, int64_t n_chains
 }
 
 int hmcb_adhmc_eps0_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
-                         const double* steps, int32_t ntry, int32_t nsteps, const hmcb_adhmc_out* out,
+                         double tint, const double* steps, int32_t ntry, int32_t nsteps, const hmcb_adhmc_out* out,
                          void* workspace, size_t workspace_bytes, void* stream) {
   int rc;
   if ((rc = check_model(model))) return rc;
   if ((rc = check_chains(chains))) return rc;
   HMCB_CHECK_ARG(rng != nullptr && steps != nullptr, "rng/steps is NULL");
   HMCB_CHECK_ARG(ntry >= 2 && ntry <= kMaxTry, "ntry=%d must be in 2..%d", ntry, kMaxTry);
-  HMCB_CHECK_ARG(n_leap >= 1 && nsteps >= 1, "n_leap and nsteps must be >= 1");
+  HMCB_CHECK_ARG((n_leap >= 1) != (tint > 0), "give either n_leap >= 1 or tint > 0 (src/adaptivehmc.py:164-171), got n_leap=%d tint=%g", n_leap, tint);
+  HMCB_CHECK_ARG(nsteps >= 1 && tint >= 0, "nsteps must be >= 1 and tint >= 0");
   HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= 3, "u_inject needs u_stride >= 3");
   if (chains->n_chains == 0) return 0;
   const Entry* e = choose_entry(*model);
@@ -559,8 +585,57 @@ int hmcb_adhmc_eps0_step(const hmcb_model* model, const hmcb_chains* chains, con
   }
   cudaStream_t st = (cudaStream_t)stream;
   if (model->dtype == HMCB_F64)
-    return adhmc_step_t<double>(e, model, chains, rng, n_leap, steps, ntry, nsteps, out, workspace, ft, st);
-  return adhmc_step_t<float>(e, model, chains, rng, n_leap, steps, ntry, nsteps, out, workspace, ft, st);
+    return adhmc_step_t<double>(e, model, chains, rng, n_leap, tint, steps, ntry, nsteps, out, workspace, ft, st);
+  return adhmc_step_t<float>(e, model, chains, rng, n_leap, tint, steps, ntry, nsteps, out, workspace, ft, st);
+}
+
+size_t hmcb_adhmc_walk_workspace_bytes(const hmcb_model* model, int64_t n_chains, int32_t n_ratios) {
+  if (check_model(model) || n_chains < 0 || n_ratios < 1 || n_ratios > kMaxRatios) return 0;
+  const Entry* e = choose_entry(*model);
+  if (!e) return 0;
+  int64_t ft;
+  int epl;
+  if (ad_frame_threads(e, model, n_chains, ft, epl, OP_QUERY_WALK)) return 0;
+  return (size_t)(3 + 2 * n_ratios) * epl * ft * (model->dtype == HMCB_F64 ? 8 : 4);
+}
+
+int hmcb_adhmc_walk_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng,
+                         const hmcb_adhmc_walk_par* par, const hmcb_adhmc_walk_out* out, void* workspace,
+                         size_t workspace_bytes, void* stream) {
+  int rc;
+  if ((rc = check_model(model))) return rc;
+  if ((rc = check_chains(chains))) return rc;
+  HMCB_CHECK_ARG(rng != nullptr && par != nullptr && par->steps != nullptr, "rng/par/steps is NULL");
+  HMCB_CHECK_ARG(par->n_segments >= 2, "n_segments=%d must be >= 2 (the reference needs at least one step-size choice)",
+                 par->n_segments);
+  HMCB_CHECK_ARG(par->tint > 0 || par->n_leap_segment >= 1, "n_leap_segment must be >= 1 when tint == 0");
+  HMCB_CHECK_ARG(par->n_ratios >= 1 && par->n_ratios <= kMaxRatios, "n_ratios=%d must be in 1..%d", par->n_ratios, kMaxRatios);
+  HMCB_CHECK_ARG(par->ntry >= 2 && par->ntry <= kMaxTry, "ntry=%d must be in 2..%d", par->ntry, kMaxTry);
+  HMCB_CHECK_ARG(par->nsteps >= 1, "nsteps must be >= 1");
+  HMCB_CHECK_ARG(par->smin > 0 && par->smax > par->smin, "need 0 < smin < smax");
+  for (int j = 0; j < par->n_ratios; ++j) {
+    HMCB_CHECK_ARG(par->ratios[j] > 0 && (j == 0 || par->ratios[j] > par->ratios[j - 1]), "ratios must be positive and increasing");
+    bool has_inverse = false;
+    for (int k = 0; k < par->n_ratios; ++k)
+      if (fabs(par->ratios[j] * par->ratios[k] - 1.0) <= 1e-8 + 1e-5) has_inverse = true;
+    HMCB_CHECK_ARG(has_inverse, "ratios[%d]=%g has no reciprocal in ratios: the reverse index of the reference is undefined", j,
+                   par->ratios[j]);
+  }
+  HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= par->n_segments + 2, "u_inject needs u_stride >= n_segments + 2");
+  if (chains->n_chains == 0) return 0;
+  const Entry* e = choose_entry(*model);
+  if (!e) return HMCB_E_UNSUPPORTED;
+  int64_t ft;
+  int epl;
+  if ((rc = ad_frame_threads(e, model, chains->n_chains, ft, epl, OP_QUERY_WALK))) return rc;
+  const size_t need = (size_t)(3 + 2 * par->n_ratios) * epl * ft * (model->dtype == HMCB_F64 ? 8 : 4);
+  if (!workspace || workspace_bytes < need) {
+    set_error("adhmc walk workspace too small: have %zu bytes, need %zu", workspace ? workspace_bytes : (size_t)0, need);
+    return HMCB_E_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (model->dtype == HMCB_F64) return adwalk_step_t<double>(e, model, chains, rng, par, out, workspace, ft, st);
+  return adwalk_step_t<float>(e, model, chains, rng, par, out, workspace, ft, st);
 }
 
 }  // extern "C"

@@ -309,6 +309,7 @@ struct AdArgs {
   int32_t u_stride;
   const T* minv;
   int32_t n_leap, ntry, nsteps;
+  double tint;             // > 0: the main trajectory takes int(tint/eps) + 1 steps (src/adaptivehmc.py:178-179)
   double steps[kMaxTry];   // trial step sizes (host-computed np.logspace)
   double pwts[kMaxTry];    // steps**0.5
   T* p_out;
@@ -439,7 +440,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_adhmc_eps0(const Model model,
 #pragma unroll
     for (int s = 0; s < EPL; ++s) p[s] = f_p0[(int64_t)s * FT];
     T Vs, Ve;
-    const int Nm = a.n_leap > 1 ? a.n_leap : 1;
+    int Nm = a.n_leap > 1 ? a.n_leap : 1;
+    if (a.tint > 0) { Nm = (int)(a.tint / (double)ss) + 1; if (Nm < 1) Nm = 1; }
     leapfrog<Model, T, EPL, LPC, UNITM>(model, q, p, minv, Nm, ss, c, Vs, Ve);
     const T H1 = Ve + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
     cH += 1; cVg += Nm + 1; cLeap += 1;
@@ -493,6 +495,339 @@ __global__ void __launch_bounds__(THREADS, MINB) k_adhmc_eps0(const Model model,
         for (int s = 0; s < EPL; ++s) p[s] = f_p0[(int64_t)s * FT];
         store_vec<T, EPL, LPC>(p, a.p_out, off, a.sd, c.lane, d);
       }
+    }
+  }
+}
+
+// ------------------------------------------------------------------ AdHMC / AdHMC_tint
+// adaptivehmc.AdHMC.hmc_step (src/adaptivehmc.py:227-354) and AdHMC_tint.hmc_step (:394-519): the
+// step size walks inside the trajectory.  The trajectory is cut into nseg segments; after each one
+// every ratio r_j proposes the step size eps*r_j, a candidate segment is integrated for each, one is
+// chosen with probability proportional to w_j e^{H1-H_j}, and the probability that the reverse walk
+// (from the same state with the momentum flipped, at the new step size) picks the old step size is
+// collected for the Hastings factor.  A segment is `nleap` steps (AdHMC) or max(1, int(tint/eps))
+// steps (AdHMC_tint).  The first step size and the last reverse probability come from the same trial
+// sweep as AdHMC_eps0 (get_stepsize, :202-224).
+//
+// Per thread the scratch holds p0, the current base state (q1, p1) and the nr candidate states;
+// everything else is scalar.  Step sizes and choice probabilities are double whatever T is.
+constexpr int kMaxRatios = 4;
+
+template <typename T>
+struct WalkArgs {
+  int64_t n_chains, chain_offset;
+  int32_t d;
+  const T* q_in;
+  T* q_out;
+  int64_t sc, sd;
+  uint64_t seed;
+  uint32_t iteration;
+  int32_t rng_flags;
+  const T* p_inject;
+  const double* u_inject;    // [C,u_stride]: sx, sx2, one per later segment (the choice), accept
+  int32_t u_stride;
+  const T* minv;
+  int32_t nseg;              // N = Nleap // nleap (AdHMC) or ntimes (AdHMC_tint)
+  int32_t nleap;             // steps per segment (AdHMC)
+  int32_t tint_mode;         // 1: steps per segment = max(1, int(tint/eps))
+  double tint;
+  int32_t nr;
+  double ratios[kMaxRatios], pwts0[kMaxRatios];
+  double smin, smax;
+  int32_t ntry, nsteps;
+  double steps[kMaxTry], pwts[kMaxTry];
+  T* p_out;
+  int32_t* code;             // 1 / 0 / 2, or 100+i when the forward weights of segment i blow up (:296-301)
+  T* probs;                  // [C,3] prob, prob/hastings, hastings (NaN on blow-up)
+  T* checks;                 // [C,3,nseg] pf_den, pb_num, eps
+  int32_t* counts;           // [C,3]
+  T* frames;                 // [(3 + 2*nr)*EPL*frame_threads]
+  int64_t frame_threads;
+};
+
+template <class Model, typename T, int EPL, int LPC, bool UNITM, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) k_adhmc_walk(const Model model, const WalkArgs<T> a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  using Lay = Layout<EPL, LPC>;
+  constexpr int GPB = THREADS / LPC;
+  const int d = a.d;
+  model.block_init(smem_raw, THREADS);
+  GroupCtx<T> c;
+  c.lane = threadIdx.x & (LPC - 1);
+  c.d = d;
+  const int group_in_warp = (threadIdx.x & 31) / LPC;
+  c.mask = (LPC == 32) ? 0xffffffffu : (((1u << LPC) - 1u) << (group_in_warp * LPC));
+  c.smem_q = nullptr;
+  if (Model::kNeedsSmem) c.smem_q = (T*)smem_raw + model.p_smem_elems() + (size_t)(threadIdx.x / LPC) * d;
+  T minv[UNITM ? 1 : EPL];
+  if (!UNITM) {
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) {
+      const int i = Lay::elem(c.lane, s);
+      minv[UNITM ? 0 : s] = (i < d) ? a.minv[i] : T(1);
+    }
+  } else {
+    minv[0] = T(1);
+  }
+  const int64_t gthread = (int64_t)blockIdx.x * THREADS + threadIdx.x;
+  const int64_t FT = a.frame_threads;
+  const int64_t slot = (int64_t)EPL * FT;
+  T* f_p0 = a.frames + gthread;
+  T* f_q1 = f_p0 + slot;
+  T* f_p1 = f_q1 + slot;
+  T* f_cand = f_p1 + slot;   // candidate j: q at (2j)*slot, p at (2j+1)*slot
+  const int64_t total_groups = (int64_t)gridDim.x * GPB;
+  const int ntry = a.ntry, nr = a.nr, N = a.nseg;
+
+  for (int64_t chain = gthread / LPC; chain < a.n_chains; chain += total_groups) {
+    const int64_t off = chain * a.sc;
+    const uint64_t gchain = (uint64_t)(a.chain_offset + chain);
+    T q[EPL], p[EPL];
+    int cH = 0, cVg = 0, cLeap = 0;
+    T pp[kMaxTry];
+
+    auto uniform = [&](int idx) -> double {
+      if (a.u_inject) return a.u_inject[chain * a.u_stride + idx];
+      uint32_t w[4];
+      Philox::gen(a.seed, gchain, a.iteration, STREAM_STEPSIZE, (uint32_t)(idx >> 1), w);
+      return (idx & 1) ? u53(w[2], w[3]) : u53(w[0], w[1]);
+    };
+    auto seg_steps = [&](double eps) -> int {
+      if (!a.tint_mode) return a.nleap > 1 ? a.nleap : 1;
+      const int n = (int)(a.tint / eps);
+      return n > 1 ? n : 1;
+    };
+    auto put_check = [&](int row, int i, double v) {
+      if (a.checks && c.lane == 0) a.checks[(chain * 3 + row) * N + i] = (T)v;
+    };
+    auto load_base = [&](T sign) {
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) { q[s] = f_q1[(int64_t)s * FT]; p[s] = sign * f_p1[(int64_t)s * FT]; }
+    };
+
+    {
+      TransArgs<T> ta;
+      ta.chain_offset = a.chain_offset; ta.sc = a.sc; ta.sd = a.sd; ta.seed = a.seed; ta.iteration = a.iteration;
+      ta.rng_flags = a.rng_flags; ta.p_inject = a.p_inject; ta.p_prev = nullptr;
+      draw_momentum<T, EPL, LPC, UNITM>(p, ta, minv, chain, c.lane, d);
+    }
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) f_p0[(int64_t)s * FT] = p[s];
+    if (a.checks && c.lane == 0)
+      for (int i = 0; i < 3 * N; ++i) a.checks[chain * 3 * N + i] = T(0);
+
+    // get_stepsize's trial sweep from (q0, p0) or from the current base with p flipped
+    auto sweep = [&](bool reverse, T& Hbase) {
+      T sum = T(0);
+      for (int i = 0; i <= ntry; ++i) {
+        if (!reverse) {
+          load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
+#pragma unroll
+          for (int s = 0; s < EPL; ++s) p[s] = f_p0[(int64_t)s * FT];
+        } else {
+          load_base(T(-1));
+        }
+        if (i == 0) {
+          const T K = kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+          T tmp[EPL];
+#pragma unroll
+          for (int s = 0; s < EPL; ++s) tmp[s] = T(0);
+          Hbase = model.template kick<EPL, LPC, true>(q, tmp, T(0), c) + K;
+          cH += 1;
+          continue;
+        }
+        T Vs, Ve;
+        const int Nt = a.nsteps > 1 ? a.nsteps : 1;
+        leapfrog<Model, T, EPL, LPC, UNITM>(model, q, p, minv, Nt, (T)a.steps[i - 1], c, Vs, Ve);
+        const T Hi = Ve + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+        cH += 1; cVg += Nt + 1; cLeap += 1;
+        T w = t_exp<T>(Hbase - Hi) * (T)a.pwts[i - 1];
+        if (t_bad(w)) w = T(0);
+        pp[i - 1] = w;
+        sum += w;
+      }
+      for (int i = 0; i < ntry; ++i) pp[i] = pp[i] / sum;
+    };
+
+    // ---- first step size (src/adaptivehmc.py:268 -> :202-222); H0 is evaluated by hmc_step and by get_stepsize
+    T H0;
+    sweep(false, H0);
+    cH += 1;
+    int isx = -1;
+    {
+      T cdf_min = pp[0], r2 = T(0), run = T(0);
+      for (int i = 0; i < ntry; ++i) { r2 += pp[i]; if (i == 0 || r2 < cdf_min) cdf_min = r2; }
+      const T sx = cdf_min + (T(1) - cdf_min) * (T)uniform(0);
+      for (int i = 0; i < ntry; ++i) { run += pp[i]; if (sx > run) isx = i; }
+    }
+    bool broken = (isx < 0) || (isx > ntry - 2);   // the reference raises IndexError here; we reject (code 2)
+    if (isx < 0) isx = 0;
+    if (isx > ntry - 2) isx = ntry - 2;
+    double ss = a.steps[isx] + (a.steps[isx + 1] - a.steps[isx]) * uniform(1);
+    double prod_pf = (double)pp[isx + 1], prod_pb = 1.0;
+    put_check(0, 0, prod_pf);
+    put_check(2, 0, ss);
+
+    // ---- first segment from (q0, p0)
+    load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) p[s] = f_p0[(int64_t)s * FT];
+    T Vs, Ve;
+    {
+      const int n0 = seg_steps(ss);
+      leapfrog<Model, T, EPL, LPC, UNITM>(model, q, p, minv, n0, (T)ss, c, Vs, Ve);
+      cH += 1; cVg += n0 + 1; cLeap += 1;
+    }
+    T H1 = Ve + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) { f_q1[(int64_t)s * FT] = q[s]; f_p1[(int64_t)s * FT] = p[s]; }
+    T Hprev = H0;
+    double ssnew = ss;
+    int blown = -1, pbind = 0;
+
+    for (int i = 0; i < N - 1; ++i) {
+      double pf[kMaxRatios], pb[kMaxRatios];
+      T Hs[kMaxRatios];
+      // forward candidates (:280-290)
+      for (int j = 0; j < nr; ++j) {
+        const double ss2 = ss * a.ratios[j];
+        const int n = seg_steps(ss2);
+        load_base(T(1));
+        leapfrog<Model, T, EPL, LPC, UNITM>(model, q, p, minv, n, (T)ss2, c, Vs, Ve);
+        Hs[j] = Ve + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+        cH += 1; cVg += n + 1; cLeap += 1;
+        T* fq = f_cand + (int64_t)(2 * j) * slot;
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) { fq[(int64_t)s * FT] = q[s]; fq[slot + (int64_t)s * FT] = p[s]; }
+        T pH = t_exp<T>(H1 - Hs[j]);
+        if (t_bad(pH)) pH = T(0);
+        pf[j] = (double)pH;
+      }
+      double sum = 0.0;
+      for (int j = 0; j < nr; ++j) {
+        double w = a.pwts0[j];
+        if (j == 0 && a.smin > ss * a.ratios[0]) w = 0.0;
+        if (j == nr - 1 && a.smax < ss * a.ratios[nr - 1]) w = 0.0;
+        pf[j] *= w;
+        sum += pf[j];
+      }
+      double sum2 = 0.0;
+      for (int j = 0; j < nr; ++j) { pf[j] /= sum; sum2 += pf[j]; }
+      if (t_bad(sum2)) { blown = i; break; }
+      // np.random.choice(nr, p=pf): cdf = cumsum(pf) / cdf[-1]; index = #(cdf <= u)
+      int pind = 0;
+      {
+        double cdf[kMaxRatios], run = 0.0;
+        for (int j = 0; j < nr; ++j) { run += pf[j]; cdf[j] = run; }
+        const double u = uniform(2 + i);
+        for (int j = 0; j < nr; ++j) if (cdf[j] / cdf[nr - 1] <= u) pind = j + 1;
+        if (pind > nr - 1) pind = nr - 1;
+      }
+      ssnew = ss * a.ratios[pind];
+      prod_pf *= pf[pind];
+      put_check(0, i + 1, pf[pind]);
+      const T H2 = Hs[pind];
+      // reverse walk from (q1, -p1) at the new step size (:311-329)
+      for (int j = 0; j < nr; ++j) {
+        const double ss2 = ssnew * a.ratios[j];
+        T Hb;
+        if (fabs(ss2 - ss) <= 1e-8 + 1e-5 * fabs(ss)) {        // np.allclose(ssnew*ratios[j], ss)
+          Hb = Hprev;
+          pbind = j;
+        } else {
+          const int n = seg_steps(ss2);
+          load_base(T(-1));
+          leapfrog<Model, T, EPL, LPC, UNITM>(model, q, p, minv, n, (T)ss2, c, Vs, Ve);
+          Hb = Ve + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+          cH += 1; cVg += n + 1; cLeap += 1;
+        }
+        T pH = t_exp<T>(H1 - Hb);
+        if (t_bad(pH)) pH = T(0);
+        pb[j] = (double)pH;
+      }
+      sum = 0.0;
+      for (int j = 0; j < nr; ++j) {
+        double w = a.pwts0[j];
+        if (j == 0 && a.smin > ssnew * a.ratios[0]) w = 0.0;
+        if (j == nr - 1 && a.smax < ssnew * a.ratios[nr - 1]) w = 0.0;
+        pb[j] *= w;
+        sum += pb[j];
+      }
+      const double pbn = pb[pbind] / sum;
+      prod_pb *= pbn;
+      put_check(1, i, pbn);
+      put_check(2, i + 1, ssnew);
+      // the chosen candidate becomes the base
+      ss = ssnew;
+      Hprev = H1;
+      H1 = H2;
+      {
+        const T* fq = f_cand + (int64_t)(2 * pind) * slot;
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) { f_q1[(int64_t)s * FT] = fq[(int64_t)s * FT]; f_p1[(int64_t)s * FT] = fq[slot + (int64_t)s * FT]; }
+      }
+    }
+
+    if (blown >= 0) {
+      // "Something blew up so returning initial position" (:296-301)
+      if (c.lane == 0) {
+        const T qn = (T)nan("");
+        if (a.code) a.code[chain] = 100 + blown;
+        if (a.probs) { a.probs[3 * chain] = qn; a.probs[3 * chain + 1] = qn; a.probs[3 * chain + 2] = qn; }
+        if (a.counts) { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = cLeap; }
+      }
+    } else {
+      // ---- probability that the reverse walk starts with the final step size (:340-342)
+      double pb_last = 0.0;
+      if (ssnew > a.smin && ssnew < a.smax) {
+        T Hb;
+        sweep(true, Hb);
+        int jb = -1;
+        for (int i = ntry - 1; i >= 0; --i) if (a.steps[i] > ssnew) jb = i;
+        if (jb < 0) { jb = ntry - 1; broken = true; }
+        pb_last = (double)pp[jb];
+      }
+      prod_pb *= pb_last;
+      put_check(1, N - 1, pb_last);
+      const double hast = prod_pb / prod_pf;
+      const double prob = (double)t_exp<T>(H0 - H1) * hast;
+      T dq = T(0);
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) {
+        const int i = Lay::elem(c.lane, s);
+        if (i < d) dq += a.q_in[off + i * a.sd] - f_q1[(int64_t)s * FT];
+      }
+      dq = group_sum_masked<LPC, T>(dq, c.mask);
+      const bool bad = broken || t_bad(prob) || dq == T(0);
+      bool accept = false;
+      if (!bad) {
+        const double u = uniform(N + 1);
+        accept = !(u > (prob < 1.0 ? prob : 1.0));
+      }
+      if (c.lane == 0) {
+        if (a.code) a.code[chain] = bad ? 2 : (accept ? 1 : 0);
+        if (a.probs) { a.probs[3 * chain] = (T)prob; a.probs[3 * chain + 1] = (T)(prob / hast); a.probs[3 * chain + 2] = (T)hast; }
+        if (a.counts) { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = cLeap; }
+      }
+      if (accept) {
+        load_base(T(1));
+        store_vec<T, EPL, LPC>(q, a.q_out, off, a.sd, c.lane, d);
+        if (a.p_out) store_vec<T, EPL, LPC>(p, a.p_out, off, a.sd, c.lane, d);
+        continue;
+      }
+    }
+    // rejected, no-move or blown up: (q0, p0)
+    if (a.q_out != a.q_in) {
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) {
+        const int i = Lay::elem(c.lane, s);
+        if (i < d) a.q_out[off + i * a.sd] = a.q_in[off + i * a.sd];
+      }
+    }
+    if (a.p_out) {
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) p[s] = f_p0[(int64_t)s * FT];
+      store_vec<T, EPL, LPC>(p, a.p_out, off, a.sd, c.lane, d);
     }
   }
 }

@@ -13,7 +13,7 @@
 namespace hmcb {
 
 enum Op { OP_HMC = 0, OP_DR0 = 1, OP_DRN = 2, OP_LEAPFROG = 3, OP_LOGPGRAD = 4, OP_QUERY = 5, OP_MALA = 6, OP_ADHMC = 7,
-          OP_QUERY_AD = 8, OP_GHMC = 9 };
+          OP_QUERY_AD = 8, OP_GHMC = 9, OP_ADWALK = 10, OP_QUERY_WALK = 11 };
 constexpr int kGhmcMaxEpl = 32;  // GHMC keeps q, p and the gradient: 3*EPL values per lane
 constexpr int kMalaMaxEpl = 28;  // MALA keeps q, grad, q1, grad1 in registers: 4*EPL values per lane
 
@@ -238,6 +238,23 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
     }
     case OP_QUERY_AD: {
       auto k = k_adhmc_eps0<Model, T, EPL, LPC, UNITM, THREADS, MINB>;
+      if ((rc = prep(k, max_blocks))) return rc;
+      LaunchInfo* li = (LaunchInfo*)args;
+      li->threads = THREADS;
+      li->max_blocks = max_blocks;
+      li->epl = EPL;
+      li->lpc = LPC;
+      return 0;
+    }
+    case OP_ADWALK: {
+      auto k = k_adhmc_walk<Model, T, EPL, LPC, UNITM, THREADS, MINB>;
+      if ((rc = prep(k, max_blocks))) return rc;
+      WalkArgs<T>& a = *(WalkArgs<T>*)args;
+      k<<<(int)(a.frame_threads / THREADS), THREADS, smem, st>>>(model, a);
+      break;
+    }
+    case OP_QUERY_WALK: {
+      auto k = k_adhmc_walk<Model, T, EPL, LPC, UNITM, THREADS, MINB>;
       if ((rc = prep(k, max_blocks))) return rc;
       LaunchInfo* li = (LaunchInfo*)args;
       li->threads = THREADS;

@@ -314,7 +314,7 @@ class Engine:
         out["_keep"] = keep
         return out
 
-    def adhmc_eps0_step(self, q, n_leap, steps, nsteps, p=None, u=None, q_out=None):
+    def adhmc_eps0_step(self, q, n_leap, steps, nsteps, p=None, u=None, q_out=None, tint=0.0):
         m = self._ensure()
         C_ = q.shape[0]
         steps = np.ascontiguousarray(steps, dtype=np.float64)
@@ -336,9 +336,48 @@ class Engine:
             ch = self._chains(q, q_out)
             r, keep = self._rng(p, u, 3, C_)
             _lib.check(self.lib.hmcb_adhmc_eps0_step(
-                C.byref(m), C.byref(ch), C.byref(r), int(n_leap), steps.ctypes.data_as(C.POINTER(C.c_double)),
+                C.byref(m), C.byref(ch), C.byref(r), int(n_leap), float(tint), steps.ctypes.data_as(C.POINTER(C.c_double)),
                 int(steps.size), int(nsteps), C.byref(so), C.c_void_p(self._ws.data_ptr()), self._ws.numel(),
                 self._stream()))
+        self.iteration += 1
+        out["_keep"] = keep
+        return out
+
+    def adhmc_walk_step(self, q, n_segments, n_leap_segment, tint, ratios, pwts0, smin, smax, steps, nsteps, p=None,
+                        u=None, q_out=None):
+        """hmcb_adhmc_walk_step on device tensor q [C,d] (AdHMC / AdHMC_tint)."""
+        m = self._ensure()
+        C_ = q.shape[0]
+        steps = np.ascontiguousarray(steps, dtype=np.float64)
+        nr = len(ratios)
+        if not 1 <= nr <= 4 or len(pwts0) != nr:
+            raise ValueError("ratios and pwts0 must have the same length, at most 4")
+        par = _lib.WalkPar()
+        par.n_segments, par.n_leap_segment, par.tint = int(n_segments), int(n_leap_segment), float(tint)
+        par.n_ratios, par.ntry, par.nsteps = nr, int(steps.size), int(nsteps)
+        for j in range(nr):
+            par.ratios[j], par.pwts0[j] = float(ratios[j]), float(pwts0[j])
+        par.smin, par.smax = float(smin), float(smax)
+        par.steps = steps.ctypes.data_as(C.POINTER(C.c_double))
+        with torch.cuda.device(self.device):
+            need = self.lib.hmcb_adhmc_walk_workspace_bytes(C.byref(m), C_, nr)
+            if need == 0:
+                _lib.check(_lib.E_ARG)
+            if self._ws is None or self._ws.numel() < need:
+                self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+            q_out = torch.empty_like(q) if q_out is None else q_out
+            out = {"q": q_out, "p": torch.empty_like(q),
+                   "code": torch.empty(C_, dtype=torch.int32, device=self.device),
+                   "probs": torch.empty((C_, 3), dtype=self.dtype, device=self.device),
+                   "checks": torch.empty((C_, 3, int(n_segments)), dtype=self.dtype, device=self.device),
+                   "counts": torch.empty((C_, 3), dtype=torch.int32, device=self.device)}
+            so = _lib.WalkOut()
+            so.p_out, so.code, so.probs = _lib.ptr(out["p"]), _lib.ptr(out["code"]), _lib.ptr(out["probs"])
+            so.checks, so.counts = _lib.ptr(out["checks"]), _lib.ptr(out["counts"])
+            ch = self._chains(q, q_out)
+            r, keep = self._rng(p, u, int(n_segments) + 2, C_)
+            _lib.check(self.lib.hmcb_adhmc_walk_step(C.byref(m), C.byref(ch), C.byref(r), C.byref(par), C.byref(so),
+                                                     C.c_void_p(self._ws.data_ptr()), self._ws.numel(), self._stream()))
         self.iteration += 1
         out["_keep"] = keep
         return out

@@ -232,8 +232,9 @@ typedef struct hmcb_ghmc_io {
 int hmcb_ghmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
                    double step_size, const hmcb_ghmc_io* io, void* stream);
 
-/* AdHMC_eps0.hmc_step with Tint = 0 (src/adaptivehmc.py:138-192) and its step-size
- * draw get_stepsize (:111-134).  `steps` is a HOST array of the ntry trial step sizes
+/* AdHMC_eps0.hmc_step (src/adaptivehmc.py:138-192) and its step-size draw get_stepsize
+ * (:111-134).  Give either n_leap >= 1 (and tint = 0) or tint = Tint > 0 (and n_leap = 0): with
+ * Tint the trajectory takes int(Tint/eps) + 1 steps of the drawn step size (:178-179).  `steps` is a HOST array of the ntry trial step sizes
  * (np.logspace(log10(smin), log10(smax), ntry), computed by the caller so that the
  * values are bit-identical to numpy's).  Uniform draws, in the reference's order:
  * u[0] bin draw, u[1] within-bin draw, u[2] accept test.  Codes 1/0/2; where the
@@ -247,7 +248,43 @@ typedef struct hmcb_adhmc_out {
 } hmcb_adhmc_out;
 size_t hmcb_adhmc_eps0_workspace_bytes(const hmcb_model* model, int64_t n_chains);
 int hmcb_adhmc_eps0_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
-                         const double* steps, int32_t ntry, int32_t nsteps, const hmcb_adhmc_out* out,
+                         double tint, const double* steps, int32_t ntry, int32_t nsteps, const hmcb_adhmc_out* out,
+                         void* workspace, size_t workspace_bytes, void* stream);
+
+/* AdHMC.hmc_step (src/adaptivehmc.py:227-354) and AdHMC_tint.hmc_step (:394-519): the step size
+ * walks inside the trajectory.  n_segments = Nleap // nleap (AdHMC, every segment n_leap_segment
+ * steps) or ntimes (AdHMC_tint, tint = Tint/ntimes > 0 and a segment of step size e is
+ * max(1, int(tint/e)) steps).  After each segment every ratio proposes e*ratio, one is chosen with
+ * probability ~ pwts0[j] * exp(H1 - H_j) (np.random.choice, :303) and the reverse walk's probability
+ * of the old step size enters the Hastings factor; the first step size and the last reverse
+ * probability come from get_stepsize's trial sweep (:202-224) over the HOST array `steps`.
+ * `ratios` must be increasing and closed under reciprocal (for every j some j' has
+ * ratios[j]*ratios[j'] == 1 to np.allclose's tolerance), as the reference's default
+ * [1/sqrt2, sqrt2]; otherwise the reference's reverse index is undefined.
+ * Uniforms, in the reference's order: u[0] bin draw, u[1] within-bin draw, u[2+i] the choice after
+ * segment i (i < n_segments-1), u[n_segments+1] accept test.  Codes 1/0/2, and 100+i when the
+ * forward weights of segment i are all zero / NaN (:296-301; (q0,p0) returned, probs NaN). */
+#define HMCB_MAX_RATIOS 4
+typedef struct hmcb_adhmc_walk_par {
+  int32_t n_segments;
+  int32_t n_leap_segment;
+  double tint;                       /* 0: AdHMC; > 0: AdHMC_tint */
+  int32_t n_ratios;
+  int32_t ntry, nsteps;              /* trial sweep: ntry_eps0, nsteps_eps0 */
+  double ratios[HMCB_MAX_RATIOS], pwts0[HMCB_MAX_RATIOS];
+  double smin, smax;
+  const double* steps;               /* host, [ntry]: np.logspace / np.linspace(smin, smax, ntry) */
+} hmcb_adhmc_walk_par;
+typedef struct hmcb_adhmc_walk_out {
+  void* p_out;         /* layout of q */
+  int32_t* code;       /* [C] */
+  void* probs;         /* [C,3] prob, prob/hastings, hastings */
+  void* checks;        /* [C,3,n_segments] pf_den, pb_num, eps (np.stack at :347) */
+  int32_t* counts;     /* [C,3] */
+} hmcb_adhmc_walk_out;
+size_t hmcb_adhmc_walk_workspace_bytes(const hmcb_model* model, int64_t n_chains, int32_t n_ratios);
+int hmcb_adhmc_walk_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng,
+                         const hmcb_adhmc_walk_par* par, const hmcb_adhmc_walk_out* out,
                          void* workspace, size_t workspace_bytes, void* stream);
 
 /* Bayesian logistic regression, log p = sum_i [y_i z_i - softplus(z_i)] - |theta|^2/(2 tau^2),

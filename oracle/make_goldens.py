@@ -100,6 +100,54 @@ ADHMC_CASES = [
 ]
 
 
+ADHMC_CASES.append(dict(name="adhmc_funnel10_tint", model=dict(kind="funnel", d=10), C=12, T=4, seed=303,
+                        args=dict(Nleap=0, Tint=1.5, smin=0.02, smax=0.5, ntry=6, nsteps=2)))
+
+WALK_CASES = [
+    dict(name="adwalk_funnel10", cls="AdHMC", model=dict(kind="funnel", d=10), C=16, T=4, seed=501,
+         args=dict(Nleap=24, nleap=4, smin=0.02, smax=0.8, ntry_eps0=6, nsteps_eps0=2)),
+    dict(name="adwalk_funnel50_tint", cls="AdHMC_tint", model=dict(kind="funnel", d=50), C=12, T=3, seed=502,
+         args=dict(Tint=2.0, ntimes=5, smin=0.02, smax=0.8, ntry_eps0=6, nsteps_eps0=2)),
+    dict(name="adwalk_rosen8_3ratios", cls="AdHMC", model=dict(kind="rosenbrock", d=8), C=16, T=4, seed=503,
+         args=dict(Nleap=20, nleap=4, ratios=[0.5, 1.0, 2.0], pwts0=[1.0, 2.0, 1.0], smin=0.005, smax=0.2, ntry_eps0=6,
+                   nsteps_eps0=2, logeps=False)),
+    dict(name="adwalk_funnel10_wide", cls="AdHMC", model=dict(kind="funnel", d=10), C=48, T=4, seed=504,
+         args=dict(Nleap=24, nleap=4, smin=0.05, smax=3.0, ntry_eps0=6, nsteps_eps0=1)),
+]
+
+
+def run_walk(case):
+    """hmc_step of adaptivehmc.AdHMC / AdHMC_tint; N+2 replayed uniforms per transition (np.random.choice included).
+    The reference's blow-up return spells NaN as np.NaN, which numpy 2 no longer has: it is given back for the run."""
+    ad = ref_loader.load("adaptivehmc")
+    model = build_model(case["model"])
+    d, C, T, a = model.d, case["C"], case["T"], case["args"]
+    N = a["ntimes"] if "ntimes" in a else a["Nleap"] // a["nleap"]
+    P, U = replay.make_draws(case["seed"], T, C, d, N + 2)
+    q0 = _q0(case, model)
+    ref = getattr(ad, case["cls"])(model.log_prob, model.grad_log_prob)
+    q = np.zeros((T, C, d)); p = np.zeros((T, C, d)); code = np.zeros((T, C))
+    probs = np.zeros((T, C, 3)); checks = np.zeros((T, C, 3, N)); counts = np.zeros((T, C, 3), dtype=np.int64)
+    had_nan = hasattr(np, "NaN")
+    if not had_nan:
+        np.NaN = np.nan
+    try:
+        with np.errstate(all="ignore"), contextlib.redirect_stdout(io.StringIO()):
+            for c in range(C):
+                qc = q0[c]
+                for t in range(T):
+                    with replay.patched_numpy_random(replay.Draws([P[t, c]], U[t, c])):
+                        out = ref.hmc_step(qc, **a)
+                    qc = out[0]
+                    q[t, c], p[t, c], code[t, c], probs[t, c], checks[t, c], counts[t, c] = out
+    finally:
+        if not had_nan:
+            del np.NaN
+    np.savez_compressed(os.path.join(OUT, case["name"] + ".npz"), spec=json.dumps(case), q0=q0, P=P, U=U, q=q, p=p,
+                        code=code, probs=probs, checks=checks, counts=counts)
+    return code
+
+
 def _q0(case, model):
     q0 = np.random.default_rng(case["seed"] + 1000).uniform(-1, 1, (case["C"], model.d))
     if case["model"]["kind"] == "rosenbrock":
@@ -142,7 +190,8 @@ def run_adhmc(case):
             qc = q0[c]
             for t in range(T):
                 with replay.patched_numpy_random(replay.Draws([P[t, c]], U[t, c])):
-                    out = ref.hmc_step(qc, a["Nleap"], smin=a["smin"], smax=a["smax"], ntry=a["ntry"], nsteps=a["nsteps"])
+                    out = ref.hmc_step(qc, a["Nleap"], smin=a["smin"], smax=a["smax"], Tint=a.get("Tint", 0), ntry=a["ntry"],
+                                       nsteps=a["nsteps"])
                 qc = out[0]
                 q[t, c], p[t, c], code[t, c], probs[t, c], aux[t, c], counts[t, c] = out
     np.savez_compressed(os.path.join(OUT, case["name"] + ".npz"), spec=json.dumps(case), q0=q0, P=P, U=U, q=q, p=p,
@@ -223,7 +272,7 @@ def main():
         print("%-24s codes %s" % (case["name"], dict(zip(vals.tolist(), n.tolist()))))
     vals, n = np.unique(run_logistic(), return_counts=True)
     print("%-24s codes %s" % ("logit_hmc", dict(zip(vals.tolist(), n.tolist()))))
-    for cases, fn in ((MALA_CASES, run_mala), (ADHMC_CASES, run_adhmc), (PROBDR_CASES, run_probdr)):
+    for cases, fn in ((MALA_CASES, run_mala), (ADHMC_CASES, run_adhmc), (PROBDR_CASES, run_probdr), (WALK_CASES, run_walk)):
         for case in cases:
             vals, n = np.unique(fn(case), return_counts=True)
             print("%-24s codes %s" % (case["name"], dict(zip(vals.tolist(), n.tolist()))))

@@ -12,6 +12,9 @@ transition:
   MALA.step            normal(size=d)  then  conditional uniform(0,1,size=1) (src/mala.py:47,40)
   AdHMC_eps0.hmc_step  normal(size=d), uniform(low=cdf.min()), uniform(lo,hi), conditional
                        uniform(0,1,size=1) (src/adaptivehmc.py:162,127,129,190)
+  AdHMC(_tint).hmc_step normal(size=d), uniform(low=cdf.min()), uniform(lo,hi), one
+                       choice(nr, p=pf) per later segment, conditional uniform(0,1,size=1)
+                       (src/adaptivehmc.py:259,219,221,303,350)
 
 ``Draws`` holds one stream of standard-normal vectors and one stream of U[0,1)
 scalars and hands them out in call order; ``low``/``high`` are applied the way
@@ -53,15 +56,26 @@ class Draws:
         return np.full(size, val, dtype=np.float64)
 
 
+    def choice(self, a, p=None):
+        """np.random.choice(n, p=p) for one draw, as numpy's legacy generator does it
+        (numpy/random/mtrand.pyx, RandomState.choice with replace=True): cdf = cumsum(p),
+        cdf /= cdf[-1], index = searchsorted(cdf, u, side='right') with one U[0,1) draw."""
+        u = self._uniforms[self.n_uniform]
+        self.n_uniform += 1
+        cdf = np.asarray(p, dtype=np.float64).cumsum()
+        cdf /= cdf[-1]
+        return int(cdf.searchsorted(u, side="right"))
+
+
 @contextlib.contextmanager
 def patched_numpy_random(draws):
-    """Route np.random.normal / np.random.uniform to ``draws`` inside the block."""
-    saved = (np.random.normal, np.random.uniform)
-    np.random.normal, np.random.uniform = draws.normal, draws.uniform
+    """Route np.random.normal / np.random.uniform / np.random.choice to ``draws`` inside the block."""
+    saved = (np.random.normal, np.random.uniform, np.random.choice)
+    np.random.normal, np.random.uniform, np.random.choice = draws.normal, draws.uniform, draws.choice
     try:
         yield draws
     finally:
-        np.random.normal, np.random.uniform = saved
+        np.random.normal, np.random.uniform, np.random.choice = saved
 
 
 def make_draws(seed, T, C, d, n_uniform):

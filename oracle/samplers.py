@@ -279,8 +279,9 @@ def _eps0_trials(model, kin, q0, p0, smin, smax, ntry, nsteps, cnt):
     return steps, pp, np.cumsum(pp)
 
 
-def adhmc_eps0_step(model, q0, Nleap, rng, smin=0.01, smax=1.0, ntry=10, nsteps=1, invmetric_diag=None):
-    """adaptivehmc.AdHMC_eps0.hmc_step with Tint=0, src/adaptivehmc.py:138-192.
+def adhmc_eps0_step(model, q0, Nleap, rng, smin=0.01, smax=1.0, ntry=10, nsteps=1, invmetric_diag=None, Tint=0):
+    """adaptivehmc.AdHMC_eps0.hmc_step, src/adaptivehmc.py:138-192 (Nleap steps, or with Tint given
+    int(Tint/eps)+1 steps of the drawn step size, :178-179).
     Draw order: normal(d), uniform(low=cdf.min()), uniform(steps[i], steps[i+1]),
     conditional uniform(0,1,size=1).  Returns the reference's 6-tuple."""
     kin, cnt = Kinetics(invmetric_diag), Counters()
@@ -292,7 +293,7 @@ def adhmc_eps0_step(model, q0, Nleap, rng, smin=0.01, smax=1.0, ntry=10, nsteps=
         isx = np.where(sx > cdf)[0][-1]
         ss = rng.uniform(steps[isx], steps[isx + 1])
         pf_den = pp[isx + 1]
-        q1, p1 = leapfrog(model, kin, q0, p0, Nleap, ss, cnt)
+        q1, p1 = leapfrog(model, kin, q0, p0, Nleap if Tint == 0 else int(Tint / ss) + 1, ss, cnt)
         H1 = _H(model, kin, q1, p1, cnt)
         steps_b, pp_b, _ = _eps0_trials(model, kin, q1, -p1, smin, smax, ntry, nsteps, cnt)
         pb_num = pp_b[np.where(steps_b > ss)[0][0]]
@@ -304,6 +305,124 @@ def adhmc_eps0_step(model, q0, Nleap, rng, smin=0.01, smax=1.0, ntry=10, nsteps=
         if rng.uniform(0.0, 1.0, size=1) > min(1.0, prob):
             return (q0, p0, 0.0, *info)
         return (q1, p1, 1.0, *info)
+
+
+# ----------------------------------------------------------------------------- AdHMC / AdHMC_tint
+# Step size adapted inside the trajectory: the trajectory is cut into segments; after each one the
+# step size is multiplied by one of `ratios`, chosen with probability proportional to e^{-dH} of
+# the candidate segment, and the probability of the reverse choice is collected for the Hastings
+# factor.  The two classes differ only in the length of a segment: `nleap` steps (AdHMC) or
+# max(1, int(tint/eps)) steps (AdHMC_tint).
+
+def _adhmc_prob_of(model, kin, q, p, eps, smin, smax, ntry, nsteps, logspace, cnt):
+    """get_stepsize(..., eps=eps), src/adaptivehmc.py:202-224: probability of the bin above eps."""
+    H0 = _H(model, kin, q, p, cnt)
+    Hs = np.zeros(ntry)
+    steps = np.logspace(np.log10(smin), np.log10(smax), ntry) if logspace else np.linspace(smin, smax, ntry)
+    pwts = steps.copy() ** 0.5
+    for i, ss in enumerate(steps):
+        q1, p1 = leapfrog(model, kin, q, p, nsteps, ss, cnt)
+        Hs[i] = _H(model, kin, q1, p1, cnt)
+    pp = np.exp(H0 - Hs) * pwts
+    pp[np.isnan(pp)] = 0
+    pp[np.isinf(pp)] = 0
+    pp /= pp.sum()
+    return steps, pp, np.cumsum(pp)
+
+
+def adhmc_step(model, q0, rng, Nleap=100, nleap=10, ratios=(1 / np.sqrt(2), np.sqrt(2)), pwts0=(1.0, 1.0), smin=0.01,
+               smax=1.0, ntry_eps0=10, nsteps_eps0=1, logeps=True, Tint=None, ntimes=None, invmetric_diag=None):
+    """adaptivehmc.AdHMC.hmc_step (src/adaptivehmc.py:227-354) and, with Tint / ntimes given,
+    adaptivehmc.AdHMC_tint.hmc_step (:394-519).  Draw order: normal(d); uniform(low=cdf.min());
+    uniform(lo, hi); one np.random.choice(nr, p=pf) per later segment; conditional
+    uniform(0, 1, size=1).  On the blow-up path (:296-301) the reference's np.NaN is spelled
+    np.nan here (np.NaN no longer exists in numpy 2); values are the same."""
+    kin, cnt = Kinetics(invmetric_diag), Counters()
+    ratios = list(ratios)
+    nr = len(ratios)
+    tmode = Tint is not None
+    with np.errstate(all="ignore"):
+        p0 = rng.normal(size=q0.size).reshape(q0.shape) * kin.metricstd
+        if tmode:
+            tint = Tint / ntimes
+            N = ntimes
+            nsteps_of = lambda e: max(1, int(tint / e))
+        else:
+            N = int(Nleap // nleap)
+            nsteps_of = lambda e: nleap
+        eps, pf_den, pb_num = np.zeros(N), np.zeros(N), np.zeros(N)
+        H0 = _H(model, kin, q0, p0, cnt)
+        steps, pp, cdf = _adhmc_prob_of(model, kin, q0, p0, None, smin, smax, ntry_eps0, nsteps_eps0, logeps, cnt)
+        sx = rng.uniform(low=cdf.min())
+        isx = np.where(sx > cdf)[0][-1]
+        ss = rng.uniform(steps[isx], steps[isx + 1])
+        pf_den[0] = pp[isx + 1]
+        eps[0] = ss
+        q1, p1 = leapfrog(model, kin, q0, p0, nsteps_of(ss), ss, cnt)
+        H1 = _H(model, kin, q1, p1, cnt)
+        Hprev = H0
+        for i in range(N - 1):
+            pf, pb = np.zeros(nr), np.zeros(nr)
+            qs, ps, Hs = [], [], []
+            for j in range(nr):
+                ss2 = ss * ratios[j]
+                q, p = leapfrog(model, kin, q1, p1, nsteps_of(ss2), ss2, cnt)
+                qs.append(q)
+                ps.append(p)
+                Hs.append(_H(model, kin, q, p, cnt))
+                pH = np.exp(H1 - Hs[-1])
+                if _bad(pH):
+                    pH = 0
+                pf[j] = pH
+            pwts = np.ones(nr) * pwts0
+            if smin > ss * ratios[0]:
+                pwts[0] = 0
+            if smax < ss * ratios[-1]:
+                pwts[-1] = 0
+            pf *= pwts
+            pf /= pf.sum()
+            if _bad(pf.sum()):
+                return (q0, p0, 100 + i, [np.nan, np.nan, np.nan], np.stack([pf_den, pb_num, eps]), cnt.as_list())
+            pind = rng.choice(nr, p=pf)
+            ssnew = ss * ratios[pind]
+            q2, p2, H2 = qs[pind], ps[pind], Hs[pind]
+            pf_den[i + 1] = pf[pind]
+            Hsb = []
+            for j in range(nr):
+                if np.allclose(ssnew * ratios[j], ss):
+                    Hsb.append(Hprev)
+                    pbind = j
+                else:
+                    ss2 = ssnew * ratios[j]
+                    q, p = leapfrog(model, kin, q1, -p1, nsteps_of(ss2), ss2, cnt)
+                    Hsb.append(_H(model, kin, q, p, cnt))
+                pH = np.exp(H1 - Hsb[-1])
+                if _bad(pH):
+                    pH = 0
+                pb[j] = pH
+            pwts = np.ones(nr) * pwts0
+            if smin > ssnew * ratios[0]:
+                pwts[0] = 0
+            if smax < ssnew * ratios[-1]:
+                pwts[-1] = 0
+            pb *= pwts
+            pb /= pb.sum()
+            pb_num[i] = pb[pbind]
+            eps[i + 1] = ssnew
+            ss = ssnew
+            Hprev = H1
+            q1, p1, H1 = q2, p2, H2
+        if (ssnew > smin) and (ssnew < smax):
+            steps_b, pp_b, _ = _adhmc_prob_of(model, kin, q2, -p2, ssnew, smin, smax, ntry_eps0, nsteps_eps0, logeps, cnt)
+            pb_num[i + 1] = pp_b[np.where(steps_b > ssnew)[0][0]]
+        hastings = np.prod(pb_num[:i + 2]) / np.prod(pf_den[:i + 2])
+        prob = np.exp(H0 - H2) * hastings
+        info = [[prob, prob / hastings, hastings], np.stack([pf_den, pb_num, eps]), cnt.as_list()]
+        if _bad(prob) or (q0 - q1).sum() == 0:
+            return (q0, p0, 2.0, *info)
+        if rng.uniform(0.0, 1.0, size=1) > min(1.0, prob):
+            return (q0, p0, 0.0, *info)
+        return (q2, p2, 1.0, *info)
 
 
 # ----------------------------------------------------------------------------- diagnostics

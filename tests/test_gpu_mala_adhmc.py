@@ -67,8 +67,8 @@ def test_adhmc_eps0_golden(path):
     s = adaptivehmc.AdHMC_eps0(pm, device=_dev())
     for t in range(g["P"].shape[0]):
         q_in = g["q0"] if t == 0 else g["q"][t - 1]
-        q, p, code, probs, aux, counts = s.hmc_step(q_in, a["Nleap"], smin=a["smin"], smax=a["smax"], ntry=a["ntry"],
-                                                    nsteps=a["nsteps"], p=g["P"][t], u=g["U"][t])
+        q, p, code, probs, aux, counts = s.hmc_step(q_in, a["Nleap"], smin=a["smin"], smax=a["smax"], Tint=a.get("Tint", 0),
+                                                    ntry=a["ntry"], nsteps=a["nsteps"], p=g["P"][t], u=g["U"][t])
         assert np.array_equal(code, g["code"][t]), (code, g["code"][t])
         assert np.array_equal(counts, g["counts"][t])
         _close(aux, g["aux"][t], rtol=1e-9, atol=1e-12)

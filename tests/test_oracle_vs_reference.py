@@ -154,6 +154,64 @@ def test_adhmc_eps0_bit_exact(mi):
         q_r, q_o = out_r[0], out_o[0]
 
 
+@pytest.mark.parametrize("mi", [0, 1, 3])
+@pytest.mark.parametrize("variant", ["nleap", "tint", "three_ratios", "linear_grid"])
+def test_adhmc_walk_bit_exact(mi, variant, monkeypatch):
+    """adaptivehmc.AdHMC / AdHMC_tint hmc_step (src/adaptivehmc.py:227-354, :394-519)."""
+    ad = ref_loader.load("adaptivehmc")
+    if not hasattr(np, "NaN"):
+        monkeypatch.setattr(np, "NaN", np.nan, raising=False)   # the reference's blow-up path spells it np.NaN
+    model = _models()[mi]
+    funnel = model.name == "funnel"
+    smin, smax = (0.02, 0.8) if funnel else (0.005, 0.2)
+    kw = dict(smin=smin, smax=smax, ntry_eps0=6, nsteps_eps0=2)
+    if variant == "tint":
+        ref = ad.AdHMC_tint(model.log_prob, model.grad_log_prob)
+        kw.update(Tint=2.0 if funnel else 0.5, ntimes=5)
+        okw = dict(kw)
+    else:
+        ref = ad.AdHMC(model.log_prob, model.grad_log_prob)
+        kw.update(Nleap=24, nleap=4)
+        if variant == "three_ratios":
+            kw.update(ratios=[0.5, 1.0, 2.0], pwts0=[1.0, 2.0, 1.0])
+        if variant == "linear_grid":
+            kw.update(logeps=False)
+        okw = dict(kw)
+    T = 25
+    nseg = kw.get("ntimes", 6)
+    P, U = replay.make_draws(261 + mi, T, 1, model.d, nseg + 2)
+    q_r = q_o = _q0(model, mi) * (1.0 if funnel else 0.1) + (0.0 if funnel else 1.0)
+    codes = []
+    for t in range(T):
+        with replay.patched_numpy_random(replay.Draws([P[t, 0]], U[t, 0])):
+            out_r = ref.hmc_step(q_r, **kw)
+        out_o = samplers.adhmc_step(model, q_o, replay.Draws([P[t, 0]], U[t, 0]), **okw)
+        assert len(out_r) == len(out_o) == 6
+        for a, b in zip(out_r, out_o):
+            assert _same(a, b)
+        q_r, q_o = out_r[0], out_o[0]
+        codes.append(float(out_r[2]))
+    assert 1.0 in codes
+
+
+@pytest.mark.parametrize("mi", [0, 3])
+def test_adhmc_eps0_tint_bit_exact(mi):
+    """AdHMC_eps0 with an integration time instead of a step count (src/adaptivehmc.py:178-179)."""
+    ad = ref_loader.load("adaptivehmc")
+    model = _models()[mi]
+    ref = ad.AdHMC_eps0(model.log_prob, model.grad_log_prob)
+    P, U = replay.make_draws(161 + mi, 20, 1, model.d, 3)
+    q_r = q_o = _q0(model, mi)
+    for t in range(20):
+        with replay.patched_numpy_random(replay.Draws([P[t, 0]], U[t, 0])):
+            out_r = ref.hmc_step(q_r, 0, smin=0.01, smax=0.5, Tint=1.5, ntry=6, nsteps=2)
+        out_o = samplers.adhmc_eps0_step(model, q_o, 0, replay.Draws([P[t, 0]], U[t, 0]), smin=0.01, smax=0.5, ntry=6,
+                                         nsteps=2, Tint=1.5)
+        for a, b in zip(out_r, out_o):
+            assert _same(a, b)
+        q_r, q_o = out_r[0], out_o[0]
+
+
 def test_utils_ess_rcc_bit_exact():
     utils = ref_loader.load("utils")
     x = np.random.default_rng(0).standard_normal((400, 5, 3)).cumsum(axis=0) * 0.1
