@@ -331,9 +331,14 @@ def run_hmcb(a):
     st_ms = stats[3:3 + a.nprops].tolist()
     s0_flops = C * (L0 + 1) * fpg
     achieved = s0_flops / (st_ms[0] * 1e-3) / 1e12
-    roofline = {"bound": "fp64", "kernel": "k_transition<Funnel,f64,MODE_DR0> (DR stage 0)",
+    default_shape = (C == 1 << 20 and d == 50 and a.nleap == 150)
+    roofline = {"bound": "fp64", "kernel": "k_transition_ws<Funnel,f64,EPL=50,MODE_DR0> (DR stage 0, warp-specialised)",
                 "achieved": achieved, "peak": fp64_peak_tflops, "unit": "TFLOP/s",
-                "frac": achieved / fp64_peak_tflops if fp64_peak_tflops else None, "traffic": None,
+                "frac": achieved / fp64_peak_tflops if fp64_peak_tflops else None,
+                # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (profiles/r1b_ncu_dr_stages.md);
+                # algorithmic HBM bytes are 2*C*d*8 + outputs = 0.87 GB, i.e. no re-reads
+                "traffic": 447266560 + 347079680 if default_shape else None,
+                "traffic_unit": "bytes per launch (HBM; the kernel is FP64-pipe-bound, HBM is at 5 % of its peak)",
                 "peak_source": "hmcb_probe_fma: register-resident DFMA loop measured in this run on this GPU "
                                "(MEASURED_PEAKS.json has no FP64 figure)",
                 "algorithmic_flops_per_launch": s0_flops, "avg_launch_ms": st_ms[0],
@@ -346,28 +351,41 @@ def run_hmcb(a):
         qh = torch.empty((C, d), dtype=torch.float64).pin_memory()
         qh.copy_(q)
         dr_e = algorithms.DRHMC(model, device=dev, seed=a.seed + 1, chain_offset=lo)
+        # the momentum is not brought back: the reference's sample loop discards the p its step returns
+        # (src/algorithms.py:546-551); the same call with p is timed after it and reported beside it
         for _ in range(2):
-            r = dr_e.step(qh, a.nleap, a.step_size, a.nprops, a.stepfactor)
+            r = dr_e.step(qh, a.nleap, a.step_size, a.nprops, a.stepfactor, want_p=False)
             qh = r[0]
         dist.barrier()
         torch.cuda.synchronize()
         t0 = time.time()
         g_e2e = 0
         for _ in range(Ke):
-            r = dr_e.step(qh, a.nleap, a.step_size, a.nprops, a.stepfactor)
+            r = dr_e.step(qh, a.nleap, a.step_size, a.nprops, a.stepfactor, want_p=False)
             qh = r[0]
             g_e2e += int(r[4][:, 1].sum())
         torch.cuda.synchronize()
         dt = torch.tensor([time.time() - t0], dtype=torch.float64, device=dev)
+        r = (qh,)
+        for _ in range(3):                                                       # warm the pinned p buffers
+            r = dr_e.step(r[0], a.nleap, a.step_size, a.nprops, a.stepfactor)
+        torch.cuda.synchronize()
+        t1 = time.time()
+        for _ in range(3):
+            r = dr_e.step(r[0], a.nleap, a.step_size, a.nprops, a.stepfactor)
+        torch.cuda.synchronize()
+        ms_with_p = 1e3 * (time.time() - t1) / 3
         ge = torch.tensor([float(g_e2e)], dtype=torch.float64, device=dev)
         if world > 1:
             torch.distributed.all_reduce(dt, op=torch.distributed.ReduceOp.MAX)
             dist.all_reduce_sum(ge)
         h2d = C * d * 8
-        d2h = C * d * 8 * 2 + C * 4 + C * a.nprops * 8 + C * 12
+        d2h = C * d * 8 + C * 4 + C * a.nprops * 8 + C * 12
         e2e = {"value": float(ge[0]) / float(dt[0]), "unit": "grad_evals/s", "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "steps": Ke, "ms_per_step": 1e3 * float(dt[0]) / Ke,
-               "api": "hmc_b200.algorithms.DRHMC.step(q_pinned_host, ...) -> host (q, p, code, avec, counts)"}
+               "api": "hmc_b200.algorithms.DRHMC.step(q_pinned_host, ..., want_p=False) -> host (q, None, code, avec, "
+                      "counts); the reference's sample loop discards the returned momentum",
+               "ms_per_step_with_p_returned": ms_with_p, "d2h_bytes_per_step_with_p": d2h + C * d * 8}
 
     if rank != 0:
         return

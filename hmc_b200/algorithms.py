@@ -176,9 +176,11 @@ class DRHMC(HMC):
     ``step`` is hmcb_drhmc_step: stage kernels over device-compacted lists of the
     chains still rejecting, ghost recursion (get_num, :474-497) included."""
 
-    def step(self, q, nleap, step_size, nprops, stepfactor, p=None, u=None):
+    def step(self, q, nleap, step_size, nprops, stepfactor, p=None, u=None, want_p=True):
         """Returns (q, p, code, avec, [Hcount, Vgcount, leapcount]); code = j+1 if
-        accepted at stage j, else 0 (src/algorithms.py:500-530)."""
+        accepted at stage j, else 0 (src/algorithms.py:500-530).  want_p=False returns None
+        for p and skips its device write and device-to-host copy: the reference's own sample
+        loop throws the returned momentum away (src/algorithms.py:546-551)."""
         e = self.engine
         if torch.is_tensor(q) and q.device.type == "cpu" and q.dim() == 2 and p is None and u is None \
                 and q.shape[0] >= 8192:
@@ -186,11 +188,11 @@ class DRHMC(HMC):
             e._ensure()
             if q.shape[1] != self.model.d:
                 raise ValueError("q has dimension %d but the model has d=%d" % (q.shape[1], self.model.d))
-            h = e.drhmc_step_host(q.to(e.dtype), nleap, step_size, nprops, stepfactor)
+            h = e.drhmc_step_host(q.to(e.dtype), nleap, step_size, nprops, stepfactor, want_p=want_p)
             self.Hcount, self.Vgcount, self.leapcount = h["counts"][:, 0], h["counts"][:, 1], h["counts"][:, 2]
             return h["q"], h["p"], h["code"], h["avec"], h["counts"]
         b = self._device_q(q)
-        out = e.drhmc_step(b.q, nleap, step_size, nprops, stepfactor, p=p, u=u)
+        out = e.drhmc_step(b.q, nleap, step_size, nprops, stepfactor, p=p, u=u, want_p=want_p)
         if b.unbatched:
             cnt = out["counts"][0].tolist()
             self.Hcount, self.Vgcount, self.leapcount = cnt

@@ -1,0 +1,5 @@
+// Funnel, float64: compiled kernel shapes (EPL slots per lane, LPC lanes per chain).  Part 2 of 4: the shape list is split over
+// several translation units only so that they compile in parallel.
+#include "launch.cuh"
+#define S(UNITM, EPL, LPC) HMCB_SHAPE(FunnelModel, HMCB_MODEL_FUNNEL, double, HMCB_F64, UNITM, EPL, LPC)
+S(1, 4, 1) S(1, 50, 1) S(1, 16, 8) S(0, 4, 1) S(0, 10, 1)

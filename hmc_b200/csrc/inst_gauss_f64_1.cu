@@ -1,0 +1,5 @@
+// Dense Gaussian, float64: compiled kernel shapes.  Part 2 of 4: the shape list is split over
+// several translation units only so that they compile in parallel.
+#include "launch.cuh"
+#define S(UNITM, EPL, LPC) HMCB_SHAPE(GaussianModel, HMCB_MODEL_GAUSSIAN, double, HMCB_F64, UNITM, EPL, LPC)
+S(1, 10, 1) S(1, 8, 8) S(1, 4, 32) S(0, 28, 4)

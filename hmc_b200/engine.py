@@ -84,6 +84,7 @@ class Engine:
         self._ws = None          # adhmc scratch
         self._ws_pool = {}       # drhmc scratch, one per concurrent stream slot
         self._streams = None
+        self._host_stage = None  # device staging of drhmc_step_host, kept between calls
         self.device = None
 
     # ------------------------------------------------------------------ set-up
@@ -189,7 +190,7 @@ class Engine:
 
     def drhmc_step(self, q, n_leap, step_size, nprops, stepfactor, p=None, u=None, want_p=True, q_out=None,
                    stage_events=None, want_avec=True, code_out=None, counts_out=None, extra_offset=0, ws_slot=0,
-                   advance=True, convention=0, p_prev=None, alpha=0.0):
+                   advance=True, convention=0, p_prev=None, alpha=0.0, p_out=None, avec_out=None):
         """hmcb_drhmc_step on device tensor q [C,d].  q_out / code_out / counts_out let a
         caller reuse its own output buffers (no allocation inside a timed loop)."""
         m = self._ensure()
@@ -203,9 +204,10 @@ class Engine:
                 ws = self._ws_pool[ws_slot] = torch.empty(need, dtype=torch.uint8, device=self.device)
             q_out = torch.empty_like(q) if q_out is None else q_out
             out = {"q": q_out,
-                   "p": torch.empty_like(q) if want_p else None,
+                   "p": p_out if p_out is not None else (torch.empty_like(q) if want_p else None),
                    "code": torch.empty(C_, dtype=torch.int32, device=self.device) if code_out is None else code_out,
-                   "avec": torch.empty((C_, nprops), dtype=self.dtype, device=self.device) if want_avec else None,
+                   "avec": avec_out if avec_out is not None else
+                   (torch.empty((C_, nprops), dtype=self.dtype, device=self.device) if want_avec else None),
                    "counts": torch.empty((C_, 3), dtype=torch.int32, device=self.device)
                    if counts_out is None else counts_out}
             prob = convention in (_lib.DR_PROB_METROP, _lib.DR_PROB_HASTINGS)
@@ -225,14 +227,16 @@ class Engine:
         out["_keep"] = keep
         return out
 
-    def drhmc_step_host(self, q_host, n_leap, step_size, nprops, stepfactor, want_p=True, n_chunks=8):
-        """One DR transition for chain state living in HOST memory: the batch is cut into
-        chunks of chains that flow H2D copy -> stage kernels -> D2H copy on three streams, so
-        the copy engines (one per direction) and the SMs work at the same time.  Chains are
+    def drhmc_step_host(self, q_host, n_leap, step_size, nprops, stepfactor, want_p=True, n_chunks=8, run_streams=2):
+        """One DR transition for chain state living in HOST memory.  The batch is cut into
+        chunks of chains that flow through three streams -- host-to-device copies, the stage
+        kernels, device-to-host copies -- chained by events, so both copy engines and the SMs
+        work at the same time and the inbound copies run back to back.  The first and last
+        chunk are half-size: the pipeline fills and drains on small pieces.  Chains are
         independent and draws are keyed by global chain id, so the result is bit-identical to
         the one-shot call.  q_host: CPU tensor [C,d] (pinned for full copy speed); returns
-        pinned CPU tensors."""
-        m = self._ensure()
+        pinned CPU tensors.  Device staging for the whole batch is kept between calls."""
+        self._ensure()
         C_, d = q_host.shape
         n_chunks = max(1, min(int(n_chunks), (C_ + 4095) // 4096))
         pin = dict(pin_memory=True)
@@ -241,28 +245,61 @@ class Engine:
                 "code": torch.empty(C_, dtype=torch.int32, **pin),
                 "avec": torch.empty((C_, nprops), dtype=self.dtype, **pin),
                 "counts": torch.empty((C_, 3), dtype=torch.int32, **pin)}
-        if self._streams is None:
-            with torch.cuda.device(self.device):
-                self._streams = [torch.cuda.Stream(device=self.device) for _ in range(3)]
         cur = torch.cuda.current_stream(self.device)
-        bounds = [(i * C_) // n_chunks for i in range(n_chunks + 1)]
+        with torch.cuda.device(self.device):
+            if self._streams is None:
+                self._streams = [torch.cuda.Stream(device=self.device) for _ in range(4)]
+            key = (C_, d, nprops, bool(want_p))
+            if self._host_stage is None or self._host_stage[0] != key:
+                dev = dict(device=self.device)
+                self._host_stage = (key, {
+                    "q_in": torch.empty((C_, d), dtype=self.dtype, **dev),
+                    "q": torch.empty((C_, d), dtype=self.dtype, **dev),
+                    "p": torch.empty((C_, d), dtype=self.dtype, **dev) if want_p else None,
+                    "code": torch.empty(C_, dtype=torch.int32, **dev),
+                    "avec": torch.empty((C_, nprops), dtype=self.dtype, **dev),
+                    "counts": torch.empty((C_, 3), dtype=torch.int32, **dev)})
+        stage = self._host_stage[1]
+        s_in, s_out = self._streams[0], self._streams[1]
+        runs = self._streams[2:2 + max(1, min(2, int(run_streams)))]
+        # chunk boundaries: halves at both ends, equal pieces between
+        if n_chunks >= 3:
+            w = [0.5] + [1.0] * (n_chunks - 1) + [0.5]
+        else:
+            w = [1.0] * n_chunks
+        acc, bounds = 0.0, [0]
+        for x in w:
+            acc += x
+            bounds.append(int(round(C_ * acc / sum(w))))
+        bounds[-1] = C_
         for st in self._streams:
             st.wait_stream(cur)
-        for i in range(n_chunks):
+        for i in range(len(bounds) - 1):
             lo, hi = bounds[i], bounds[i + 1]
             if hi == lo:
                 continue
-            st = self._streams[i % 3]
-            with torch.cuda.stream(st):
-                qd = torch.empty((hi - lo, d), dtype=self.dtype, device=self.device)
-                qd.copy_(q_host[lo:hi], non_blocking=True)
-                out = self.drhmc_step(qd, n_leap, step_size, nprops, stepfactor, want_p=want_p, extra_offset=lo,
-                                      ws_slot=i % 3, advance=False)
+            with torch.cuda.stream(s_in):
+                stage["q_in"][lo:hi].copy_(q_host[lo:hi], non_blocking=True)
+                ev_in = s_in.record_event()
+            # consecutive chunks alternate between two compute streams (each with its own scratch), so the
+            # thin last DR stages of one chunk share the GPU with the first stage of the next
+            s_run = runs[i % len(runs)]
+            with torch.cuda.stream(s_run):
+                s_run.wait_event(ev_in)
+                self.drhmc_step(stage["q_in"][lo:hi], n_leap, step_size, nprops, stepfactor, want_p=want_p,
+                                q_out=stage["q"][lo:hi], p_out=None if not want_p else stage["p"][lo:hi],
+                                code_out=stage["code"][lo:hi], avec_out=stage["avec"][lo:hi],
+                                counts_out=stage["counts"][lo:hi], extra_offset=lo, ws_slot=i % len(runs),
+                                advance=False)
+                ev_run = s_run.record_event()
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(ev_run)
                 for k in ("q", "p", "code", "avec", "counts"):
                     if host[k] is not None:
-                        host[k][lo:hi].copy_(out[k], non_blocking=True)
-        for st in self._streams:
-            st.synchronize()
+                        host[k][lo:hi].copy_(stage[k][lo:hi], non_blocking=True)
+        s_out.synchronize()
+        for s_run in runs:
+            cur.wait_stream(s_run)
         self.iteration += 1
         return host
 

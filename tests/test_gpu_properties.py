@@ -180,3 +180,7 @@ def test_host_pipeline_equals_one_shot_call():
     qa2 = a.step(qa, 8, 0.3, 3, 2.0)[0]
     qb2 = b.step(qb, 8, 0.3, 3, 2.0)[0]
     assert torch.equal(qa2.cpu(), qb2)
+    # without the momentum (what a sample loop needs): same chain, p is None
+    qa3 = a.step(qa2, 8, 0.3, 3, 2.0)[0]
+    qb3, pb3, cb3, _, _ = b.step(qb2, 8, 0.3, 3, 2.0, want_p=False)
+    assert pb3 is None and torch.equal(qa3.cpu(), qb3)

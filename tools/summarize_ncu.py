@@ -17,6 +17,10 @@ def short(name):
     if m:
         mode = {"0": "HMC", "1": "DR stage 0", "2": "DR stage>=1"}[m.group(6)]
         return "hmcb::k_transition<%s,%s,EPL=%s,LPC=%s> [%s]" % (m.group(1), m.group(2), m.group(3), m.group(4), mode)
+    m = re.match(r"hmcb::k_transition_ws<hmcb::(\w+)<(\w+)>, \w+, (?:\(int\))?(\d+), (?:\(int\))?(\d)", name)
+    if m:
+        mode = {"0": "HMC", "1": "DR stage 0"}[m.group(4)]
+        return "hmcb::k_transition_ws<%s,%s,EPL=%s> [%s, warp-specialised]" % (m.group(1), m.group(2), m.group(3), mode)
     name = name.replace("hmcb::lr::", "hmcb::lr::").replace("(bool)", "").replace("(int)", "")
     return re.sub(r"\(.*", "", name)[:100]
 
