@@ -106,4 +106,9 @@ def test_static_scratch_refuses_oversized_batches():
                                         None)
     assert rc == _lib.E_WORKSPACE
     msg = lib.hmcb_last_error().decode()
-    assert str(need) in msg and str(_lib.STATIC_SCRATCH_BYTES) in msg
+    # the message names both byte counts: what this batch needs as one range (hmcb_drhmc_workspace_bytes may
+    # be a little larger: it sizes the multi-stream form of hmcb_drhmc_step) and what the library holds
+    import re
+    stated = [int(x) for x in re.findall(r"\d{6,}", msg)]
+    assert _lib.STATIC_SCRATCH_BYTES in stated
+    assert any(_lib.STATIC_SCRATCH_BYTES < x <= need for x in stated), msg

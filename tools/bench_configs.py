@@ -6,6 +6,8 @@ import argparse
 import os
 import sys
 
+import time
+
 import numpy as np
 import torch
 
@@ -120,6 +122,47 @@ def main():
         grads = float(out["counts"][:, 1].double().sum())
         rows.append(("cfg5 rosenbrock d=%d AdHMC_eps0 ntry=10 Nleap=20" % d, ms, grads / ms * 1e3, grads * fpg / ms * 1e-9,
                      grads * fpg / ms * 1e-9 / peak, float((out["code"] == 1).double().mean())))
+
+        # AdHMC: step size walking inside the trajectory (Nleap=20 in 4 segments of 5, default ratios)
+        aw = adaptivehmc.AdHMC(rm, device=dev, seed=4)
+        steps = aw.get_steps(0.005, 0.2, 10)
+        ms, out = timed(lambda: aw.engine.adhmc_walk_step(q, 4, 5, 0.0, [2 ** -0.5, 2 ** 0.5], [1.0, 1.0], 0.005, 0.2, steps, 1))
+        grads = float(out["counts"][:, 1].double().sum())
+        rows.append(("cfg5 rosenbrock d=%d AdHMC Nleap=20 nleap=5 ntry=10" % d, ms, grads / ms * 1e3, grads * fpg / ms * 1e-9,
+                     grads * fpg / ms * 1e-9 / peak, float((out["code"] == 1).double().mean())))
+
+    # config 5 (iii): dual-averaging warm-up, 200 adaptation transitions with the accept statistic reduced over
+    # all chains every iteration (one host round trip per iteration: this row is latency, not throughput), then
+    # (ii) MALA at a step size adapted the same way to the 0.574 target
+    for d in ((10,) if a.quick else (10, 100)):
+        C = 131072
+        rm = models.Rosenbrock(d)
+        q = (1.0 + 0.1 * torch.randn(C, d, generator=g, dtype=torch.float64)).to(dev)
+        h = algorithms.HMC(rm, device=dev, seed=4)
+        h.step_size = 0.05
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        q1 = h.adapt_stepsize(q, 200, nsamples=0, burnin=0, step_size=0.05, nleap=20)
+        torch.cuda.synchronize()
+        ms = (time.perf_counter() - t0) * 1e3 / 201
+        grads = C * 21
+        out = h.engine.hmc_step(q1, 20, h.step_size, _lib.RULE_ALG, want_p=False)
+        rows.append(("cfg5(iii) rosenbrock d=%d HMC L=20 dual-averaging warm-up, 201 iterations (adapted eps=%.4f)" % (d, h.step_size),
+                     ms, grads / ms * 1e3, grads * 8.5 * d / ms * 1e-9, grads * 8.5 * d / ms * 1e-9 / peak,
+                     float((out["code"] == 1).double().mean())))
+        m = mala.MALA(rm, device=dev, seed=4)
+        da = algorithms.DualAveragingStepSize(0.02, target_accept=0.574)
+        eps, qm = 0.02, q1
+        for it in range(100):
+            o = m.engine.mala_step(qm, eps, n_steps=1)
+            qm = o["q"]
+            eps, eps_avg = da.update(float(o["n_accept"].double().mean()))
+        K = 32
+        ms, out = timed(lambda: m.engine.mala_step(qm, eps_avg, n_steps=K))
+        grads = C * (K + 1)
+        rows.append(("cfg5(ii) rosenbrock d=%d MALA %d fused steps at the dual-averaging eps=%.4f (target 0.574)" % (d, K, eps_avg),
+                     ms, grads / ms * 1e3, grads * 8.5 * d / ms * 1e-9, grads * 8.5 * d / ms * 1e-9 / peak,
+                     float(out["n_accept"].double().mean()) / K))
 
     print("Measured FP64 DFMA peak: %.2f TFLOP/s\n" % peak)
     print(lr_line + "\n")
