@@ -432,6 +432,8 @@ def main():
         run_reference(a)
     else:
         run_hmcb(a)
+    if torch.distributed.is_available() and torch.distributed.is_initialized():
+        torch.distributed.destroy_process_group()
 
 
 if __name__ == "__main__":

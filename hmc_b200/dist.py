@@ -32,7 +32,9 @@ def init_from_env(backend=None):
         lr = int(os.environ.get("LOCAL_RANK", "0"))
         if backend == "nccl":
             torch.cuda.set_device(lr)
-        td.init_process_group(backend=backend)
+            td.init_process_group(backend=backend, device_id=torch.device("cuda", lr))
+        else:
+            td.init_process_group(backend=backend)
     return rank(), world_size(), int(os.environ.get("LOCAL_RANK", "0"))
 
 

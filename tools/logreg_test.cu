@@ -53,6 +53,17 @@ int main(int argc, char** argv) {
   CK(cudaFuncSetAttribute(k_logreg_grad_v1<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemV1));
   CK(cudaFuncSetAttribute(k_logreg_grad_v1<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemV1));
   CK(cudaMemset(dV, 0, (size_t)slabs * C * 8));
+  // optional trace of CTA (0,0): argv[7] = 1
+  const bool want_trace = argc > 7 && atoi(argv[7]) != 0;
+  unsigned long long* dtr = nullptr;
+  const int nb0 = b.blocks_per_slab < nblk ? b.blocks_per_slab : nblk;
+  if (want_trace) {
+    CK(cudaMalloc(&dtr, (size_t)nb0 * 16 * 8));
+    CK(cudaMemset(dtr, 0, (size_t)nb0 * 16 * 8));
+    b.trace = dtr;
+    b.trace_x = argc > 8 ? atoi(argv[8]) : 0;
+    b.trace_y = argc > 9 ? atoi(argv[9]) : 0;
+  }
   cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
   float best = 1e30f;
   for (int r = 0; r < reps; ++r) {
@@ -95,6 +106,21 @@ int main(int argc, char** argv) {
   }
   const double flops = 4.0 * N * (double)kD * C;
   const int nprod = mode == 2 ? 1 : 3;
+  if (want_trace) {
+    std::vector<unsigned long long> tr((size_t)nb0 * 16);
+    cudaMemcpy(tr.data(), dtr, tr.size() * 8, cudaMemcpyDeviceToHost);
+    const unsigned long long t0 = tr[(size_t)8 * 16 + 1];
+    printf("trace of CTA (0,0), cycles relative to block 8's x_full; per block: prod x_empty | mma x_full, G1 issued, p_full seen, G2 issued | "
+           "epi z_full seen, Z loaded, R stored, p_full arrived\n");
+    printf("CTA entry %lld, prologue done %lld, first x_full %lld, first z_full seen %lld, last p_full arrived %lld, G drained %lld, exit %lld\n",
+           (long long)(tr[9] - t0), (long long)(tr[10] - t0), (long long)(tr[1] - t0), (long long)(tr[5] - t0),
+           (long long)(tr[(size_t)(nb0 - 1) * 16 + 8] - t0), (long long)(tr[11] - t0), (long long)(tr[12] - t0));
+    for (int i = 8; i < 12 && i < nb0; ++i) {
+      printf("blk %2d:", i);
+      for (int k = 0; k < 9; ++k) printf(" %7lld", (long long)(tr[(size_t)i * 16 + k] - t0));
+      printf("\n");
+    }
+  }
   printf("mode %d N=%d d=%d C=%d slabs=%d: %.3f ms  algorithmic %.0f TFLOP/s, executed fp16 %.0f TFLOP/s  |G|max %.3g  max abs err %.3g (rel %.3g)  V rel err %.3g\n",
          mode, N, d, C, slabs, best, flops / (best * 1e-3) / 1e12, nprod * flops / (best * 1e-3) / 1e12, gnorm, max_abs,
          max_abs / gnorm, vmax);
