@@ -432,8 +432,9 @@ def main():
         run_reference(a)
     else:
         run_hmcb(a)
-    if torch.distributed.is_available() and torch.distributed.is_initialized():
-        torch.distributed.destroy_process_group()
+    td = sys.modules.get("torch.distributed")
+    if td is not None and td.is_available() and td.is_initialized():
+        td.destroy_process_group()
 
 
 if __name__ == "__main__":
