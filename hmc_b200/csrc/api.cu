@@ -572,6 +572,10 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
   if (S == 1) return run(chains, rng, out, workspace, L[0], st);
   HelperStreams* h;
   if ((rc = helper_streams(&h))) return rc;
+  // the fork/join events are shared by every call on this device: enqueue the whole fork - launch - join sequence
+  // of one call before another host thread's (only the enqueueing is serialised; the work itself is asynchronous)
+  static std::mutex seq_mu;
+  std::lock_guard<std::mutex> seq_lock(seq_mu);
   HMCB_CUDA(cudaEventRecord(h->fork, st));
   char* w = (char*)workspace;
   for (int i = 0; i < S; ++i) {
