@@ -130,16 +130,25 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
     smem = model.p_in_smem ? withP : stage;
   }
 
-  auto prep = [&](auto kernel, int& max_blocks) -> int {
-    if (smem > 48 * 1024) HMCB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  auto prep_smem = [&](auto kernel, int& max_blocks, size_t bytes) -> int {
+    if (bytes > 48 * 1024) HMCB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     int per_sm = 0;
-    HMCB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, THREADS, smem));
+    HMCB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, THREADS, bytes));
     if (per_sm < 1) {
-      set_error("kernel shape EPL=%d LPC=%d does not fit on an SM (smem %zu B)", EPL, LPC, smem);
+      set_error("kernel shape EPL=%d LPC=%d does not fit on an SM (smem %zu B)", EPL, LPC, bytes);
       return HMCB_E_UNSUPPORTED;
     }
     max_blocks = per_sm * sm_count();
     return 0;
+  };
+  auto prep = [&](auto kernel, int& max_blocks) -> int { return prep_smem(kernel, max_blocks, smem); };
+  // per-warp staging tile of the single-trajectory kernels (transition.cuh, warp_tile_copy): one row of d|1
+  // elements per chain of the block; only for row-major state and models that use no shared memory themselves
+  constexpr size_t kTileBytes = GAUSS ? 0 : (size_t)GPB * ((EPL * LPC) | 1) * sizeof(T);
+  // measured on the funnel, 2^20 chains, L=20: d=50 0.81 -> 0.63 ms with the tile, d=10 0.13 -> 0.18 ms without
+  // it paying (a 80-byte row per lane already uses most of every sector it touches), hence the lower bound on d
+  auto use_tile = [&](const TransArgs<T>& a) -> bool {
+    return !GAUSS && a.d >= 24 && a.sd == 1 && a.sc == a.d && !getenv("HMCB_NO_TILE");
   };
   auto grid_for = [&](int64_t items, int max_blocks) -> int {
     int64_t need = (items + GPB - 1) / GPB;
@@ -153,6 +162,7 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
     if ((op == OP_HMC || op == OP_DR0) && !getenv("HMCB_NO_WS")) {
       TransArgs<T>& a = *(TransArgs<T>*)args;
       if (!a.p_inject && !a.p_prev && a.n_chains >= 4096) {
+        a.tile_io = 0;   // measured: the staging tile does not pay in the warp-specialised kernel (L=150: 2.02 -> 2.18 ms)
         const size_t ws_smem = 2 * (size_t)EPL * kWsComputeThreads * sizeof(float) + 64;
         const int grid = (int)((a.n_chains + kWsComputeThreads - 1) / kWsComputeThreads < sm_count()
                                    ? (a.n_chains + kWsComputeThreads - 1) / kWsComputeThreads
@@ -174,16 +184,20 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
   switch (op) {
     case OP_HMC: {
       auto k = k_transition<Model, T, EPL, LPC, UNITM, MODE_HMC, THREADS, MINB>;
-      if ((rc = prep(k, max_blocks))) return rc;
       TransArgs<T>& a = *(TransArgs<T>*)args;
-      k<<<grid_for(a.n_chains, max_blocks), THREADS, smem, st>>>(model, a);
+      a.tile_io = use_tile(a) ? 1 : 0;
+      const size_t bytes = smem + (a.tile_io ? kTileBytes : 0);
+      if ((rc = prep_smem(k, max_blocks, bytes))) return rc;
+      k<<<grid_for(a.n_chains, max_blocks), THREADS, bytes, st>>>(model, a);
       break;
     }
     case OP_DR0: {
       auto k = k_transition<Model, T, EPL, LPC, UNITM, MODE_DR0, THREADS, MINB>;
-      if ((rc = prep(k, max_blocks))) return rc;
       TransArgs<T>& a = *(TransArgs<T>*)args;
-      k<<<grid_for(a.n_chains, max_blocks), THREADS, smem, st>>>(model, a);
+      a.tile_io = use_tile(a) ? 1 : 0;
+      const size_t bytes = smem + (a.tile_io ? kTileBytes : 0);
+      if ((rc = prep_smem(k, max_blocks, bytes))) return rc;
+      k<<<grid_for(a.n_chains, max_blocks), THREADS, bytes, st>>>(model, a);
       break;
     }
     case OP_DRN: {

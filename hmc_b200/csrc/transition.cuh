@@ -60,6 +60,7 @@ struct TransArgs {
   int32_t dr_prob;   // probabilistic DR: 0 off, 1 p_try = 1 - min(1, e^{H0-Hj}), 2 p_try = 1 - alpha_j
   T* ptries_out;     // [n_chains, nprops] or nullptr
   int32_t nprops, stage;
+  int32_t tile_io;   // set by the launcher when the per-warp staging tile was allocated (see warp_tile_load)
   int32_t L[kMaxProps];
   T eps[kMaxProps];
   DrScratch<T> ws;
@@ -244,6 +245,41 @@ __device__ __forceinline__ void leapfrog(const Model& model, T (&q)[EPL], T (&p)
   V_end = model.template kick<EPL, LPC, true>(q, p, T(0.5) * eps, c);
 }
 
+// ------------------------------------------------------------------ coalesced state I/O through a warp tile
+// Row-major [C, d] chain state read lane-per-chain touches 32 different sectors per load instruction
+// (ncu at L = 20: 27 sectors per request, long_scoreboard 3.1 per issue; one transition of 2^20 chains
+// of d = 50 cost 0.51 ms before its first leapfrog step).  The chains of a warp are adjacent rows, so
+// their states are one contiguous run of (32/LPC)*d elements: the warp copies that run with
+// consecutive lanes on consecutive elements into a shared-memory tile (row stride d|1, so that the
+// row-per-lane reads that follow are free of bank conflicts), takes q from there, keeps the tile as
+// q0 for the no-move test, overwrites the rows of accepted chains and writes the run back the same
+// way.  Rows of rejected (or, in DR stage 0, not yet finished) chains go back unchanged.
+template <typename T>
+__device__ __forceinline__ void warp_tile_copy(T* tile, int rs, T* __restrict__ gmem, int d, int n_rows, int wlane, bool to_tile) {
+  // batches of kU independent global accesses per lane: written as load-then-store per element the
+  // compiler kept them in order (it cannot rule out aliasing) and every element paid a full memory latency
+  constexpr int kU = 8;
+  const int ne = n_rows * d;
+  int row = 0, col = wlane;
+  while (col >= d) { col -= d; ++row; }
+  for (int f0 = wlane; f0 < ne; f0 += 32 * kU) {
+    T v[kU];
+    if (to_tile) {
+#pragma unroll
+      for (int u = 0; u < kU; ++u) v[u] = (f0 + 32 * u < ne) ? gmem[f0 + 32 * u] : T(0);
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      if (f0 + 32 * u < ne) {
+        if (to_tile) tile[row * rs + col] = v[u];
+        else gmem[f0 + 32 * u] = tile[row * rs + col];
+      }
+      col += 32;
+      while (col >= d) { col -= d; ++row; }
+    }
+  }
+}
+
 // Everything of a single-trajectory transition (vanilla HMC step, or DR stage 0) after the
 // chain's position q and refreshed momentum p are in registers: energies, trajectory, no-move
 // test, accept rule, outputs, and for DR the hand-over of rejected chains to stage 1.  Shared by
@@ -251,7 +287,9 @@ __device__ __forceinline__ void leapfrog(const Model& model, T (&q)[EPL], T (&p)
 template <class Model, typename T, int EPL, int LPC, bool UNITM, int MODE>
 __device__ __forceinline__ void finish_single(const Model& model, const TransArgs<T>& a, const GroupCtx<T>& c,
                                               const T (&minv)[UNITM ? 1 : EPL], int64_t chain, int64_t qoff,
-                                              T (&q)[EPL], T (&p)[EPL]) {
+                                              T (&q)[EPL], T (&p)[EPL], T* trow = nullptr) {
+  // trow: this chain's row of the warp tile (holds q0; takes the new q on acceptance), or nullptr when
+  // the state is read from and written to global memory directly
   using Lay = Layout<EPL, LPC>;
   const int d = a.d;
   int cH, cVg, cLeap;
@@ -263,7 +301,7 @@ __device__ __forceinline__ void finish_single(const Model& model, const TransArg
     const T H1 = V1 + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
     cH = 2; cVg = N + 1; cLeap = 1;
     // sum(q0 - q1) == 0 is the reference's "did not move" test (src/pyhmc.py:57)
-    T dq = diff_sum<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d);
+    T dq = trow ? diff_sum<T, EPL, LPC>(q, trow, 0, 1, c.lane, d) : diff_sum<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d);
     dq = group_sum_masked<LPC, T>(dq, c.mask);
     T prob = t_exp<T>(H0 - H1);
 
@@ -322,10 +360,11 @@ __device__ __forceinline__ void finish_single(const Model& model, const TransArg
       if (a.counts) { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = cLeap; }
     }
     if (accept) {
-      store_vec<T, EPL, LPC>(q, a.q_out, qoff, a.sd, c.lane, d);
+      if (trow) store_vec<T, EPL, LPC>(q, trow, 0, 1, c.lane, d);
+      else store_vec<T, EPL, LPC>(q, a.q_out, qoff, a.sd, c.lane, d);
       if (a.p_out) store_vec<T, EPL, LPC>(p, a.p_out, qoff, a.sd, c.lane, d);
     } else if (finished) {
-      if (a.q_out != a.q_in) {
+      if (!trow && a.q_out != a.q_in) {
 #pragma unroll
         for (int s = 0; s < EPL; ++s) {
           const int i = Lay::elem(c.lane, s);
@@ -380,6 +419,34 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
   const int64_t count = (MODE == MODE_DRN) ? (int64_t)a.ws.count[a.stage] : a.n_chains;
   const int32_t* list = (MODE == MODE_DRN) ? a.ws.list + (int64_t)a.stage * a.n_chains : nullptr;
   const int J = (MODE == MODE_DRN) ? a.stage : 0;
+
+  if constexpr (MODE != MODE_DRN && !Model::kNeedsSmem) {
+    if (a.tile_io && a.sd == 1 && a.sc == d) {
+      // single-trajectory transition with the state staged through a warp tile (see warp_tile_copy)
+      constexpr int CPW = 32 / LPC;                         // chains per warp
+      const int rs = d | 1;
+      const int wlane = threadIdx.x & 31;
+      T* tile = reinterpret_cast<T*>(smem_raw) + (size_t)(threadIdx.x >> 5) * CPW * ((EPL * LPC) | 1);
+      const int g = wlane / LPC;
+      for (int64_t w0 = (gthread - wlane) / LPC; w0 < count; w0 += total_groups) {
+        const int nv = (int)(count - w0 < CPW ? count - w0 : CPW);
+        warp_tile_copy<T>(tile, rs, const_cast<T*>(a.q_in) + w0 * d, d, nv, wlane, true);
+        __syncwarp();
+        if (g < nv) {
+          const int64_t chain = w0 + g;
+          T q[EPL], p[EPL];
+          T* trow = tile + g * rs;
+          load_vec<T, EPL, LPC>(q, trow, 0, 1, c.lane, d, T(1));
+          draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);
+          finish_single<Model, T, EPL, LPC, UNITM, MODE>(model, a, c, minv, chain, chain * a.sc, q, p, trow);
+        }
+        __syncwarp();
+        warp_tile_copy<T>(tile, rs, a.q_out + w0 * d, d, nv, wlane, false);
+        __syncwarp();
+      }
+      return;
+    }
+  }
 
   for (int64_t item = gthread / LPC; item < count; item += total_groups) {
     const int64_t chain = (MODE == MODE_DRN) ? (int64_t)list[item] : item;
