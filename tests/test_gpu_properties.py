@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 import torch
 
-from hmc_b200 import algorithms, models, pyhmc
+from hmc_b200 import _lib, algorithms, models, pyhmc
 
 pytestmark = pytest.mark.gpu
 
@@ -184,3 +184,36 @@ def test_host_pipeline_equals_one_shot_call():
     qa3 = a.step(qa2, 8, 0.3, 3, 2.0)[0]
     qb3, pb3, cb3, _, _ = b.step(qb2, 8, 0.3, 3, 2.0, want_p=False)
     assert pb3 is None and torch.equal(qa3.cpu(), qb3)
+
+
+@pytest.mark.parametrize("d,C", [(50, 4097), (26, 1000), (100, 777)])
+def test_state_io_paths_agree_and_work_in_place(d, C, monkeypatch):
+    """The single-trajectory kernels read and write row-major chain state either lane-per-row or
+    through a per-warp shared-memory tile (coalesced), and the thread-per-chain float64 shapes have a
+    warp-specialised form: same transition, same draws -> identical results, also when q_out is q_in
+    and on a ragged last warp."""
+    dev = _dev()
+    q0 = _exact_funnel(C, d, 5, dev)
+    outs = []
+    for env in ({}, {"HMCB_NO_TILE": "1"}, {"HMCB_NO_WS": "1"}, {"HMCB_NO_WS": "1", "HMCB_NO_TILE": "1"}):
+        for k in ("HMCB_NO_TILE", "HMCB_NO_WS"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        s = pyhmc.HMC(models.Funnel(d), device=dev, seed=9)
+        o = s.engine.hmc_step(q0, 7, 0.25, _lib.RULE_PYHMC)
+        outs.append((o["q"].clone(), o["p"].clone(), o["code"].clone()))
+        # in place
+        s2 = pyhmc.HMC(models.Funnel(d), device=dev, seed=9)
+        qi = q0.clone()
+        o2 = s2.engine.hmc_step(qi, 7, 0.25, _lib.RULE_PYHMC, q_out=qi)
+        assert torch.equal(qi, o["q"]) and torch.equal(o2["code"], o["code"])
+        # delayed rejection, stage 0 through the same paths
+        dr = algorithms.DRHMC(models.Funnel(d), device=dev, seed=9)
+        od = dr.engine.drhmc_step(q0, 7, 0.6, 3, 2.0)
+        outs[-1] += (od["q"].clone(), od["code"].clone(), od["counts"].clone())
+    for o in outs[1:]:
+        for a, b in zip(outs[0], o):
+            assert torch.equal(a, b)
+    codes = outs[0][2]
+    assert (codes == 1).any() and (codes != 1).any()         # accepted and rejected rows both went through the tile
