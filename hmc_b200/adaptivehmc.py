@@ -38,6 +38,48 @@ class AdHMC_eps0(HMC):
             return np.logspace(np.log10(smin), np.log10(smax), ntry)
         return np.linspace(smin, smax, ntry)
 
+    def get_stepsize(self, q0, p0, smin=0.01, smax=1.0, ntry=20, logspace=True, nsteps=1, eps=None, u=None):
+        """The step-size distribution on its own (src/adaptivehmc.py:111-134; the same method in AdHMC
+        :202-224 and AdHMC_tint :368-390): ntry trial trajectories of nsteps steps from (q0, p0), weights
+        exp(H0 - H_i) sqrt(eps_i) normalised to pp.  Without ``eps`` it draws a step size -- a bin from the
+        CDF, then uniformly inside the bin -- and returns (step size, pp[bin + 1]); with ``eps`` it returns
+        the probability of the bin above eps.  Batched over chains; ``u`` [C, 2] injects the two uniforms
+        (else torch's generator on the device is used).  hmc_step does all of this inside one kernel;
+        this method is ntry leapfrog launches and exists for callers that use it directly."""
+        e = self.engine
+        bq = Batch(q0, e.dev, e.dtype)
+        bp = Batch(p0, e.dev, e.dtype)
+        e.check_dim(bq)
+        steps = self.get_steps(smin, smax, ntry, logspace)
+        H0 = self.H(bq.q, bp.q)
+        Hs = []
+        for ss in steps:
+            q1, p1 = self.leapfrog(bq.q, bp.q, nsteps, float(ss))
+            Hs.append(self.H(q1, p1))
+        Hs = torch.stack(Hs, dim=1)                                            # [C, ntry]
+        st = torch.as_tensor(steps, dtype=torch.float64, device=Hs.device)
+        pp = torch.exp(H0.double()[:, None] - Hs.double()) * st ** 0.5
+        pp = torch.where(torch.isnan(pp) | torch.isinf(pp), torch.zeros_like(pp), pp)
+        pp = pp / pp.sum(dim=1, keepdim=True)
+        if eps is not None:
+            epst = torch.as_tensor(eps, dtype=torch.float64, device=pp.device).reshape(-1, 1).expand(pp.shape[0], 1)
+            j = (st[None, :] > epst).to(torch.int8).argmax(dim=1)              # first bin edge above eps
+            return bq.out(pp.gather(1, j[:, None])[:, 0])
+        cdf = torch.cumsum(pp, dim=1)
+        if u is None:
+            ut = torch.rand((pp.shape[0], 2), dtype=torch.float64, device=pp.device)
+        else:
+            ut = torch.as_tensor(np.asarray(u, dtype=np.float64) if not torch.is_tensor(u) else u).to(pp.device).reshape(-1, 2)
+        lo = cdf.min(dim=1).values
+        sx = lo + (1.0 - lo) * ut[:, 0]
+        above = sx[:, None] > cdf                                              # isx = last index with sx > cdf
+        isx = (above.to(torch.int64) * torch.arange(ntry, device=pp.device)[None, :]).max(dim=1).values
+        if bool(((~above.any(dim=1)) | (isx > ntry - 2)).any()):
+            raise IndexError("get_stepsize: no bin below the draw (all trial weights NaN, or the draw fell in the "
+                             "last bin); the reference raises here too")
+        sx2 = st[isx] + (st[isx + 1] - st[isx]) * ut[:, 1]
+        return bq.out(sx2), bq.out(pp.gather(1, (isx + 1)[:, None])[:, 0])
+
     def hmc_step(self, q0, Nleap, smin=0.01, smax=1.0, Tint=0, ntry=10, nsteps=1, p=None, u=None):
         if (Tint == 0) and (Nleap == 0):
             raise ValueError("Tint and Nleap cannot be both zeros")

@@ -157,3 +157,25 @@ def test_adhmc_vs_oracle_fresh_and_stationarity():
         q = s2.hmc_step(q, 10, smin=0.01, smax=0.5, ntry=8, nsteps=1)[0]
     assert abs(q[:, 0].mean().item()) < 6 * 3.0 / np.sqrt(C2)
     assert abs(q[:, 0].std().item() - 3.0) < 0.1
+
+
+def test_get_stepsize_standalone_vs_oracle():
+    """AdHMC_eps0.get_stepsize used on its own (src/adaptivehmc.py:111-134), both of its modes."""
+    dev = _dev()
+    d, C, ntry = 10, 29, 8
+    pm, om = _models(dict(kind="funnel", d=d))
+    rng = np.random.default_rng(12)
+    q0 = rng.uniform(-1, 1, (C, d))
+    p0 = rng.standard_normal((C, d))
+    U = rng.random((C, 2))
+    s = adaptivehmc.AdHMC_eps0(pm, device=dev)
+    ss, prob = s.get_stepsize(q0, p0, smin=0.02, smax=0.6, ntry=ntry, nsteps=2, u=U)
+    pe = s.get_stepsize(q0, p0, smin=0.02, smax=0.6, ntry=ntry, nsteps=2, eps=0.1)
+    for c in range(C):
+        kin, cnt = samplers.Kinetics(None), samplers.Counters()
+        steps, pp, cdf = samplers._eps0_trials(om, kin, q0[c], p0[c], 0.02, 0.6, ntry, 2, cnt)
+        sx = cdf.min() + (1.0 - cdf.min()) * U[c, 0]
+        isx = np.where(sx > cdf)[0][-1]
+        want = steps[isx] + (steps[isx + 1] - steps[isx]) * U[c, 1]
+        assert np.isclose(ss[c], want, rtol=1e-12) and np.isclose(prob[c], pp[isx + 1], rtol=1e-9)
+        assert np.isclose(pe[c], pp[np.where(steps > 0.1)[0][0]], rtol=1e-9)
