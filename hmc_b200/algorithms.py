@@ -112,6 +112,37 @@ class HMC(_PyHMCBase):
         """One transition per chain (src/algorithms.py:192-198)."""
         return self._step(q, nleap, step_size, p=p, u=u)
 
+    def V_vandg(self, x):
+        """(V, grad V) from one evaluation (src/algorithms.py:109-115)."""
+        b = self._device_q(x)
+        self.Vgcount += 1
+        logp, g = self.engine.logp_grad(b.q)
+        return b.out(-logp), b.out(-g)
+
+    def leapfrog_Vgq(self, q, p, N, step_size, V_q=None, V_gq=None):
+        """Leapfrog trajectory that may reuse a cached gradient for its first half kick and returns the
+        potential and gradient at its end point for the next one (src/algorithms.py:150-172):
+        (q1, p1, V(q1), grad V(q1)).  The fused kernel always evaluates its first gradient itself, so a
+        supplied V_gq enters as the difference to it (identical when V_gq is grad V(q), as in every use
+        the reference makes of it); the counters follow the reference (N gradients with a cache, N+1
+        without)."""
+        self.leapcount += 1
+        e = self.engine
+        bq = self._device_q(q)
+        bp = Batch(p, e.dev, e.dtype)
+        pd = bp.q
+        n = max(int(N), 1)
+        if V_gq is not None:
+            g = Batch(V_gq, e.dev, e.dtype).q
+            _, gl = e.logp_grad(bq.q)
+            pd = pd - 0.5 * step_size * g - 0.5 * step_size * gl     # gl = -grad V(q)
+            self.Vgcount += n
+        else:
+            self.Vgcount += n + 1
+        q1, p1 = e.leapfrog(bq.q, pd, N, step_size)
+        logp, g1 = e.logp_grad(q1)
+        return bq.out(q1), bq.out(p1), bq.out(-logp), bq.out(-g1)
+
     def _parse_kwargs_sample(self, **kwargs):
         self.nsamples = kwargs["nsamples"]
         self.burnin = kwargs["burnin"]

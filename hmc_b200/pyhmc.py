@@ -58,6 +58,14 @@ class HMC:
         m = self._minv()
         return b.out(b.q if m is None else b.q * m)
 
+    def unit_norm_KE(self, p):
+        """0.5 * sum(p**2) whatever the metric (src/pyhmc.py:24-25)."""
+        b = Batch(p, self.engine.dev, self.engine.dtype)
+        return b.out(0.5 * (b.q * b.q).sum(dim=1))
+
+    def unit_norm_KE_g(self, p):
+        return p
+
     def H(self, q, p):
         self.Hcount += 1
         bq = Batch(q, self.engine.dev, self.engine.dtype)

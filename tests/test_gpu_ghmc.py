@@ -116,3 +116,34 @@ def test_ghmc_sample_keeps_the_gaussian_invariant():
         q = st.samples[-1]
         assert abs(q.mean().item()) < 0.03, name
         assert abs(q.std(dim=0).mean().item() - 1.0) < 0.03, name
+
+
+def test_leapfrog_Vgq_and_V_vandg_standalone():
+    """algorithms.HMC.leapfrog_Vgq / V_vandg called on their own (src/algorithms.py:109-115,150-172)."""
+    import torch
+    from hmc_b200 import algorithms, models
+    from oracle import models as omodels
+    from oracle import samplers
+    dev = torch.device("cuda:0")
+    d, C, N, eps = 12, 17, 9, 0.07
+    pm, om = models.Rosenbrock(d), omodels.Rosenbrock(d)
+    rng = np.random.default_rng(4)
+    q0 = 1.0 + 0.1 * rng.standard_normal((C, d))
+    p0 = rng.standard_normal((C, d))
+    s = algorithms.HMC(pm, device=dev)
+    V, Vg = s.V_vandg(q0)
+    for c in range(C):
+        v, g = om.log_prob_and_grad(q0[c])
+        assert np.isclose(V[c], -v, rtol=1e-12) and np.allclose(Vg[c], -g, rtol=1e-12, atol=1e-13)
+    s.Vgcount = s.leapcount = 0
+    out_cached = s.leapfrog_Vgq(q0, p0, N, eps, V, Vg)
+    assert s.Vgcount == N and s.leapcount == 1
+    out_plain = s.leapfrog_Vgq(q0, p0, N, eps)
+    assert s.Vgcount == 2 * N + 1
+    for c in range(C):
+        kin, cnt = samplers.Kinetics(None), samplers.Counters()
+        ref = samplers._leapfrog_Vgq(om, kin, q0[c], p0[c], N, eps, cnt, -om.log_prob(q0[c]), -om.grad_log_prob(q0[c]))
+        for out in (out_cached, out_plain):
+            for a, b in zip(out, ref):
+                assert np.allclose(np.asarray(a[c], dtype=float), np.asarray(b, dtype=float), rtol=1e-10, atol=1e-11)
+    assert np.array_equal(s.unit_norm_KE(p0), 0.5 * (p0 ** 2).sum(axis=1)) or np.allclose(s.unit_norm_KE(p0), 0.5 * (p0 ** 2).sum(axis=1), rtol=1e-14)
