@@ -3,6 +3,12 @@
 // helper warpgroup (128 threads, 32 registers) that generates the NEXT round's momenta into a
 // double-buffered shared-memory tile while the compute warps integrate, so the compute warps'
 // per-transition prologue no longer contains the random-number generation.
+#ifndef KB_TILE_STORE
+#define KB_TILE_STORE 0
+#endif
+#ifndef KB_HELPER_ILP
+#define KB_HELPER_ILP 1
+#endif
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -16,6 +22,11 @@ int cuda_fail(cudaError_t e, const char* what) { fprintf(stderr, "CUDA %s at %s\
 int sm_count() { return 148; }
 int max_optin_smem() { return 232448; }
 std::vector<Entry>& registry() { static std::vector<Entry> r; return r; }
+
+// clock64 stamps of block 0 (development aid): 8 per round --
+// helper warp 8: empty seen, momenta written | compute warp 0: q loaded, full seen, p read, trajectory done, outputs done
+__device__ unsigned long long* g_trace = nullptr;
+#define WS_TRACE(slot, r) do { if (g_trace && blockIdx.x == 0 && (threadIdx.x & 31) == 0) g_trace[(size_t)(r) * 8 + (slot)] = clock64(); } while (0)
 
 template <int EPL>
 __global__ void __launch_bounds__(384, 1) k_hmc_ws(const FunnelModel<double> model, const TransArgs<double> a) {
@@ -38,7 +49,32 @@ __global__ void __launch_bounds__(384, 1) k_hmc_ws(const FunnelModel<double> mod
     for (int r = 0; r < rounds; ++r) {
       const int s = r & 1;
       lr::mbar_wait(empty + s, ((r >> 1) & 1) ^ 1);
+      if (tid == 256) WS_TRACE(0, r);
       float* dst = sP + (size_t)s * EPL * 256;
+#if KB_HELPER_ILP == 2
+      {
+        const int64_t chain0 = ((int64_t)r * gridDim.x + blockIdx.x) * 256 + ht;
+        const uint64_t g0 = (uint64_t)(a.chain_offset + chain0);
+        if (chain0 < a.n_chains) {
+          const bool live1 = chain0 + 128 < a.n_chains;
+#pragma unroll 1
+          for (int b = 0; b < (EPL + 3) / 4; ++b) {
+            uint32_t w0[4], w1[4];
+            float z0[4], z1[4];
+            Philox::gen(a.seed, g0, a.iteration, STREAM_MOMENTUM, (uint32_t)b, w0);
+            Philox::gen(a.seed, g0 + 128, a.iteration, STREAM_MOMENTUM, (uint32_t)b, w1);
+            normal4_f32(w0, z0);
+            normal4_f32(w1, z1);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              if (4 * b + k < EPL) {
+                dst[(4 * b + k) * 256 + ht] = (4 * b + k < d) ? z0[k] : 0.f;
+                if (live1) dst[(4 * b + k) * 256 + ht + 128] = (4 * b + k < d) ? z1[k] : 0.f;
+              }
+          }
+        }
+      }
+#else
 #pragma unroll 1
       for (int h = 0; h < 2; ++h) {
         const int c = ht + 128 * h;
@@ -57,6 +93,8 @@ __global__ void __launch_bounds__(384, 1) k_hmc_ws(const FunnelModel<double> mod
           }
         }
       }
+#endif
+      if (tid == 256) WS_TRACE(1, r);
       lr::mbar_arrive(full + s);
     }
   } else {
@@ -64,6 +102,9 @@ __global__ void __launch_bounds__(384, 1) k_hmc_ws(const FunnelModel<double> mod
     GroupCtx<double> c;
     c.lane = 0; c.d = d; c.mask = 0xffffffffu; c.smem_q = nullptr;
     double minv[1] = {1.0};
+#if KB_TILE_STORE
+    double* tile = reinterpret_cast<double*>(smem_raw + 2 * EPL * 256 * 4 + 64) + (size_t)(tid >> 5) * 32 * (EPL | 1);
+#endif
     for (int r = 0; r < rounds; ++r) {
       const int s = r & 1;
       const int64_t chain = ((int64_t)r * gridDim.x + blockIdx.x) * 256 + tid;
@@ -71,18 +112,22 @@ __global__ void __launch_bounds__(384, 1) k_hmc_ws(const FunnelModel<double> mod
       const int64_t qoff = (live ? chain : 0) * a.sc;
       double q[EPL], p[EPL];
       load_vec<double, EPL, 1>(q, a.q_in, qoff, a.sd, 0, d, 1.0);
+      if (tid == 0) { double sink = 0; for (int k = 0; k < EPL; ++k) sink += q[k]; if (sink == 1.2345e300) g_trace[7] = 1; WS_TRACE(2, r); }
       lr::mbar_wait(full + s, (r >> 1) & 1);
+      if (tid == 0) WS_TRACE(3, r);
       const float* src = sP + (size_t)s * EPL * 256 + tid;
 #pragma unroll
       for (int k = 0; k < EPL; ++k) p[k] = (double)src[k * 256];
       lr::mbar_arrive(empty + s);
-      if (!live) continue;
+      if (tid == 0) WS_TRACE(4, r);
+      if (live) {
       const double K0 = kinetic<double, EPL, 1, true>(p, minv, c.mask);
       double V0, V1;
       const int N = a.L[0] > 1 ? a.L[0] : 1;
       leapfrog<FunnelModel<double>, double, EPL, 1, true>(model, q, p, minv, N, a.eps[0], c, V0, V1);
       const double H0 = V0 + K0;
       const double H1 = V1 + kinetic<double, EPL, 1, true>(p, minv, c.mask);
+      if (tid == 0) WS_TRACE(5, r);
       const double dq = diff_sum<double, EPL, 1>(q, a.q_in, qoff, a.sd, 0, d);
       const double prob = exp(H0 - H1);
       const bool bad = t_bad(prob) || dq == 0.0;
@@ -90,12 +135,42 @@ __global__ void __launch_bounds__(384, 1) k_hmc_ws(const FunnelModel<double> mod
       const double pm = prob < 1.0 ? prob : 1.0;
       const bool accept = !bad && !(u > pm);
       if (a.code) a.code[chain] = bad ? 2 : (accept ? 1 : 0);
+#if KB_TILE_STORE
+      // rows go to the warp's tile (q1 if accepted, q0 again otherwise) and out of it coalesced
+      {
+        double* trow = tile + (tid & 31) * (EPL | 1);
+        if (!accept) load_vec<double, EPL, 1>(q, a.q_in, qoff, a.sd, 0, d, 1.0);
+#pragma unroll
+        for (int k = 0; k < EPL; ++k) trow[k] = q[k];
+      }
+#else
       if (accept) {
         store_vec<double, EPL, 1>(q, a.q_out, qoff, a.sd, 0, d);
       } else if (a.q_out != a.q_in) {
         load_vec<double, EPL, 1>(q, a.q_in, qoff, a.sd, 0, d, 1.0);
         store_vec<double, EPL, 1>(q, a.q_out, qoff, a.sd, 0, d);
       }
+#endif
+      }   // live
+#if KB_TILE_STORE
+      {
+        __syncwarp();
+        const int wl = tid & 31;
+        const int64_t w0 = chain - wl;
+        const int nv = (int)(a.n_chains - w0 < 32 ? (a.n_chains - w0 > 0 ? a.n_chains - w0 : 0) : 32);
+        double* dstg = a.q_out + w0 * d;
+        constexpr int RS = EPL | 1;
+        int row = 0, col = wl;
+        while (col >= d) { col -= d; ++row; }
+        for (int f = wl; f < nv * d; f += 32) {
+          dstg[f] = tile[row * RS + col];
+          col += 32;
+          while (col >= d) { col -= d; ++row; }
+        }
+        __syncwarp();
+      }
+#endif
+      if (tid == 0) WS_TRACE(6, r);
     }
   }
 }
@@ -118,7 +193,11 @@ int main(int argc, char** argv) {
   auto model = FunnelModel<double>::make(hm);
   TransArgs<double> a{};
   a.n_chains = C; a.d = d; a.q_in = q; a.q_out = qo; a.sc = d; a.sd = 1; a.seed = 1; a.nprops = 1; a.L[0] = L; a.eps[0] = 0.05; a.code = code;
+#if KB_TILE_STORE
+  const size_t smem = 2 * EPL * 256 * 4 + 64 + 256 * (EPL | 1) * 8;
+#else
   const size_t smem = 2 * EPL * 256 * 4 + 64;
+#endif
   auto k = k_hmc_ws<EPL>;
   cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   cudaFuncAttributes fa; cudaFuncGetAttributes(&fa, k);
@@ -131,6 +210,22 @@ int main(int argc, char** argv) {
     k<<<grid, 384, smem>>>(model, a);
     cudaEventRecord(e1); cudaEventSynchronize(e1);
     float ms; cudaEventElapsedTime(&ms, e0, e1); if (r && ms < best) best = ms;
+  }
+  if (argc > 3 && atoi(argv[3])) {
+    unsigned long long* dtr; cudaMalloc(&dtr, 64 * 8 * 8); cudaMemset(dtr, 0, 64 * 8 * 8);
+    cudaMemcpyToSymbol(g_trace, &dtr, sizeof(dtr));
+    a.iteration = 9;
+    k<<<grid, 384, smem>>>(model, a);
+    cudaDeviceSynchronize();
+    std::vector<unsigned long long> tr(64 * 8);
+    cudaMemcpy(tr.data(), dtr, tr.size() * 8, cudaMemcpyDeviceToHost);
+    const unsigned long long t0 = tr[2];
+    printf("round: helper[empty seen, written] compute[q loaded, full seen, p read, trajectory done, outputs done]  (cycles from round 0's q load)\n");
+    for (int r = 0; r < 8; ++r) {
+      printf("r%d:", r);
+      for (int k = 0; k < 7; ++k) printf(" %8lld", (long long)(tr[r * 8 + k] - t0));
+      printf("\n");
+    }
   }
   cudaError_t err = cudaDeviceSynchronize();
   std::vector<int> hc(C);
