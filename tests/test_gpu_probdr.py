@@ -118,3 +118,22 @@ def test_needs_enough_injected_uniforms():
     q0 = np.zeros((3, 10))
     with pytest.raises(ValueError):
         s.multi_step(3, q0, 5, 0.1, 2.0, p=np.zeros((3, 10)), u=np.zeros((3, 3)))
+
+
+@pytest.mark.parametrize("cls", [algorithms.Prob_DRHMC_Metrop, algorithms.Prob_DRHMC_Hastings])
+def test_production_path_keeps_the_funnel_marginal(cls):
+    """With the library's own draws (Philox: u_acc and u_try from one stream, consumption order as the
+    reference), exact funnel samples stay funnel samples."""
+    dev = _dev()
+    d, C = 10, 1 << 15
+    g = torch.Generator().manual_seed(11)
+    v = 3.0 * torch.randn(C, 1, generator=g, dtype=torch.float64)
+    q = torch.cat([v, torch.exp(v / 2) * torch.randn(C, d - 1, generator=g, dtype=torch.float64)], dim=1).to(dev)
+    s = cls(models.Funnel(d), device=dev, seed=5)
+    seen = set()
+    for _ in range(30):
+        q, p, code, avec, counts, ptries = s.multi_step(3, q, 8, 0.5, 2.0)
+        seen |= set(torch.unique(code).tolist())
+    assert {-2, -1, 0, 1, 2} <= seen
+    assert abs(q[:, 0].mean().item()) < 5 * 3.0 / np.sqrt(C)
+    assert abs(q[:, 0].std().item() - 3.0) < 0.08
