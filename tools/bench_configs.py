@@ -99,6 +99,32 @@ def main():
         rows.append(("funnel d=50 HMC L=%d, 2^20 chains" % L, ms, grads / ms * 1e3, grads * 7 * d / ms * 1e-9, grads * 7 * d / ms * 1e-9 / peak,
                      float((out["code"] == 1).double().mean())))
 
+    # the other sampler families on the funnel (d=50, 2^20 chains, light variant nleap=20, eps=0.1): every one is a
+    # call of the class's own engine entry point; work is the kernel's own Vgcount
+    d, C = 50, 1 << 20
+    fm = models.Funnel(d)
+    q = (torch.rand(C, d, generator=g, dtype=torch.float64) * 2 - 1).to(dev)
+    for name, conv in (("DRHMC nprops=3", _lib.DR_ALGORITHMS), ("PyHMC_multistep m=3", _lib.DR_MULTISTEP),
+                       ("Prob_DRHMC_Metrop m=3", _lib.DR_PROB_METROP), ("Prob_DRHMC_Hastings m=3", _lib.DR_PROB_HASTINGS)):
+        dr = algorithms.DRHMC(fm, device=dev, seed=1)
+        ms, out = timed(lambda: dr.engine.drhmc_step(q, 20, 0.1, 3, 2.0, want_p=False, convention=conv))
+        grads = float(out["counts"][:, 1].double().sum())
+        ok = (out["code"] >= 1) if conv == _lib.DR_ALGORITHMS else (out["code"] >= 0)
+        rows.append(("funnel d=50 %s nleap=20, 2^20 chains" % name, ms, grads / ms * 1e3, grads * 7 * d / ms * 1e-9,
+                     grads * 7 * d / ms * 1e-9 / peak, float(ok.double().mean())))
+    gh = algorithms.GHMC(fm, device=dev, seed=1)
+    pprev = torch.randn(C, d, generator=g, dtype=torch.float64).to(dev)
+    o0 = gh.engine.ghmc_step(q, pprev, 20, 0.1, 0.5)
+    ms, out = timed(lambda: gh.engine.ghmc_step(o0["q"], o0["p"], 20, 0.1, 0.5, V=o0["V"], Vg=o0["Vg"]))
+    grads = float(out["counts"][:, 1].double().sum())
+    rows.append(("funnel d=50 GHMC alpha=0.5 nleap=20 (cached V, grad V), 2^20 chains", ms, grads / ms * 1e3, grads * 7 * d / ms * 1e-9,
+                 grads * 7 * d / ms * 1e-9 / peak, float((out["code"] == 1).double().mean())))
+    drg = algorithms.DRGHMC(fm, device=dev, seed=1)
+    ms, out = timed(lambda: drg.engine.drhmc_step(q, 20, 0.1, 3, 2.0, want_p=True, p_prev=pprev, alpha=0.5))
+    grads = float(out["counts"][:, 1].double().sum())
+    rows.append(("funnel d=50 DRGHMC alpha=0.5 nprops=3 nleap=20, 2^20 chains", ms, grads / ms * 1e3, grads * 7 * d / ms * 1e-9,
+                 grads * 7 * d / ms * 1e-9 / peak, float((out["code"] >= 1).double().mean())))
+
     # config 5: Rosenbrock sweep, 131,072 chains: HMC L=20, MALA (32 fused steps), AdHMC_eps0
     for d in ((2, 10, 100) if a.quick else (2, 4, 10, 20, 50, 100)):
         C = 131072
