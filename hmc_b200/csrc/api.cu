@@ -57,16 +57,18 @@ std::vector<Entry>& registry() {
   return r;
 }
 
-const Entry* choose_entry(const hmcb_model& hm, int max_epl) {
+static const Entry* choose_entry_lanes(const hmcb_model& hm, int max_epl, int min_lpc) {
   const int unitm = hm.invmetric_diag ? 0 : 1;
   int force_lpc = 0;
   if (const char* e = getenv("HMCB_LPC")) force_lpc = atoi(e);
   const Entry* best = nullptr;
   long best_cost = 0;
+  // pass 0: the caller's wishes (forced or minimum lanes per chain); pass 1: any shape that holds d
   for (int pass = 0; pass < 2 && !best; ++pass) {
     for (const Entry& e : registry()) {
       if (e.kind != hm.kind || e.dtype != hm.dtype || e.unitm != unitm) continue;
       if (pass == 0 && force_lpc && e.lpc != force_lpc) continue;
+      if (pass == 0 && !force_lpc && e.lpc < min_lpc) continue;
       if (slots_needed(hm.d, e.lpc) > e.epl || e.epl > max_epl) continue;
       if (hm.kind == HMCB_MODEL_ROSENBROCK && (e.epl & 1)) continue;
       // least padded slots first, then fewest lanes per chain
@@ -76,13 +78,15 @@ const Entry* choose_entry(const hmcb_model& hm, int max_epl) {
         best_cost = cost;
       }
     }
-    if (!force_lpc) break;
+    if (!force_lpc && min_lpc <= 1) break;
   }
   if (!best)
     set_error("no compiled kernel shape for model kind %d, dtype %d, d=%d, %s metric", hm.kind, hm.dtype, hm.d,
               unitm ? "unit" : "diagonal");
   return best;
 }
+
+const Entry* choose_entry(const hmcb_model& hm, int max_epl) { return choose_entry_lanes(hm, max_epl, 1); }
 
 static int check_model(const hmcb_model* m) {
   HMCB_CHECK_ARG(m != nullptr, "model is NULL");
@@ -663,7 +667,10 @@ int hmcb_ghmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmc
   HMCB_CHECK_ARG(n_leap >= 0, "n_leap must be >= 0");
   HMCB_CHECK_ARG(!rng->p_prev || (rng->alpha >= -1.0 && rng->alpha <= 1.0), "alpha must be in [-1, 1]");
   if (chains->n_chains == 0) return 0;
-  const Entry* e = choose_entry(*model, kGhmcMaxEpl);
+  // GHMC moves six state arrays per transition (q, p and the cached gradient, in and out): it is bound by
+  // memory, and lanes of a chain that sit side by side read whole lines.  Measured on the d=50 funnel, 2^20
+  // chains, nleap=20: 1.61 ms with 2 lanes per chain, 1.34 ms with 4; nleap=1: 1.01 / 0.77 ms.
+  const Entry* e = choose_entry_lanes(*model, kGhmcMaxEpl, model->d >= 32 ? 4 : 1);
   if (!e) return HMCB_E_UNSUPPORTED;
   cudaStream_t st = (cudaStream_t)stream;
   if (model->dtype == HMCB_F64) return ghmc_step_t<double>(e, model, chains, rng, n_leap, step_size, io, st);
