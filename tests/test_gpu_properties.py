@@ -217,3 +217,30 @@ def test_state_io_paths_agree_and_work_in_place(d, C, monkeypatch):
             assert torch.equal(a, b)
     codes = outs[0][2]
     assert (codes == 1).any() and (codes != 1).any()         # accepted and rejected rows both went through the tile
+
+
+@pytest.mark.parametrize("d", [10, 50])
+def test_structure_of_arrays_state_gives_the_same_transitions(d):
+    """The C ABI addresses chain state through (stride_chain, stride_dim): a [d][C] structure-of-arrays
+    buffer, seen as a [C, d] view with strides (1, C), goes through the same kernels as row-major state
+    and must give the same chains (vanilla step and all delayed-rejection stages)."""
+    dev = _dev()
+    C = 5000
+    q0 = _exact_funnel(C, d, 6, dev)
+    soa = q0.t().contiguous()                    # [d, C]
+    qs = soa.t()                                  # [C, d] view, strides (1, C)
+    assert qs.stride() == (1, C)
+    a = pyhmc.HMC(models.Funnel(d), device=dev, seed=4)
+    b = pyhmc.HMC(models.Funnel(d), device=dev, seed=4)
+    oa = a.engine.hmc_step(q0, 9, 0.2, _lib.RULE_PYHMC)
+    ob = b.engine.hmc_step(qs, 9, 0.2, _lib.RULE_PYHMC)
+    assert ob["q"].stride() == (1, C)
+    for k in ("q", "p", "code", "counts"):
+        assert torch.equal(oa[k], ob[k]), k
+    da = algorithms.DRHMC(models.Funnel(d), device=dev, seed=4)
+    db = algorithms.DRHMC(models.Funnel(d), device=dev, seed=4)
+    ra = da.engine.drhmc_step(q0, 9, 0.6, 3, 2.0)
+    rb = db.engine.drhmc_step(qs, 9, 0.6, 3, 2.0)
+    for k in ("q", "p", "code", "avec", "counts"):
+        assert torch.equal(ra[k], rb[k]), k
+    assert len(torch.unique(ra["code"])) >= 3                 # later stages ran too
