@@ -418,7 +418,10 @@ def run_hmcb(a):
             "grad_evals_per_transition": grads / (K * n_total), "accept_rate": float(stats[-1]) / n_total,
             "code_fractions": {"note": "rank 0: fraction of chain-transitions by DRHMC code (0 = rejected at every "
                                "stage, j+1 = accepted at stage j)", "by_code": code_frac},
-            "rhat_max": float(rhat.max()), "v_mean": float(mean[0]), "v_std": float(std[0]),
+            "rhat_max": float(rhat.max()),
+            "rhat_note": "R-hat (between- over within-chain variance, all-reduced moments) over the %d timed transitions "
+                         "only: with windows that short it mostly says how far a chain moves in %d transitions of the "
+                         "funnel, not whether the ensemble has converged" % (K, K), "v_mean": float(mean[0]), "v_std": float(std[0]),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks.summary(t_wall0, t_wall1),
             "gpu_launches": K * (n_split * a.nprops + 1),
             "gpu_launches_note": "per step: %d chain ranges x %d DR stage kernels + 1 moments kernel (all libhmcb.so)"
