@@ -229,8 +229,9 @@ class Engine:
 
     def drhmc_step_host(self, q_host, n_leap, step_size, nprops, stepfactor, want_p=True, n_chunks=8, run_streams=2):
         """One DR transition for chain state living in HOST memory.  The batch is cut into
-        chunks of chains that flow through three streams -- host-to-device copies, the stage
-        kernels, device-to-host copies -- chained by events, so both copy engines and the SMs
+        chunks of chains that flow through a copy-in stream, two compute streams and a copy-out
+        stream -- host-to-device copies, the stage kernels, device-to-host copies -- chained by
+        events, so both copy engines and the SMs
         work at the same time and the inbound copies run back to back.  The first and last
         chunk are half-size: the pipeline fills and drains on small pieces.  Chains are
         independent and draws are keyed by global chain id, so the result is bit-identical to
