@@ -138,6 +138,22 @@ __device__ __forceinline__ T diff_sum(const T (&x)[EPL], const T* base, int64_t 
 // kernel 26k instructions; calling an out-of-line function per block instead spilled the
 // ~100 live state registers around each call and cost 0.55 ms per 2^20-chain transition
 // (a quarter of the L=150 kernel).  The loop form has neither problem.
+// CNT Philox blocks of one chain side by side (independent ten-round chains), 4 normals each
+template <int CNT, int LPC>
+__device__ __forceinline__ void normal_group(float* zl, int b0, uint64_t seed, uint64_t gchain, uint32_t iter, int lane) {
+  uint32_t w[CNT][4];
+  float z4[CNT][4];
+#pragma unroll
+  for (int j = 0; j < CNT; ++j) Philox::gen(seed, gchain, iter, STREAM_MOMENTUM, (uint32_t)((b0 + j) * LPC + lane), w[j]);
+#pragma unroll
+  for (int j = 0; j < CNT; ++j) normal4_f32(w[j], z4[j]);
+#pragma unroll
+  for (int j = 0; j < CNT; ++j) {
+    zl[4 * (b0 + j)] = z4[j][0]; zl[4 * (b0 + j) + 1] = z4[j][1];
+    zl[4 * (b0 + j) + 2] = z4[j][2]; zl[4 * (b0 + j) + 3] = z4[j][3];
+  }
+}
+
 template <typename T, int EPL, int LPC>
 __device__ __forceinline__ void fill_normals(T (&z)[EPL], uint64_t seed, uint64_t gchain, uint32_t iter, int lane,
                                              int d, int flags) {
@@ -160,22 +176,11 @@ __device__ __forceinline__ void fill_normals(T (&z)[EPL], uint64_t seed, uint64_
     for (int s = 0; s < EPL; ++s) z[s] = (Layout<EPL, LPC>::elem(lane, s) < d) ? (T)zl[s] : T(0);
   } else {
     constexpr int UNR = NB >= 4 ? 4 : NB;          // independent blocks in flight per iteration
-    constexpr int NBP = (NB + UNR - 1) / UNR * UNR;
-    float zl[4 * NBP];
+    constexpr int NFULL = NB / UNR * UNR;          // blocks covered by whole groups; the rest is one smaller group
+    float zl[4 * NB];
 #pragma unroll 1
-    for (int b0 = 0; b0 < NBP; b0 += UNR) {
-      uint32_t w[UNR][4];
-      float z4[UNR][4];
-#pragma unroll
-      for (int j = 0; j < UNR; ++j) Philox::gen(seed, gchain, iter, STREAM_MOMENTUM, (uint32_t)((b0 + j) * LPC + lane), w[j]);
-#pragma unroll
-      for (int j = 0; j < UNR; ++j) normal4_f32(w[j], z4[j]);
-#pragma unroll
-      for (int j = 0; j < UNR; ++j) {
-        zl[4 * (b0 + j)] = z4[j][0]; zl[4 * (b0 + j) + 1] = z4[j][1];
-        zl[4 * (b0 + j) + 2] = z4[j][2]; zl[4 * (b0 + j) + 3] = z4[j][3];
-      }
-    }
+    for (int b0 = 0; b0 < NFULL; b0 += UNR) normal_group<UNR, LPC>(zl, b0, seed, gchain, iter, lane);
+    if constexpr (NB > NFULL) normal_group<NB - NFULL, LPC>(zl, NFULL, seed, gchain, iter, lane);
 #pragma unroll
     for (int s = 0; s < EPL; ++s) z[s] = (Layout<EPL, LPC>::elem(lane, s) < d) ? (T)zl[s] : T(0);
   }
