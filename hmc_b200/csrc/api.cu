@@ -87,6 +87,14 @@ static const Entry* choose_entry_lanes(const hmcb_model& hm, int max_epl, int mi
 }
 
 const Entry* choose_entry(const hmcb_model& hm, int max_epl) { return choose_entry_lanes(hm, max_epl, 1); }
+static const Entry* choose_entry_quiet(const hmcb_model& hm, int max_epl) {
+  const int unitm = hm.invmetric_diag ? 0 : 1;
+  for (const Entry& e : registry())
+    if (e.kind == hm.kind && e.dtype == hm.dtype && e.unitm == unitm && slots_needed(hm.d, e.lpc) <= e.epl && e.epl <= max_epl &&
+        !(hm.kind == HMCB_MODEL_ROSENBROCK && (e.epl & 1)))
+      return choose_entry_lanes(hm, max_epl, 1);
+  return nullptr;
+}
 
 static int check_model(const hmcb_model* m) {
   HMCB_CHECK_ARG(m != nullptr, "model is NULL");
@@ -677,9 +685,16 @@ int hmcb_ghmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmc
   return ghmc_step_t<float>(e, model, chains, rng, n_leap, step_size, io, st);
 }
 
+// The step-size kernels keep the base state of their trial sweeps in registers when a lane holds at most
+// kAdRegBaseMaxEpl slots (extra_kernels.cuh): prefer such a shape (more lanes per chain) when one holds d.
+static const Entry* choose_adaptive_entry(const hmcb_model& hm) {
+  if (const Entry* e = choose_entry_quiet(hm, kAdRegBaseMaxEpl)) return e;
+  return choose_entry(hm);
+}
+
 size_t hmcb_adhmc_eps0_workspace_bytes(const hmcb_model* model, int64_t n_chains) {
   if (check_model(model) || n_chains < 1) return 0;
-  const Entry* e = choose_entry(*model);
+  const Entry* e = choose_adaptive_entry(*model);
   if (!e) return 0;
   int64_t ft;
   int epl;
@@ -699,7 +714,7 @@ int hmcb_adhmc_eps0_step(const hmcb_model* model, const hmcb_chains* chains, con
   HMCB_CHECK_ARG(nsteps >= 1 && tint >= 0, "nsteps must be >= 1 and tint >= 0");
   HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= 3, "u_inject needs u_stride >= 3");
   if (chains->n_chains == 0) return 0;
-  const Entry* e = choose_entry(*model);
+  const Entry* e = choose_adaptive_entry(*model);
   if (!e) return HMCB_E_UNSUPPORTED;
   int64_t ft;
   int epl;
@@ -717,7 +732,7 @@ int hmcb_adhmc_eps0_step(const hmcb_model* model, const hmcb_chains* chains, con
 
 size_t hmcb_adhmc_walk_workspace_bytes(const hmcb_model* model, int64_t n_chains, int32_t n_ratios) {
   if (check_model(model) || n_chains < 0 || n_ratios < 1 || n_ratios > kMaxRatios) return 0;
-  const Entry* e = choose_entry(*model);
+  const Entry* e = choose_adaptive_entry(*model);
   if (!e) return 0;
   int64_t ft;
   int epl;
@@ -749,7 +764,7 @@ int hmcb_adhmc_walk_step(const hmcb_model* model, const hmcb_chains* chains, con
   }
   HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= par->n_segments + 2, "u_inject needs u_stride >= n_segments + 2");
   if (chains->n_chains == 0) return 0;
-  const Entry* e = choose_entry(*model);
+  const Entry* e = choose_adaptive_entry(*model);
   if (!e) return HMCB_E_UNSUPPORTED;
   int64_t ft;
   int epl;

@@ -329,6 +329,8 @@ __device__ __forceinline__ double draw_uniform_ad(const AdArgs<T>& a, int64_t ch
   return (idx & 1) ? u53(w[2], w[3]) : u53(w[0], w[1]);
 }
 
+constexpr int kAdRegBaseMaxEpl = 28;   // q, p and the base state (q, p) of the trial sweeps: 4*EPL values per lane
+
 template <class Model, typename T, int EPL, int LPC, bool UNITM, int THREADS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB) k_adhmc_eps0(const Model model, const AdArgs<T> a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -365,6 +367,10 @@ __global__ void __launch_bounds__(THREADS, MINB) k_adhmc_eps0(const Model model,
     const int64_t off = chain * a.sc;
     const uint64_t gchain = (uint64_t)(a.chain_offset + chain);
     T q[EPL], p[EPL];
+    // the state every trial trajectory of a sweep starts from: in registers when the shape leaves room
+    // (4*EPL values per lane), else re-read from global memory / the per-thread scratch for every trial
+    constexpr bool REGBASE = EPL <= kAdRegBaseMaxEpl;
+    T qb[REGBASE ? EPL : 1], pb[REGBASE ? EPL : 1];
     int cH = 0, cVg = 0, cLeap = 0;
     T pp[kMaxTry];
 
@@ -377,13 +383,21 @@ __global__ void __launch_bounds__(THREADS, MINB) k_adhmc_eps0(const Model model,
     }
 #pragma unroll
     for (int s = 0; s < EPL; ++s) f_p0[(int64_t)s * FT] = p[s];
+    if (REGBASE) {
+      load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) { qb[REGBASE ? s : 0] = q[s]; pb[REGBASE ? s : 0] = p[s]; }
+    }
 
     // sweep(from forward base or reverse base): fills pp[] normalised; returns H at the base
     auto sweep = [&](bool reverse, T& Hbase) {
       T sum = T(0);
       for (int i = 0; i <= ntry; ++i) {
         // i == 0 evaluates H at the base through a zero-length "trajectory" (kick with h=0)
-        if (!reverse) {
+        if (REGBASE) {
+#pragma unroll
+          for (int s = 0; s < EPL; ++s) { q[s] = qb[REGBASE ? s : 0]; p[s] = reverse ? -pb[REGBASE ? s : 0] : pb[REGBASE ? s : 0]; }
+        } else if (!reverse) {
           load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
 #pragma unroll
           for (int s = 0; s < EPL; ++s) p[s] = f_p0[(int64_t)s * FT];
@@ -436,9 +450,14 @@ __global__ void __launch_bounds__(THREADS, MINB) k_adhmc_eps0(const Model model,
     const T pf_den = pp[isx + 1];
 
     // main trajectory from (q0, p0)
-    load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
+    if (REGBASE) {
 #pragma unroll
-    for (int s = 0; s < EPL; ++s) p[s] = f_p0[(int64_t)s * FT];
+      for (int s = 0; s < EPL; ++s) { q[s] = qb[REGBASE ? s : 0]; p[s] = pb[REGBASE ? s : 0]; }
+    } else {
+      load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) p[s] = f_p0[(int64_t)s * FT];
+    }
     T Vs, Ve;
     int Nm = a.n_leap > 1 ? a.n_leap : 1;
     if (a.tint > 0) { Nm = (int)(a.tint / (double)ss) + 1; if (Nm < 1) Nm = 1; }
@@ -449,9 +468,10 @@ __global__ void __launch_bounds__(THREADS, MINB) k_adhmc_eps0(const Model model,
 #pragma unroll
     for (int s = 0; s < EPL; ++s) {
       const int i = Lay::elem(c.lane, s);
-      if (i < d) dq += a.q_in[off + i * a.sd] - q[s];
+      if (i < d) dq += (REGBASE ? qb[REGBASE ? s : 0] : a.q_in[off + i * a.sd]) - q[s];
       f_q1[(int64_t)s * FT] = q[s];
       f_p1[(int64_t)s * FT] = p[s];
+      if (REGBASE) { qb[REGBASE ? s : 0] = q[s]; pb[REGBASE ? s : 0] = p[s]; }
     }
     dq = group_sum_masked<LPC, T>(dq, c.mask);
 
@@ -583,6 +603,10 @@ __global__ void __launch_bounds__(THREADS, MINB) k_adhmc_walk(const Model model,
     const int64_t off = chain * a.sc;
     const uint64_t gchain = (uint64_t)(a.chain_offset + chain);
     T q[EPL], p[EPL];
+    // the base state (q0, p0) and later (q1, p1) that sweeps, candidate segments and reverse segments all start
+    // from: in registers when the shape leaves room, else in the per-thread scratch (k_adhmc_eps0 does the same)
+    constexpr bool REGBASE = EPL <= kAdRegBaseMaxEpl;
+    T qb[REGBASE ? EPL : 1], pb[REGBASE ? EPL : 1];
     int cH = 0, cVg = 0, cLeap = 0;
     T pp[kMaxTry];
 
@@ -601,8 +625,21 @@ __global__ void __launch_bounds__(THREADS, MINB) k_adhmc_walk(const Model model,
       if (a.checks && c.lane == 0) a.checks[(chain * 3 + row) * N + i] = (T)v;
     };
     auto load_base = [&](T sign) {
+      if (REGBASE) {
 #pragma unroll
-      for (int s = 0; s < EPL; ++s) { q[s] = f_q1[(int64_t)s * FT]; p[s] = sign * f_p1[(int64_t)s * FT]; }
+        for (int s = 0; s < EPL; ++s) { q[s] = qb[REGBASE ? s : 0]; p[s] = sign * pb[REGBASE ? s : 0]; }
+      } else {
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) { q[s] = f_q1[(int64_t)s * FT]; p[s] = sign * f_p1[(int64_t)s * FT]; }
+      }
+    };
+    auto set_base = [&]() {      // (q, p) becomes the base
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) {
+        f_q1[(int64_t)s * FT] = q[s];
+        f_p1[(int64_t)s * FT] = p[s];
+        if (REGBASE) { qb[REGBASE ? s : 0] = q[s]; pb[REGBASE ? s : 0] = p[s]; }
+      }
     };
 
     {
@@ -613,6 +650,11 @@ __global__ void __launch_bounds__(THREADS, MINB) k_adhmc_walk(const Model model,
     }
 #pragma unroll
     for (int s = 0; s < EPL; ++s) f_p0[(int64_t)s * FT] = p[s];
+    if (REGBASE) {
+      load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) { qb[REGBASE ? s : 0] = q[s]; pb[REGBASE ? s : 0] = p[s]; }
+    }
     if (a.checks && c.lane == 0)
       for (int i = 0; i < 3 * N; ++i) a.checks[chain * 3 * N + i] = T(0);
 
@@ -620,7 +662,9 @@ __global__ void __launch_bounds__(THREADS, MINB) k_adhmc_walk(const Model model,
     auto sweep = [&](bool reverse, T& Hbase) {
       T sum = T(0);
       for (int i = 0; i <= ntry; ++i) {
-        if (!reverse) {
+        if (REGBASE) {
+          load_base(reverse ? T(-1) : T(1));      // the base registers hold (q0, p0) until the first segment is done
+        } else if (!reverse) {
           load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
 #pragma unroll
           for (int s = 0; s < EPL; ++s) p[s] = f_p0[(int64_t)s * FT];
@@ -669,9 +713,13 @@ __global__ void __launch_bounds__(THREADS, MINB) k_adhmc_walk(const Model model,
     put_check(2, 0, ss);
 
     // ---- first segment from (q0, p0)
-    load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
+    if (REGBASE) {
+      load_base(T(1));
+    } else {
+      load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
 #pragma unroll
-    for (int s = 0; s < EPL; ++s) p[s] = f_p0[(int64_t)s * FT];
+      for (int s = 0; s < EPL; ++s) p[s] = f_p0[(int64_t)s * FT];
+    }
     T Vs, Ve;
     {
       const int n0 = seg_steps(ss);
@@ -679,8 +727,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_adhmc_walk(const Model model,
       cH += 1; cVg += n0 + 1; cLeap += 1;
     }
     T H1 = Ve + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
-#pragma unroll
-    for (int s = 0; s < EPL; ++s) { f_q1[(int64_t)s * FT] = q[s]; f_p1[(int64_t)s * FT] = p[s]; }
+    set_base();
     T Hprev = H0;
     double ssnew = ss;
     int blown = -1, pbind = 0;
@@ -764,7 +811,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_adhmc_walk(const Model model,
       {
         const T* fq = f_cand + (int64_t)(2 * pind) * slot;
 #pragma unroll
-        for (int s = 0; s < EPL; ++s) { f_q1[(int64_t)s * FT] = fq[(int64_t)s * FT]; f_p1[(int64_t)s * FT] = fq[slot + (int64_t)s * FT]; }
+        for (int s = 0; s < EPL; ++s) { q[s] = fq[(int64_t)s * FT]; p[s] = fq[slot + (int64_t)s * FT]; }
+        set_base();
       }
     }
 
