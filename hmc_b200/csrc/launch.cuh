@@ -161,6 +161,8 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
   if constexpr (LPC == 1 && UNITM && sizeof(T) == 8 && EPL >= 20 && !GAUSS) {
     if ((op == OP_HMC || op == OP_DR0) && !getenv("HMCB_NO_WS")) {
       TransArgs<T>& a = *(TransArgs<T>*)args;
+      // (not with a partial momentum refresh: at nleap=20 the plain kernel with its staging tile measured
+      // 1.25 ms against 1.40 ms here, the strided p_prev / p_out rows being what costs)
       if (!a.p_inject && !a.p_prev && a.n_chains >= 4096) {
         a.tile_io = 0;   // measured: the staging tile does not pay in the warp-specialised kernel (L=150: 2.02 -> 2.18 ms)
         const size_t ws_smem = 2 * (size_t)EPL * kWsComputeThreads * sizeof(float) + 64;

@@ -186,6 +186,15 @@ __device__ __forceinline__ void fill_normals(T (&z)[EPL], uint64_t seed, uint64_
   }
 }
 
+// p = alpha*p_prev + sqrt(1 - alpha**2)*pn (src/algorithms.py:269,603) with numpy's rounding: two products and
+// a sum, none of them fused
+__device__ __forceinline__ double mix_momentum(double alpha, double pv, double beta, double pn) {
+  return __dadd_rn(__dmul_rn(alpha, pv), __dmul_rn(beta, pn));
+}
+__device__ __forceinline__ float mix_momentum(float alpha, float pv, float beta, float pn) {
+  return __fadd_rn(__fmul_rn(alpha, pv), __fmul_rn(beta, pn));
+}
+
 // momentum p = z * metricstd, z ~ N(0,1) (src/pyhmc.py:66); z from Philox or injected
 template <typename T, int EPL, int LPC, bool UNITM>
 __device__ __forceinline__ void draw_momentum(T (&p)[EPL], const TransArgs<T>& a, const T (&minv)[UNITM ? 1 : EPL],
@@ -204,7 +213,7 @@ __device__ __forceinline__ void draw_momentum(T (&p)[EPL], const TransArgs<T>& a
     T pv[EPL];
     load_vec<T, EPL, LPC>(pv, a.p_prev, chain * a.sc, a.sd, lane, d, T(1));
 #pragma unroll
-    for (int s = 0; s < EPL; ++s) p[s] = a.alpha * pv[s] + a.beta * p[s];
+    for (int s = 0; s < EPL; ++s) p[s] = mix_momentum(a.alpha, pv[s], a.beta, p[s]);
   }
 }
 
