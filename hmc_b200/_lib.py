@@ -43,7 +43,7 @@ class Profile(C.Structure):
 
 class StepOut(C.Structure):
     _fields_ = [("p_out", C.c_void_p), ("code", C.c_void_p), ("energies", C.c_void_p), ("avec", C.c_void_p),
-                ("counts", C.c_void_p), ("accept_prob", C.c_void_p), ("ptries", C.c_void_p)]
+                ("counts", C.c_void_p), ("accept_prob", C.c_void_p), ("ptries", C.c_void_p), ("p0_out", C.c_void_p)]
 
 
 class MalaIO(C.Structure):
@@ -71,6 +71,9 @@ class AdhmcOut(C.Structure):
 SIGNATURES = {
     "hmcb_version": (C.c_int, []),
     "hmcb_last_error": (C.c_char_p, []),
+    "hmcb_philox4x32_10": (None, [C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "hmcb_philox_block": (None, [C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]),
+    "hmcb_u53": (C.c_double, [C.c_uint32, C.c_uint32]),
     "hmcb_hmc_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double, C.c_int32,
                                 C.POINTER(StepOut), C.c_void_p]),
     "hmcb_leapfrog": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.c_void_p, C.c_void_p, C.c_int32, C.c_double,

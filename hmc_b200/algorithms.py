@@ -154,18 +154,23 @@ class HMC(_PyHMCBase):
         self.engine.check_dim(b)
         return b
 
-    def adapt_stepsize(self, q, epsadapt, **kwargs):
+    def adapt_stepsize(self, q, epsadapt, p=None, u=None, **kwargs):
         """Dual-averaging warm-up (src/algorithms.py:209-230): epsadapt+1 transitions,
         each feeding the update with prob = exp(H0-H1) clipped to [0,1], or 0 for a
         chain that did not move.  With C chains (and R ranks) the statistic is the
-        mean over all chains -- one shared step size, all-reduced over NCCL."""
+        mean over all chains -- one shared step size, all-reduced over NCCL; with one
+        chain it is the reference's update.  p [epsadapt+1, C, d] / u [epsadapt+1, C, 1]
+        replay the draws of each iteration (parity runs)."""
         step_size = self.step_size
         da = DualAveragingStepSize(step_size)
         self._parse_kwargs_sample(**kwargs)
         b = self._device_q(q)
         qd = b.q
+        self.adapt_trace = []
         for i in range(epsadapt + 1):
-            out = self.engine.hmc_step(qd, self.nleap, step_size, self._rule, want_p=False, want_prob=True)
+            self.adapt_trace.append(step_size)
+            out = self.engine.hmc_step(qd, self.nleap, step_size, self._rule, want_p=False, want_prob=True,
+                                       p=None if p is None else p[i], u=None if u is None else u[i])
             qd = out["q"]
             stat = torch.stack([out["prob"].sum(dtype=torch.float64),
                                 torch.tensor(float(qd.shape[0]), dtype=torch.float64, device=qd.device)])
@@ -178,17 +183,25 @@ class HMC(_PyHMCBase):
                 self.step_size = step_size
         return b.out(qd)
 
-    def sample(self, q, p=None, callback=None, skipburn=True, epsadapt=0, **kwargs):
+    def sample(self, q, p=None, callback=None, skipburn=True, epsadapt=0, draws=None, **kwargs):
         """src/algorithms.py:233-254.  ``accepts`` is kept for every iteration, samples /
-        Hs / counts only for i > burnin (strict, as the reference)."""
+        Hs / counts only for i > burnin (strict, as the reference): nsamples-1 rows.
+        ``p`` is accepted and ignored, as in the reference.  draws=(P, U), P [T, C, d] and
+        U [T, C, 1] with T = (epsadapt+1 if epsadapt else 0) + nsamples + burnin, replays the
+        draws in the order the reference would consume them (parity runs)."""
         self._parse_kwargs_sample(**kwargs)
         state = Sampler()
+        P, U = (None, None) if draws is None else draws
+        t0 = 0
         if epsadapt:
-            q = self.adapt_stepsize(q, epsadapt, **kwargs)
+            t0 = epsadapt + 1
+            q = self.adapt_stepsize(q, epsadapt, p=None if P is None else P[:t0], u=None if U is None else U[:t0],
+                                    **kwargs)
         b = self._device_q(q)
         qd = b.q
         for i in range(self.nsamples + self.burnin):
-            out = self.engine.hmc_step(qd, self.nleap, self.step_size, self._rule, want_p=False)
+            out = self.engine.hmc_step(qd, self.nleap, self.step_size, self._rule, want_p=False,
+                                       p=None if P is None else P[t0 + i], u=None if U is None else U[t0 + i])
             qd = out["q"]
             state.i += 1
             state.accepts.append(b.out(out["code"].to(torch.float64)))
@@ -231,16 +244,19 @@ class DRHMC(HMC):
         self.Hcount, self.Vgcount, self.leapcount = out["counts"][:, 0], out["counts"][:, 1], out["counts"][:, 2]
         return b.out(out["q"]), b.out(out["p"]), b.out(out["code"]), b.out(out["avec"]), b.out(out["counts"])
 
-    def sample(self, q, p=None, callback=None, **kwargs):
-        """src/algorithms.py:534-555: every iteration (burn-in included) is stored."""
+    def sample(self, q, p=None, callback=None, draws=None, **kwargs):
+        """src/algorithms.py:534-555: every iteration (burn-in included) is stored.  (The reference draws
+        one unused normal vector when ``p`` is None, :538; nothing is drawn for it here.)  draws=(P, U),
+        P [T, C, d] and U [T, C, nprops] with T = nsamples + burnin, replays the draws (parity runs)."""
         self._parse_kwargs_sample(**kwargs)
         state = Sampler()
         state.avecs = []
         b = self._device_q(q)
         qd = b.q
+        P, U = (None, None) if draws is None else draws
         for i in range(self.nsamples + self.burnin):
             out = self.engine.drhmc_step(qd, self.nleap, self.step_size, kwargs["nprops"], kwargs["stepfactor"],
-                                         want_p=False)
+                                         want_p=False, p=None if P is None else P[i], u=None if U is None else U[i])
             qd = out["q"]
             state.i += 1
             state.samples.append(b.out(qd))
@@ -405,8 +421,6 @@ def dr_stage_lengths(nleap, nprops, stepfactor):
     return [int(nleap * stepfactor ** j) for j in range(nprops)], [1.0 / stepfactor ** j for j in range(nprops)]
 
 
-# name -> class registry (src/algorithms.py:823-832); the probabilistic-DR keys of the reference
-# ('pdrhmc_metrop', 'pdrhmc_hasting') are a later row of SURVEY.md section 8f
 class _ProbDRHMC(HMC):
     """Probabilistic delayed rejection in src/algorithms.py: the classes add get_num and
     multi_step to algorithms.HMC and inherit its step / sample unchanged."""
@@ -443,5 +457,7 @@ class Prob_DRHMC_Hastings(_ProbDRHMC):
         super().__init__(log_prob, grad_log_prob, invmetric_diag=invmetric_diag, **engine_kw)
 
 
-alg_dict = {"hmc": HMC, "ghmc": GHMC, "pghmc": Persistent_GHMC, "drhmc": DRHMC, "drghmc": DRGHMC}
+# name -> class registry (src/algorithms.py:823-832), the reference's keys
+alg_dict = {"hmc": HMC, "ghmc": GHMC, "pghmc": Persistent_GHMC, "drhmc": DRHMC, "drghmc": DRGHMC,
+            "pdrhmc_metrop": Prob_DRHMC_Metrop, "pdrhmc_hasting": Prob_DRHMC_Hastings}
 

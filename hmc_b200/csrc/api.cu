@@ -156,6 +156,7 @@ static void fill_args(TransArgs<T>& a, const hmcb_model* m, const hmcb_chains* c
     a.counts = o->counts;
     a.accept_prob = (T*)o->accept_prob;
     a.ptries_out = (T*)o->ptries;
+    a.p0_out = (T*)o->p0_out;
   }
   a.minv = (const T*)m->invmetric_diag;
 }
@@ -171,7 +172,8 @@ static int hmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c,
   a.eps[0] = (T)eps;
   if constexpr (sizeof(T) == 8) {
     // dense Gaussian, f64, unit metric, d <= 104: gradient on the FP64 tensor path
-    if (m->kind == HMCB_MODEL_GAUSSIAN && !getenv("HMCB_GAUSS_GENERIC")) {
+    // (not with a partial momentum refresh: the tensor-path kernel draws a full refresh only)
+    if (m->kind == HMCB_MODEL_GAUSSIAN && !r->p_prev && !a.p0_out && !getenv("HMCB_GAUSS_GENERIC")) {
       const int rc = gauss_dmma_hmc(*m, a, st);
       if (rc != 1) return rc;
     }
@@ -416,6 +418,7 @@ static void sub_range(const hmcb_model* m, const hmcb_chains* c, const hmcb_rng*
     os.counts = o->counts ? o->counts + 3 * lo : nullptr;
     os.accept_prob = at(o->accept_prob, lo);
     os.ptries = at(o->ptries, lo * nprops);
+    os.p0_out = at(o->p0_out, lo * c->stride_chain);
   }
 }
 
@@ -467,6 +470,25 @@ extern "C" {
 int hmcb_version(void) { return HMCB_VERSION; }
 
 const char* hmcb_last_error(void) { return g_err; }
+
+void hmcb_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
+  uint32_t c[4] = {ctr[0], ctr[1], ctr[2], ctr[3]};
+  uint32_t k0 = key[0], k1 = key[1];
+  for (int r = 0; r < 10; ++r) {
+    Philox::round(c, k0, k1);
+    k0 += Philox::W0; k1 += Philox::W1;
+  }
+  for (int i = 0; i < 4; ++i) out[i] = c[i];
+}
+
+void hmcb_philox_block(uint64_t seed, uint64_t chain, uint32_t iteration, uint32_t stream, uint32_t block,
+                       uint32_t out[4]) {
+  uint32_t w[4];
+  Philox::gen(seed, chain, iteration, stream, block, w);
+  for (int i = 0; i < 4; ++i) out[i] = w[i];
+}
+
+double hmcb_u53(uint32_t a, uint32_t b) { return u53(a, b); }
 
 int hmcb_hmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
                   double step_size, int32_t rule, const hmcb_step_out* out, void* stream) {
@@ -590,22 +612,29 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
   std::lock_guard<std::mutex> seq_lock(seq_mu);
   HMCB_CUDA(cudaEventRecord(h->fork, st));
   char* w = (char*)workspace;
-  for (int i = 0; i < S; ++i) {
+  rc = 0;
+  for (int i = 0; i < S && rc == 0; ++i) {
     const int64_t lo = split_bound(chains->n_chains, S, i), hi = split_bound(chains->n_chains, S, i + 1);
     hmcb_chains cs;
     hmcb_rng rs;
     hmcb_step_out os;
     sub_range(model, chains, rng, out, nprops, lo, hi, cs, rs, os);
     cudaStream_t on = i == 0 ? st : h->s[i - 1];
-    if (i > 0) HMCB_CUDA(cudaStreamWaitEvent(on, h->fork, 0));
-    if ((rc = run(&cs, &rs, out ? &os : nullptr, w, L[i], on))) return rc;
     if (i > 0) {
-      HMCB_CUDA(cudaEventRecord(h->join[i - 1], on));
-      HMCB_CUDA(cudaStreamWaitEvent(st, h->join[i - 1], 0));
+      cudaError_t ce = cudaStreamWaitEvent(on, h->fork, 0);
+      if (ce != cudaSuccess) { rc = cuda_fail(ce, "cudaStreamWaitEvent(helper, fork)"); break; }
+    }
+    rc = run(&cs, &rs, out ? &os : nullptr, w, L[i], on);
+    if (i > 0) {
+      // a helper stream that was forked is always joined back, whatever happened on it: the caller's stream
+      // stays ordered after the library's own streams (and a stream capture stays joined) on the error path too
+      cudaError_t ce = cudaEventRecord(h->join[i - 1], on);
+      if (ce == cudaSuccess) ce = cudaStreamWaitEvent(st, h->join[i - 1], 0);
+      if (ce != cudaSuccess && rc == 0) rc = cuda_fail(ce, "join of the helper stream");
     }
     w += L[i].total;
   }
-  return 0;
+  return rc;
 }
 
 int hmcb_drhmc_step_static(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,

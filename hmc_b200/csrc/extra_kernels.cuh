@@ -60,11 +60,9 @@ __global__ void __launch_bounds__(THREADS, MINB) k_mala(const Model model, const
     T q[EPL], g[EPL], q1[EPL], g1[EPL];
     load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
     int nvg = 0, nacc = 0, code = 0;
-    T Vq;
-    if (a.Vg_in) {
-      load_vec<T, EPL, LPC>(g, a.Vg_in, off, a.sd, c.lane, d, T(1));
-      Vq = a.V_in ? a.V_in[chain] : T(0);
-    }
+    // V_q and V_gq are cached independently (src/mala.py:49-52): either may be supplied without the other
+    T Vq = a.V_in ? a.V_in[chain] : T(0);
+    if (a.Vg_in) load_vec<T, EPL, LPC>(g, a.Vg_in, off, a.sd, c.lane, d, T(1));
     if (!a.Vg_in || !a.V_in) {
       T tmp[EPL];
 #pragma unroll

@@ -163,7 +163,9 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
       TransArgs<T>& a = *(TransArgs<T>*)args;
       // (not with a partial momentum refresh: at nleap=20 the plain kernel with its staging tile measured
       // 1.25 ms against 1.40 ms here, the strided p_prev / p_out rows being what costs)
-      if (!a.p_inject && !a.p_prev && a.n_chains >= 4096) {
+      // (nor with the exact f64 normal generator: the helper warpgroup draws with normal4_f32 only, and every
+      // other place that re-draws p0 -- the DR stages >= 1, p_out of rejected chains -- would use the f64 one)
+      if (!a.p_inject && !a.p_prev && !(a.rng_flags & HMCB_RNG_NORMAL_F64) && a.n_chains >= 4096) {
         a.tile_io = 0;   // measured: the staging tile does not pay in the warp-specialised kernel (L=150: 2.02 -> 2.18 ms)
         const size_t ws_smem = 2 * (size_t)EPL * kWsComputeThreads * sizeof(float) + 64;
         const int grid = (int)((a.n_chains + kWsComputeThreads - 1) / kWsComputeThreads < sm_count()

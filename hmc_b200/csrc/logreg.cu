@@ -253,18 +253,13 @@ static int launch_grad(const hmcb_model& m, const unsigned char* prep, const Pre
   g.n_slabs = W.n_slabs;
   g.x_scale_dev = (const int32_t*)prep;
   dim3 grid(W.n_tiles, W.n_slabs);
-  static bool attr_done[2] = {false, false};
+  // the opt-in is a per-device attribute of the function: set on every call (cheap), as launch_any does, so that a
+  // second device in the same process gets it too
   if (want_v) {
-    if (!attr_done[0]) {
-      HMCB_CUDA(cudaFuncSetAttribute(k_logreg_grad_v1<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemV1));
-      attr_done[0] = true;
-    }
+    HMCB_CUDA(cudaFuncSetAttribute(k_logreg_grad_v1<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemV1));
     k_logreg_grad_v1<true, 3><<<grid, kThreadsV1, kSmemV1, st>>>(g);
   } else {
-    if (!attr_done[1]) {
-      HMCB_CUDA(cudaFuncSetAttribute(k_logreg_grad_v1<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemV1));
-      attr_done[1] = true;
-    }
+    HMCB_CUDA(cudaFuncSetAttribute(k_logreg_grad_v1<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemV1));
     k_logreg_grad_v1<false, 3><<<grid, kThreadsV1, kSmemV1, st>>>(g);
   }
   HMCB_CUDA(cudaPeekAtLastError());
@@ -336,6 +331,7 @@ int hmcb_logreg_hmc_step(const hmcb_model* model, const void* prepared, const hm
                  "logistic regression needs contiguous row-major [C,d] chain state");
   HMCB_CHECK_ARG(rule == HMCB_RULE_PYHMC || rule == HMCB_RULE_ALG, "unknown accept rule %d", rule);
   HMCB_CHECK_ARG(n_leap >= 0, "n_leap must be >= 0");
+  HMCB_CHECK_ARG(!out || !out->p0_out, "p0_out is not provided by the logistic-regression step");
   const int64_t C = chains->n_chains;
   const PrepLayout P = prep_layout(model->n_data);
   const WsLayout W = ws_layout(C, model->d, P.n_blocks);

@@ -59,6 +59,7 @@ struct TransArgs {
   int32_t dr_conv;   // 0 algorithms.DRHMC conventions, 1 pyhmc.PyHMC_multistep's (also the probabilistic classes')
   int32_t dr_prob;   // probabilistic DR: 0 off, 1 p_try = 1 - min(1, e^{H0-Hj}), 2 p_try = 1 - alpha_j
   T* ptries_out;     // [n_chains, nprops] or nullptr
+  T* p0_out;         // starting momentum of every chain (layout of q) or nullptr
   int32_t nprops, stage;
   int32_t tile_io;   // set by the launcher when the per-warp staging tile was allocated (see warp_tile_load)
   int32_t L[kMaxProps];
@@ -307,6 +308,7 @@ __device__ __forceinline__ void finish_single(const Model& model, const TransArg
   using Lay = Layout<EPL, LPC>;
   const int d = a.d;
   int cH, cVg, cLeap;
+    if (a.p0_out) store_vec<T, EPL, LPC>(p, a.p0_out, qoff, a.sd, c.lane, d);
     const T K0 = kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
     T V0, V1;
     const int N = a.L[0] > 1 ? a.L[0] : 1;

@@ -158,21 +158,24 @@ class Engine:
             raise ValueError("q has dimension %d but the model has d=%d" % (b.d, self.model.d))
 
     # ------------------------------------------------------------------ calls
-    def hmc_step(self, q, n_leap, step_size, rule, p=None, u=None, want_p=True, want_prob=False, q_out=None):
-        """hmcb_hmc_step on device tensor q [C,d]; returns dict of device tensors."""
+    def hmc_step(self, q, n_leap, step_size, rule, p=None, u=None, want_p=True, want_prob=False, q_out=None,
+                 want_p0=False):
+        """hmcb_hmc_step on device tensor q [C,d]; returns dict of device tensors.  want_p0 also returns
+        the momentum every chain started from (hmcb_step_out.p0_out)."""
         m = self._ensure()
         C_ = q.shape[0]
         with torch.cuda.device(self.device):
             q_out = torch.empty_like(q) if q_out is None else q_out
             out = {"q": q_out,
                    "p": torch.empty_like(q) if want_p else None,
+                   "p0": torch.empty_like(q) if want_p0 else None,
                    "code": torch.empty(C_, dtype=torch.int32, device=self.device),
                    "Hs": torch.empty((C_, 2), dtype=self.dtype, device=self.device),
                    "counts": torch.empty((C_, 3), dtype=torch.int32, device=self.device),
                    "prob": torch.empty(C_, dtype=self.dtype, device=self.device) if want_prob else None}
             so = _lib.StepOut()
             so.p_out, so.code, so.energies = _lib.ptr(out["p"]), _lib.ptr(out["code"]), _lib.ptr(out["Hs"])
-            so.counts, so.accept_prob = _lib.ptr(out["counts"]), _lib.ptr(out["prob"])
+            so.counts, so.accept_prob, so.p0_out = _lib.ptr(out["counts"]), _lib.ptr(out["prob"]), _lib.ptr(out["p0"])
             ch = self._chains(q, q_out)
             r, keep = self._rng(p, u, 1, C_)
             if self.is_logistic:
@@ -190,7 +193,7 @@ class Engine:
 
     def drhmc_step(self, q, n_leap, step_size, nprops, stepfactor, p=None, u=None, want_p=True, q_out=None,
                    stage_events=None, want_avec=True, code_out=None, counts_out=None, extra_offset=0, ws_slot=0,
-                   advance=True, convention=0, p_prev=None, alpha=0.0, p_out=None, avec_out=None):
+                   advance=True, convention=0, p_prev=None, alpha=0.0, p_out=None, avec_out=None, want_p0=False):
         """hmcb_drhmc_step on device tensor q [C,d].  q_out / code_out / counts_out let a
         caller reuse its own output buffers (no allocation inside a timed loop)."""
         m = self._ensure()
@@ -216,6 +219,9 @@ class Engine:
             so = _lib.StepOut()
             so.p_out, so.code, so.avec = _lib.ptr(out["p"]), _lib.ptr(out["code"]), _lib.ptr(out["avec"])
             so.counts, so.ptries = _lib.ptr(out["counts"]), _lib.ptr(out.get("ptries"))
+            if want_p0:
+                out["p0"] = torch.empty_like(q)
+                so.p0_out = _lib.ptr(out["p0"])
             ch = self._chains(q, q_out, extra_offset)
             r, keep = self._rng(p, u, 2 * nprops - 1 if prob else nprops, C_, p_prev, alpha)
             _lib.check(self.lib.hmcb_drhmc_step(C.byref(m), C.byref(ch), C.byref(r), int(n_leap), float(step_size),

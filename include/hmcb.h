@@ -8,8 +8,12 @@
  *
  * Conventions
  *  - Plain pointers and sizes only.  Every buffer is DEVICE memory owned by the
- *    caller; the library allocates nothing and keeps no state between calls
- *    besides a thread-local error string.
+ *    caller; the library allocates no device memory.  What it does keep between
+ *    calls, per process: a thread-local error string; per device, created on first
+ *    use and never destroyed: the helper streams and fork/join events of the staged
+ *    delayed-rejection path (see hmcb_drhmc_step; their enqueueing is serialised by
+ *    a process-wide mutex) and the cached device address of the built-in scratch of
+ *    hmcb_drhmc_step_static (a fixed array inside the library image).
  *  - All work is enqueued on `stream` (a cudaStream_t passed as void*); no call
  *    synchronises the host.  Errors detected at launch are returned.
  *  - Return value: 0 on success, a negative HMCB_E_* on failure;
@@ -89,6 +93,10 @@ typedef struct hmcb_step_out {
                                  (what src/algorithms.py:218-224 feeds dual averaging) */
   void* ptries;               /* [C,nprops] try probabilities, probabilistic DR conventions only
                                  (6th return value of multi_step, src/algorithms.py:706) */
+  void* p0_out;               /* the momentum every chain STARTED from (after metric scaling and partial
+                                 refresh: the p of src/pyhmc.py:66, p0 of src/algorithms.py:506), layout of q.
+                                 Lets a test replay a production (Philox) transition through the reference:
+                                 hmcb_hmc_step and hmcb_drhmc_step only; hmcb_logreg_hmc_step rejects it */
 } hmcb_step_out;
 
 /* Accept-rule conventions:
@@ -315,6 +323,21 @@ int hmcb_logreg_hmc_step(const hmcb_model* model, const void* prepared, const hm
                          const hmcb_step_out* out, void* workspace, size_t workspace_bytes, void* stream);
 int hmcb_logreg_logp_grad(const hmcb_model* model, const void* prepared, const void* theta, int64_t n_chains,
                           void* logp, void* grad, void* workspace, size_t workspace_bytes, void* stream);
+
+/* The draw contract, on the host (no GPU needed), so that tests can pin it:
+ *  - hmcb_philox4x32_10: the raw Philox4x32-10 block function (Salmon et al. 2011), checked
+ *    against the published Random123 known-answer vectors;
+ *  - hmcb_philox_block: the block a kernel draws for (seed, global chain id, iteration,
+ *    stream, block): key = seed, counter = (chain lo, chain hi, iteration, stream<<24 | block).
+ *    Streams: 0 momentum normals (block b -> elements 4b..4b+3 with the f32 generator; blocks
+ *    2b, 2b+1 -> elements 4b..4b+1, 4b+2..4b+3 with HMCB_RNG_NORMAL_F64), 1 accept uniforms
+ *    (uniform i = words (0,1) of block i/2 if i is even, words (2,3) if odd), 2 step-size draws;
+ *  - hmcb_u53: the 53-bit uniform in [0,1) made from two words.
+ * They stand where the reference calls np.random.normal / np.random.uniform (src/pyhmc.py:66,59). */
+void hmcb_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);
+void hmcb_philox_block(uint64_t seed, uint64_t chain, uint32_t iteration, uint32_t stream, uint32_t block,
+                       uint32_t out[4]);
+double hmcb_u53(uint32_t a, uint32_t b);
 
 /* Measurement probe: a register-resident dependent-FMA loop (FP64 or FP32) used
  * to measure the pipe peak that roofline fractions are quoted against.

@@ -259,6 +259,43 @@ def hmc_adapt_stepsize(model, q, epsadapt, nleap, step_size, rng, invmetric_diag
     return q, step_size, used
 
 
+def hmc_sample(model, q, nsamples, burnin, step_size, nleap, rng, skipburn=True, epsadapt=0, invmetric_diag=None):
+    """algorithms.HMC.sample, src/algorithms.py:233-254: optional dual-averaging warm-up, then
+    nsamples+burnin steps; ``accepts`` for every iteration, samples / Hs / counts only for
+    i > burnin (strict) -> nsamples-1 rows.  Returns a dict of stacked arrays and the step size used."""
+    if epsadapt:
+        q, step_size, _ = hmc_adapt_stepsize(model, q, epsadapt, nleap, step_size, rng, invmetric_diag)
+    samples, accepts, Hs, counts = [], [], [], []
+    n = 0
+    for i in range(nsamples + burnin):
+        q, p, acc, H, count = hmc_step_alg(model, q, nleap, step_size, rng, invmetric_diag)
+        n += 1
+        accepts.append(acc)
+        if skipburn & (i > burnin):
+            samples.append(q)
+            Hs.append(H)
+            counts.append(count)
+    return dict(samples=np.array(samples), accepts=np.array(accepts), Hs=np.array(Hs), counts=np.array(counts), i=n,
+                step_size=step_size)
+
+
+def drhmc_sample(model, q, nsamples, burnin, step_size, nleap, nprops, stepfactor, rng, p=None, invmetric_diag=None):
+    """algorithms.DRHMC.sample, src/algorithms.py:534-555: one (unused) normal vector is drawn when p is
+    None (:538); every iteration, burn-in included, is stored."""
+    if p is None:
+        p = rng.normal(0, 1, q.size).reshape(q.shape)
+    samples, accepts, avecs, counts = [], [], [], []
+    n = 0
+    for i in range(nsamples + burnin):
+        q, p, acc, avec, count = drhmc_step(model, q, nleap, step_size, nprops, stepfactor, rng, invmetric_diag)
+        n += 1
+        samples.append(q)
+        accepts.append(acc)
+        avecs.append(avec)
+        counts.append(count)
+    return dict(samples=np.array(samples), accepts=np.array(accepts), avecs=np.array(avecs), counts=np.array(counts), i=n)
+
+
 # ----------------------------------------------------------------------------- AdHMC_eps0
 
 def _eps0_trials(model, kin, q0, p0, smin, smax, ntry, nsteps, cnt):

@@ -48,6 +48,28 @@ def test_logp_and_grad_vs_float64(N, d, C):
     assert _rel(Vg, rg, 1.0) < 2e-5          # relative to the largest gradient entry
 
 
+def test_logp_and_grad_at_config4_size():
+    """BASELINE.json config 4's data size (N=100,000 rows, D=128) on a 256-chain slice: the fp32 accumulator of the
+    tensor core truncates, and that error grows with the number of rows summed before a drain -- only this size shows
+    whether the drain interval holds it."""
+    N, d, C = 100000, 128, 256
+    X, y = _data(N, d, 4)
+    s = pyhmc.HMC(models.LogisticRegression(X, y, 1.0), device=_dev())
+    th = (0.3 * np.random.default_rng(5).standard_normal((C, d))).astype(np.float32)
+    V, Vg = np.asarray(s.V(th), dtype=np.float64), np.asarray(s.V_g(th), dtype=np.float64)
+    X64, y64, t64 = X.astype(np.float64), y.astype(np.float64), th.astype(np.float64)
+    Z = t64 @ X64.T                                                    # [C, N]
+    rV = (np.logaddexp(0.0, Z) - Z * y64[None, :]).sum(axis=1) + 0.5 * (t64 * t64).sum(axis=1)
+    rg = (1.0 / (1.0 + np.exp(-Z)) - y64[None, :]) @ X64 + t64
+    om = omodels.LogisticRegression(X64[:2000], y64[:2000], 1.0)       # the closed forms above are the oracle's
+    assert abs(-om.log_prob(t64[0]) - ((np.logaddexp(0.0, Z[0, :2000]) - Z[0, :2000] * y64[:2000]).sum()
+                                       + 0.5 * (t64[0] ** 2).sum())) < 1e-8
+    eV, eg = _rel(V, rV, 1.0), _rel(Vg, rg, 1.0)
+    print("config-4 size: rel err of V %.3e, of grad V %.3e (of the largest entry)" % (eV, eg))
+    assert eV < 2e-6
+    assert eg < 2e-5
+
+
 def test_golden_transitions_within_1e5():
     g = np.load(os.path.join(HERE, "golden", "logit_hmc.npz"))
     spec = json.loads(str(g["spec"]))

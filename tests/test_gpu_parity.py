@@ -172,9 +172,9 @@ def test_drhmc_step_vs_oracle(kind, d, nleap, eps, nprops, f, lpc, monkeypatch):
     rcounts = np.array([r[4] for r in ref])
     assert np.array_equal(code, rcode), "stage codes differ: %s vs %s" % (code, rcode)
     assert np.array_equal(counts, rcounts)
-    _close(avec, np.array([r[3] for r in ref]), rtol=1e-8, atol=1e-12)
-    _close(q, np.array([r[0] for r in ref]), rtol=1e-9, atol=1e-10)
-    _close(p, np.array([r[1] for r in ref]), rtol=1e-9, atol=1e-10)
+    _close(avec, np.array([r[3] for r in ref]), rtol=1e-9, atol=1e-12)
+    _close(q, np.array([r[0] for r in ref]))      # north_star: 1e-10 relative (atol 1e-11)
+    _close(p, np.array([r[1] for r in ref]))
     if kind == "funnel" and nprops >= 3:
         assert len(set(rcode.tolist())) >= 3  # the case really exercises several stages
 
@@ -219,8 +219,24 @@ def test_leapfrog_and_energy_api_vs_oracle():
     _close(s.V(q0), np.array([-om.log_prob(x) for x in q0]), rtol=1e-12)
     _close(s.V_g(q0), np.array([-om.grad_log_prob(x) for x in q0]), rtol=1e-12, atol=1e-13)
     _close(s.H(q0, p0), np.array([-om.log_prob(x) + 0.5 * (y * y).sum() for x, y in zip(q0, p0)]), rtol=1e-12)
-    qa, pa, code, Hs = s.metropolis([q0, p0], [q1, p1], u=np.full(C, 0.5))
-    assert set(np.unique(code)) <= {0.0, 1.0, 2.0}
+    # standalone metropolis (src/pyhmc.py:50-61) against the rule restated in numpy on the oracle's energies:
+    # code 2 if prob is NaN/inf or sum(q0-q1) == 0, else reject iff u > min(1, prob)
+    q1n, p1n = np.asarray(q1), np.asarray(p1)
+    q1n[3], p1n[3] = q0[3], p0[3]                       # a proposal that did not move
+    q0 = q0.copy()
+    q0[5, 0] = -800.0                                   # exp(-v) overflows: H0 = inf, prob = inf
+    u = np.random.default_rng(6).random(C)
+    qa, pa, code, Hs = s.metropolis([q0, p0], [q1n, p1n], u=u)
+    with np.errstate(all="ignore"):
+        H0 = np.array([-om.log_prob(x) + 0.5 * (y * y).sum() for x, y in zip(q0, p0)])
+        H1 = np.array([-om.log_prob(x) + 0.5 * (y * y).sum() for x, y in zip(q1n, p1n)])
+        prob = np.exp(H0 - H1)
+    bad = np.isnan(prob) | np.isinf(prob) | ((q0 - q1n).sum(axis=1) == 0)
+    want = np.where(bad, 2.0, np.where(u > np.minimum(1.0, prob), 0.0, 1.0))
+    assert np.array_equal(code, want) and want[3] == 2.0 and want[5] == 2.0 and {0.0, 1.0} <= set(want.tolist())
+    acc = want == 1.0
+    assert np.array_equal(np.asarray(qa)[acc], q1n[acc]) and np.array_equal(np.asarray(qa)[~acc], q0[~acc])
+    _close(np.asarray(Hs)[~bad], np.stack([H0, H1], axis=1)[~bad], rtol=1e-12)
 
 
 def test_empty_batch_is_a_no_op():
@@ -264,6 +280,7 @@ def test_pyhmc_multistep_vs_oracle(kind, d, N, eps, m, fsub):
     ref = [samplers.multistep_step(om, m, q0[c], N, eps, fsub, replay.Draws([P[0, c]], U[0, c])) for c in range(C)]
     assert np.array_equal(code, [r[2] for r in ref])
     assert np.array_equal(counts, [r[4] for r in ref])
-    _close(avec, np.array([r[3] for r in ref]), rtol=1e-8, atol=1e-12)
-    _close(q, np.array([r[0] for r in ref]), rtol=1e-9, atol=1e-10)
+    _close(avec, np.array([r[3] for r in ref]), rtol=1e-9, atol=1e-12)
+    _close(q, np.array([r[0] for r in ref]))
+    _close(p, np.array([r[1] for r in ref]))
     assert code[0] == 0       # the u = 0 chain accepted at the first stage (<=)

@@ -137,6 +137,45 @@ def test_adapt_stepsize_bit_exact(capsys):
     assert _same(q_r, q_o) and ref.step_size == eps_o
 
 
+@pytest.mark.parametrize("epsadapt", [0, 6])
+def test_hmc_sample_bookkeeping_bit_exact(epsadapt, capsys):
+    """algorithms.HMC.sample (src/algorithms.py:233-254): accepts for every iteration, nsamples-1 stored rows."""
+    alg = ref_loader.load("algorithms")
+    model = models.Funnel(10)
+    ref = alg.HMC(model.log_prob, model.grad_log_prob)
+    ns, nb = 7, 4
+    T = ns + nb + (epsadapt + 1 if epsadapt else 0)
+    P, U = replay.make_draws(21, T, 1, model.d, 1)
+    q0 = _q0(model, 5)
+    with replay.patched_numpy_random(replay.Draws(list(P[:, 0]), U[:, 0, 0])):
+        st = ref.sample(q0, nsamples=ns, burnin=nb, step_size=0.1, nleap=8, epsadapt=epsadapt)
+    capsys.readouterr()
+    o = samplers.hmc_sample(model, q0, ns, nb, 0.1, 8, replay.Draws(list(P[:, 0]), U[:, 0, 0]), epsadapt=epsadapt)
+    assert st.samples.shape == (ns - 1, model.d) and st.accepts.shape == (ns + nb,) and st.i == o["i"] == ns + nb
+    assert _same(st.samples, o["samples"]) and _same(st.accepts, o["accepts"])
+    assert _same(st.Hs, o["Hs"]) and _same(st.counts, o["counts"])
+    assert ref.step_size == o["step_size"]
+
+
+def test_drhmc_sample_bookkeeping_bit_exact(capsys):
+    """algorithms.DRHMC.sample (src/algorithms.py:534-555): all nsamples+burnin rows, one unused leading normal."""
+    alg = ref_loader.load("algorithms")
+    model = models.Funnel(10)
+    ref = alg.DRHMC(model.log_prob, model.grad_log_prob)
+    ns, nb, nprops = 6, 3, 3
+    P, U = replay.make_draws(22, ns + nb + 1, 1, model.d, nprops)
+    q0 = _q0(model, 6)
+    # uniforms are consumed one per executed stage: hand both sides the same flat stream
+    with replay.patched_numpy_random(replay.Draws(list(P[:, 0]), U[:, 0].ravel())):
+        st = ref.sample(q0, nsamples=ns, burnin=nb, step_size=0.5, nleap=6, nprops=nprops, stepfactor=2)
+    capsys.readouterr()
+    o = samplers.drhmc_sample(model, q0, ns, nb, 0.5, 6, nprops, 2, replay.Draws(list(P[:, 0]), U[:, 0].ravel()))
+    assert st.samples.shape == (ns + nb, model.d) and st.avecs.shape == (ns + nb, nprops)
+    assert _same(st.samples, o["samples"]) and _same(st.accepts, o["accepts"])
+    assert _same(st.avecs, o["avecs"]) and _same(st.counts, o["counts"])
+    assert len(set(st.accepts.tolist())) >= 2
+
+
 @pytest.mark.parametrize("mi", [0, 3])
 def test_adhmc_eps0_bit_exact(mi):
     ad = ref_loader.load("adaptivehmc")

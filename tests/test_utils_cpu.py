@@ -49,7 +49,13 @@ def test_sampler_container():
     assert s.samples.shape == (2, 3) and s.counts.shape == (2, 3) and s.i == 2
     s.to_list()
     assert isinstance(s.samples, list)
-    assert set(algorithms.alg_dict) >= {"hmc", "drhmc"}
+    # the reference's registry keys (src/algorithms.py:823-832)
+    assert set(algorithms.alg_dict) == {"hmc", "ghmc", "pghmc", "drhmc", "drghmc", "pdrhmc_metrop", "pdrhmc_hasting"}
+    from oracle import ref_loader
+    if ref_loader.available():
+        ref = ref_loader.load("algorithms").alg_dict
+        assert set(ref) == set(algorithms.alg_dict)
+        assert all(ref[k].__name__ == algorithms.alg_dict[k].__name__ for k in ref)
 
 
 def test_shard_range_partitions():
