@@ -153,18 +153,20 @@ def test_headline_transition_without_injection_vs_oracle():
             "p_relerr_max": float(ep.max()), "p_relerr_median": float(np.median(ep))}
     ea = _relerr(avec[same], ravec[same])
     stats["avec_relerr_max"] = float(ea.max())
+    stats["avec_relerr_p99"] = float(np.quantile(ea, 0.99))
+    stats["avec_note"] = ("alpha = exp(H0 - Hj) * num / den carries the ABSOLUTE error of energies of size up to 1e5 in the "
+                          "neck of the funnel; |u - alpha| of the worst chain is far above it (no decision differs)")
     stats["code_fractions"] = [float((rcode == k).mean()) for k in range(nprops + 1)]
     _dump("headline_parity.json", stats)
     print(json.dumps(stats))
     assert len(stats["by_code"]) == nprops + 1, "the case must exercise every stage: %s" % stats["code_fractions"]
     # Rejected chains return q0 unchanged: exact.  Accepted chains carry the rounding differences of a 150- to
-    # 600-step trajectory (fused multiply-adds on the GPU, none in numpy) amplified by the funnel's dynamics:
-    # the bulk must sit at the 1e-10 bound of the short-trajectory tests, the worst chain within 1e-7.
+    # 600-step trajectory (fused multiply-adds on the GPU, none in numpy) amplified by the funnel's dynamics.
     assert stats["by_code"]["0"]["q_relerr_max"] == 0.0
     for k in range(1, nprops + 1):
         s = stats["by_code"][str(k)]
-        assert s["q_relerr_median"] < 1e-10, (k, s)
-        assert s["q_relerr_max"] < 1e-7, (k, s)
+        assert s["q_relerr_max"] < 1e-10, (k, s)       # measured: 6e-12 (stage 0), 2e-12, 7e-13
+        assert s["p_relerr_max"] < 1e-9, (k, s)        # measured: 1.5e-10 on one chain of 3053, median 3e-14
 
 
 # ------------------------------------------------------------------ error against trajectory length
@@ -180,12 +182,13 @@ def test_error_vs_trajectory_length_curve():
     kin = samplers.Kinetics()
     rows = []
     for mode in ("length30", "eps0.05"):
-        for L in (10, 20, 50, 150, 300, 600):
+        for L in ((150, 300, 600, 1200) if mode == "length30" else (10, 20, 50, 150, 300, 600)):
             eps = 30.0 / L if mode == "length30" else 0.05
             q1, p1 = s.leapfrog(q0, p0, L, eps)
             ref = [samplers.leapfrog(om, kin, q0[c], p0[c], L, eps, samplers.Counters()) for c in range(C)]
             rq, rp = np.array([r[0] for r in ref]), np.array([r[1] for r in ref])
             ok = np.isfinite(rq).all(axis=1) & np.isfinite(rp).all(axis=1) & (np.abs(rq).max(axis=1) < 1e6)
+            assert ok.sum() >= C // 4, "only %d of %d reference trajectories stay finite at L=%d eps=%g" % (ok.sum(), C, L, eps)
             e = np.maximum(_relerr(q1[ok], rq[ok]).max(axis=1), _relerr(p1[ok], rp[ok]).max(axis=1))
             rows.append({"mode": mode, "L": L, "eps": eps, "chains": int(ok.sum()),
                          "diverged_in_both": int(C - ok.sum()), "relerr_median": float(np.median(e)),
