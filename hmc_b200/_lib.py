@@ -46,6 +46,11 @@ class StepOut(C.Structure):
                 ("counts", C.c_void_p), ("accept_prob", C.c_void_p), ("ptries", C.c_void_p), ("p0_out", C.c_void_p)]
 
 
+class SampleIO(C.Structure):
+    _fields_ = [("n_transitions", C.c_int32), ("moment_sum", C.c_void_p), ("moment_sumsq", C.c_void_p),
+                ("n_accept", C.c_void_p)]
+
+
 class MalaIO(C.Structure):
     _fields_ = [("V_in", C.c_void_p), ("Vg_in", C.c_void_p), ("V_out", C.c_void_p), ("Vg_out", C.c_void_p),
                 ("code", C.c_void_p), ("n_accept", C.c_void_p), ("counts", C.c_void_p)]
@@ -83,6 +88,10 @@ SIGNATURES = {
     "hmcb_drhmc_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
                                   C.c_int32, C.c_double, C.c_int32, C.POINTER(StepOut), C.c_void_p, C.c_size_t,
                                   C.POINTER(Profile), C.c_void_p]),
+    "hmcb_drhmc_sample_workspace_bytes": (C.c_size_t, [C.POINTER(Model), C.c_int64, C.c_int32]),
+    "hmcb_drhmc_sample": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
+                                    C.c_int32, C.c_double, C.c_int32, C.POINTER(SampleIO), C.POINTER(StepOut),
+                                    C.c_void_p, C.c_size_t, C.c_void_p]),
     "hmcb_drhmc_step_static": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
                                          C.c_int32, C.c_double, C.c_int32, C.POINTER(StepOut), C.c_void_p]),
     "hmcb_moments_accumulate": (C.c_int, [C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_int64, C.c_int64,

@@ -255,6 +255,67 @@ static int drhmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* 
   return rc;
 }
 
+// ------------------------------------------------------------------ DR as tasks (dr_tasks.cuh)
+struct TaskLayout {
+  size_t off_ctrl, off_rings, off_iter, off_sti, off_stf, off_frames, total;
+};
+
+static void task_layout(const hmcb_model* m, int64_t n_chains, int nprops, TaskLayout& L) {
+  const size_t ts = m->dtype == HMCB_F64 ? 8 : 4;
+  const size_t np = (size_t)nprops;
+  size_t off = 0;
+  L.off_ctrl = off;   off = align_up(off + (2 + 2 * (np + 1)) * kCtrlStride * sizeof(int32_t), 256);
+  L.off_rings = off;  off = align_up(off + (np + 1) * (size_t)n_chains * sizeof(int32_t), 256);
+  L.off_iter = off;   off = align_up(off + (size_t)n_chains * sizeof(int32_t), 256);
+  L.off_sti = off;    off = align_up(off + (size_t)n_chains * (6 + 2 * np) * sizeof(int32_t), 256);
+  L.off_stf = off;    off = align_up(off + (size_t)n_chains * (2 * np + 2 * np * np) * ts, 256);
+  L.off_frames = off; off = align_up(off + (size_t)n_chains * (2 * np - 1) * (size_t)m->d * ts, 256);
+  L.total = off;
+}
+
+struct SampleIo {   // hmcb_sample_io with defaults for the single-transition call
+  int K;
+  void* msum;
+  void* msumsq;
+  int32_t* n_accept;
+};
+
+template <typename T>
+static int drhmc_tasks_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r, int n_leap,
+                         double eps, int nprops, double stepfactor, int conv, const SampleIo& io, const hmcb_step_out* o,
+                         void* ws, const TaskLayout& L, cudaStream_t st) {
+  TaskArgs<T> A;
+  memset(&A, 0, sizeof(A));
+  TransArgs<T>& a = A.t;
+  fill_args(a, m, c, r, o);
+  a.nprops = nprops;
+  a.dr_conv = conv != HMCB_DR_ALGORITHMS;
+  a.dr_prob = conv == HMCB_DR_PROB_METROP ? 1 : (conv == HMCB_DR_PROB_HASTINGS ? 2 : 0);
+  if (!a.dr_prob) a.ptries_out = nullptr;
+  for (int j = 0; j < nprops; ++j) {
+    const double fac = pow(stepfactor, (double)j);     // src/algorithms.py:510-511
+    a.L[j] = (int32_t)(n_leap * fac);
+    a.eps[j] = (T)(eps / fac);
+  }
+  A.K = io.K;
+  A.msum = (T*)io.msum;
+  A.msumsq = (T*)io.msumsq;
+  A.n_accept = io.n_accept;
+  char* w = (char*)ws;
+  A.ctrl = (int32_t*)(w + L.off_ctrl);
+  A.rings = (int32_t*)(w + L.off_rings);
+  A.ring_cap = (int32_t)c->n_chains;
+  A.iter = (int32_t*)(w + L.off_iter);
+  A.st_i = (int32_t*)(w + L.off_sti);
+  A.st_f = (T*)(w + L.off_stf);
+  A.frames = (T*)(w + L.off_frames);
+  HMCB_CUDA(cudaMemsetAsync(A.ctrl, 0, L.off_rings - L.off_ctrl, st));
+  // rings start empty (-1); ring nprops (chains entering a later transition) is only used with K > 1
+  HMCB_CUDA(cudaMemsetAsync(A.rings, 0xFF, (size_t)(nprops + (io.K > 1 ? 1 : 0)) * c->n_chains * sizeof(int32_t), st));
+  if (io.K > 1) HMCB_CUDA(cudaMemsetAsync(A.iter, 0, (size_t)c->n_chains * sizeof(int32_t), st));
+  return e->fn(*m, OP_DRTASK, &A, st);
+}
+
 template <typename T>
 static int mala_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r, double eps,
                        int n_steps, const hmcb_mala_io* io, cudaStream_t st) {
@@ -355,6 +416,15 @@ static int adwalk_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains*
 // any stream capture); they fork from and join back into the caller's stream through events, so
 // from the caller's side all work is still ordered on the stream it passed.
 constexpr int kMaxSplit = 4;
+
+// hmcb_drhmc_step runs the transition as tasks in one persistent kernel (dr_tasks.cuh) when HMCB_DR_TASKS=1 is set;
+// per-stage events (profile) only make sense for the staged form
+static bool dr_use_tasks(int64_t n_chains, const hmcb_profile* prof) {
+  (void)n_chains;
+  if (prof) return false;
+  const char* e = getenv("HMCB_DR_TASKS");
+  return e && atoi(e) != 0;
+}
 
 static int dr_split_for(int64_t n_chains, const hmcb_profile* prof) {
   if (prof) return 1;                       // per-stage events want the stages one after another
@@ -564,7 +634,56 @@ size_t hmcb_drhmc_workspace_bytes(const hmcb_model* model, int64_t n_chains, int
     if (dr_layout(e, model, split_bound(n_chains, S, i + 1) - split_bound(n_chains, S, i), nprops, L)) return 0;
     total += L.total;
   }
+  if (dr_use_tasks(n_chains, nullptr)) {
+    TaskLayout TL;
+    task_layout(model, n_chains, nprops, TL);
+    if (TL.total > total) total = TL.total;
+  }
   return total;
+}
+
+size_t hmcb_drhmc_sample_workspace_bytes(const hmcb_model* model, int64_t n_chains, int32_t nprops) {
+  if (check_model(model)) return 0;
+  if (n_chains < 1 || nprops < 1 || nprops > kMaxProps) {
+    set_error("workspace query: n_chains=%lld nprops=%d out of range (nprops <= %d)", (long long)n_chains, nprops, kMaxProps);
+    return 0;
+  }
+  TaskLayout TL;
+  task_layout(model, n_chains, nprops, TL);
+  return TL.total;
+}
+
+int hmcb_drhmc_sample(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
+                      double step_size, int32_t nprops, double stepfactor, int32_t convention, const hmcb_sample_io* io,
+                      const hmcb_step_out* out, void* workspace, size_t workspace_bytes, void* stream) {
+  int rc;
+  if ((rc = check_model(model))) return rc;
+  if ((rc = check_chains(chains))) return rc;
+  HMCB_CHECK_ARG(rng != nullptr && io != nullptr, "rng/io is NULL");
+  HMCB_CHECK_ARG(nprops >= 1 && nprops <= kMaxProps, "nprops=%d must be in 1..%d", nprops, kMaxProps);
+  HMCB_CHECK_ARG(stepfactor > 0, "stepfactor must be > 0");
+  HMCB_CHECK_ARG(convention >= HMCB_DR_ALGORITHMS && convention <= HMCB_DR_PROB_HASTINGS, "unknown DR convention %d", convention);
+  HMCB_CHECK_ARG(n_leap >= 0, "n_leap must be >= 0");
+  HMCB_CHECK_ARG(io->n_transitions >= 1, "n_transitions must be >= 1");
+  HMCB_CHECK_ARG(io->n_transitions == 1 || (!rng->p_inject && !rng->u_inject && !rng->p_prev),
+                 "injected draws and a partial momentum refresh are defined for n_transitions == 1 only");
+  HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= dr_uniforms(nprops, convention),
+                 "u_inject needs u_stride >= %d for nprops=%d under convention %d", dr_uniforms(nprops, convention), nprops, convention);
+  HMCB_CHECK_ARG((io->moment_sum == nullptr) == (io->moment_sumsq == nullptr), "give both moment_sum and moment_sumsq or neither");
+  if (chains->n_chains == 0) return 0;
+  const Entry* e = choose_entry(*model);
+  if (!e) return HMCB_E_UNSUPPORTED;
+  TaskLayout TL;
+  task_layout(model, chains->n_chains, nprops, TL);
+  if (!workspace || workspace_bytes < TL.total) {
+    set_error("drhmc sample workspace too small: have %zu bytes, need %zu", workspace ? workspace_bytes : (size_t)0, TL.total);
+    return HMCB_E_WORKSPACE;
+  }
+  const SampleIo sio{io->n_transitions, io->moment_sum, io->moment_sumsq, io->n_accept};
+  cudaStream_t st = (cudaStream_t)stream;
+  if (model->dtype == HMCB_F64)
+    return drhmc_tasks_t<double>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, convention, sio, out, workspace, TL, st);
+  return drhmc_tasks_t<float>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, convention, sio, out, workspace, TL, st);
 }
 
 int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
@@ -583,6 +702,20 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
   if (chains->n_chains == 0) return 0;
   const Entry* e = choose_entry(*model);
   if (!e) return HMCB_E_UNSUPPORTED;
+  if (dr_use_tasks(chains->n_chains, profile)) {
+    TaskLayout TL;
+    task_layout(model, chains->n_chains, nprops, TL);
+    if (!workspace || workspace_bytes < TL.total) {
+      set_error("drhmc workspace too small: have %zu bytes, need %zu", workspace ? workspace_bytes : (size_t)0, TL.total);
+      return HMCB_E_WORKSPACE;
+    }
+    const SampleIo sio{1, nullptr, nullptr, nullptr};
+    if (model->dtype == HMCB_F64)
+      return drhmc_tasks_t<double>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, convention, sio, out,
+                                   workspace, TL, (cudaStream_t)stream);
+    return drhmc_tasks_t<float>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, convention, sio, out,
+                                workspace, TL, (cudaStream_t)stream);
+  }
   // the workspace is always sized for the un-profiled call (hmcb_drhmc_workspace_bytes), which is the larger one
   const int S = dr_split_for(chains->n_chains, profile);
   DrLayout L[kMaxSplit];

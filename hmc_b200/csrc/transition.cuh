@@ -199,11 +199,11 @@ __device__ __forceinline__ float mix_momentum(float alpha, float pv, float beta,
 // momentum p = z * metricstd, z ~ N(0,1) (src/pyhmc.py:66); z from Philox or injected
 template <typename T, int EPL, int LPC, bool UNITM>
 __device__ __forceinline__ void draw_momentum(T (&p)[EPL], const TransArgs<T>& a, const T (&minv)[UNITM ? 1 : EPL],
-                                              int64_t chain, int lane, int d) {
+                                              int64_t chain, int lane, int d, uint32_t iter_add = 0) {
   if (a.p_inject) {
     load_vec<T, EPL, LPC>(p, a.p_inject, chain * a.sc, a.sd, lane, d, T(1));
   } else {
-    fill_normals<T, EPL, LPC>(p, a.seed, (uint64_t)(a.chain_offset + chain), a.iteration, lane, d, a.rng_flags);
+    fill_normals<T, EPL, LPC>(p, a.seed, (uint64_t)(a.chain_offset + chain), a.iteration + iter_add, lane, d, a.rng_flags);
   }
   if (!UNITM) {
 #pragma unroll
@@ -219,10 +219,10 @@ __device__ __forceinline__ void draw_momentum(T (&p)[EPL], const TransArgs<T>& a
 }
 
 template <typename T>
-__device__ __forceinline__ double draw_uniform(const TransArgs<T>& a, int64_t chain, int idx) {
+__device__ __forceinline__ double draw_uniform(const TransArgs<T>& a, int64_t chain, int idx, uint32_t iter_add = 0) {
   if (a.u_inject) return a.u_inject[chain * a.u_stride + idx];
   uint32_t w[4];
-  Philox::gen(a.seed, (uint64_t)(a.chain_offset + chain), a.iteration, STREAM_ACCEPT, (uint32_t)(idx >> 1), w);
+  Philox::gen(a.seed, (uint64_t)(a.chain_offset + chain), a.iteration + iter_add, STREAM_ACCEPT, (uint32_t)(idx >> 1), w);
   return (idx & 1) ? u53(w[2], w[3]) : u53(w[0], w[1]);
 }
 

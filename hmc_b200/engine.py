@@ -233,6 +233,45 @@ class Engine:
         out["_keep"] = keep
         return out
 
+    def drhmc_sample(self, q, n_leap, step_size, nprops, stepfactor, n_transitions, msum=None, msumsq=None,
+                     n_accept=None, q_out=None, want_p=False, convention=0, code_out=None, counts_out=None,
+                     want_avec=True, p=None, u=None):
+        """hmcb_drhmc_sample on device tensor q [C,d]: n_transitions DR transitions of every chain in one launch,
+        running moments folded into msum / msumsq ([C,d], updated in place) when given.  Returns the state after the
+        last transition, the last transition's code / avec, and the work counters summed over the transitions."""
+        m = self._ensure()
+        C_ = q.shape[0]
+        with torch.cuda.device(self.device):
+            need = self.lib.hmcb_drhmc_sample_workspace_bytes(C.byref(m), C_, int(nprops))
+            if need == 0:
+                _lib.check(_lib.E_ARG)
+            ws = self._ws_pool.get("sample")
+            if ws is None or ws.numel() < need:
+                ws = self._ws_pool["sample"] = torch.empty(need, dtype=torch.uint8, device=self.device)
+            q_out = torch.empty_like(q) if q_out is None else q_out
+            out = {"q": q_out, "p": torch.empty_like(q) if want_p else None,
+                   "code": torch.empty(C_, dtype=torch.int32, device=self.device) if code_out is None else code_out,
+                   "avec": torch.empty((C_, nprops), dtype=self.dtype, device=self.device) if want_avec else None,
+                   "counts": torch.empty((C_, 3), dtype=torch.int32, device=self.device)
+                   if counts_out is None else counts_out}
+            prob = convention in (_lib.DR_PROB_METROP, _lib.DR_PROB_HASTINGS)
+            if prob:
+                out["ptries"] = torch.empty((C_, nprops), dtype=self.dtype, device=self.device)
+            so = _lib.StepOut()
+            so.p_out, so.code, so.avec = _lib.ptr(out["p"]), _lib.ptr(out["code"]), _lib.ptr(out["avec"])
+            so.counts, so.ptries = _lib.ptr(out["counts"]), _lib.ptr(out.get("ptries"))
+            io = _lib.SampleIO()
+            io.n_transitions = int(n_transitions)
+            io.moment_sum, io.moment_sumsq, io.n_accept = _lib.ptr(msum), _lib.ptr(msumsq), _lib.ptr(n_accept)
+            ch = self._chains(q, q_out)
+            r, keep = self._rng(p, u, 2 * nprops - 1 if prob else nprops, C_)
+            _lib.check(self.lib.hmcb_drhmc_sample(C.byref(m), C.byref(ch), C.byref(r), int(n_leap), float(step_size),
+                                                  int(nprops), float(stepfactor), int(convention), C.byref(io),
+                                                  C.byref(so), C.c_void_p(ws.data_ptr()), ws.numel(), self._stream()))
+        self.iteration += int(n_transitions)
+        out["_keep"] = keep
+        return out
+
     def drhmc_step_host(self, q_host, n_leap, step_size, nprops, stepfactor, want_p=True, n_chunks=8, run_streams=2):
         """One DR transition for chain state living in HOST memory.  The batch is cut into
         chunks of chains that flow through a copy-in stream, two compute streams and a copy-out

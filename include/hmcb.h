@@ -168,6 +168,31 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
                     const hmcb_step_out* out, void* workspace, size_t workspace_bytes,
                     const hmcb_profile* profile /* may be NULL */, void* stream);
 
+/* K delayed-rejection transitions of every chain in ONE launch: the loop of DRHMC.sample
+ * (src/algorithms.py:542-552; scripts_old/funnel/funnelmpi_multistep.py runs the same loop over
+ * PyHMC_multistep.multi_step) with the chain state kept on the device.  Each transition is
+ * hmcb_drhmc_step's, bit for bit (transition k of a chain draws with iteration rng->iteration + k);
+ * chains advance independently inside one persistent kernel that schedules single leapfrog
+ * trajectories (hmc_b200/csrc/dr_tasks.cuh), so nothing waits for the slowest chain between
+ * transitions.  The reference keeps every sample (state.samples, :548); at 2^20 chains that does
+ * not fit, so the running moments the diagnostics need are folded in instead: after every
+ * transition moment_sum += q, moment_sumsq += q*q (contiguous [C,d], model dtype; as
+ * hmcb_moments_accumulate).  out: code / avec / ptries / p_out / p0_out of the LAST transition,
+ * counts summed over the K transitions; n_accept[c] += transitions accepted at any stage.
+ * Injected draws and p_prev need n_transitions == 1.  Workspace: hmcb_drhmc_sample_workspace_bytes()
+ * (per-chain scratch: (2 nprops - 1) d + O(nprops^2) values per chain). */
+typedef struct hmcb_sample_io {
+  int32_t n_transitions;      /* K >= 1 */
+  void* moment_sum;           /* [C,d] or NULL (both or neither) */
+  void* moment_sumsq;         /* [C,d] or NULL */
+  int32_t* n_accept;          /* [C] or NULL */
+} hmcb_sample_io;
+size_t hmcb_drhmc_sample_workspace_bytes(const hmcb_model* model, int64_t n_chains, int32_t nprops);
+int hmcb_drhmc_sample(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng,
+                      int32_t n_leap, double step_size, int32_t nprops, double stepfactor, int32_t convention,
+                      const hmcb_sample_io* io, const hmcb_step_out* out, void* workspace, size_t workspace_bytes,
+                      void* stream);
+
 /* hmcb_drhmc_step without a caller-supplied workspace.  No counterpart in the
  * reference (its Python never manages device memory); added for hosts that cannot
  * give us scratch: a thin C / ctypes caller that only holds the q and output buffers

@@ -1,0 +1,140 @@
+"""Delayed rejection as per-trajectory tasks in one persistent kernel (csrc/dr_tasks.cuh,
+hmcb_drhmc_sample) against the staged kernels (hmcb_drhmc_step, one kernel per stage), which the
+oracle and golden tests pin to algorithms.DRHMC.step / get_num (src/algorithms.py:474-530) and
+PyHMC_multistep / the probabilistic classes: every per-chain output must be IDENTICAL, bit for
+bit, for every convention, kernel shape and number of stages, with replayed and with Philox draws;
+K transitions in one launch must equal K single calls; and the folded running moments must equal
+hmcb_moments_accumulate's."""
+import numpy as np
+import pytest
+import torch
+
+from hmc_b200 import _lib, algorithms, models
+from oracle import models as omodels
+from oracle import replay, samplers
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    assert torch.cuda.is_available()
+    return torch.device("cuda:0")
+
+
+def _model(kind, d):
+    return {"funnel": lambda: models.Funnel(d), "rosenbrock": lambda: models.Rosenbrock(d),
+            "gaussian": lambda: models.CorrGaussian.ar1(d)}[kind]()
+
+
+def _q0(kind, C, d, seed):
+    rng = np.random.default_rng(seed)
+    if kind == "funnel":
+        v = 1.5 * rng.standard_normal((C, 1))
+        return np.concatenate([v, np.exp(v / 2) * rng.standard_normal((C, d - 1))], axis=1)
+    q = rng.uniform(-1, 1, (C, d))
+    return 1.0 + 0.1 * q if kind == "rosenbrock" else q
+
+
+def _same(a, b, keys):
+    for k in keys:
+        if a.get(k) is None and b.get(k) is None:
+            continue
+        assert torch.equal(a[k], b[k]), "%s differs: %d of %d entries" % (k, (a[k] != b[k]).sum().item(), a[k].numel())
+
+
+@pytest.mark.parametrize("kind,d,nleap,eps", [("funnel", 10, 6, 0.6), ("funnel", 50, 10, 0.35), ("rosenbrock", 10, 8, 0.1),
+                                              ("gaussian", 12, 6, 0.9)])
+@pytest.mark.parametrize("nprops,f", [(1, 2.0), (2, 2.0), (3, 2.0), (4, 1.5), (5, 1.3)])
+@pytest.mark.parametrize("conv", [_lib.DR_ALGORITHMS, _lib.DR_MULTISTEP, _lib.DR_PROB_METROP, _lib.DR_PROB_HASTINGS])
+@pytest.mark.parametrize("lpc", [0, 8])
+def test_tasks_equal_stages_with_replayed_draws(kind, d, nleap, eps, nprops, f, conv, lpc, monkeypatch):
+    if lpc:
+        monkeypatch.setenv("HMCB_LPC", str(lpc))
+    else:
+        monkeypatch.delenv("HMCB_LPC", raising=False)
+    C = 77
+    q0 = torch.as_tensor(_q0(kind, C, d, 3 * nprops + d), device=_dev())
+    P, U = replay.make_draws(500 + d + nprops, 1, C, d, 2 * nprops - 1)
+    e = algorithms.DRHMC(_model(kind, d), device=_dev()).engine
+    a = e.drhmc_step(q0, nleap, eps, nprops, f, p=P[0], u=U[0], convention=conv, want_p0=True)
+    b = e.drhmc_sample(q0, nleap, eps, nprops, f, 1, p=P[0], u=U[0], convention=conv, want_p=True)
+    _same(a, b, ("q", "p", "code", "avec", "counts", "ptries"))
+    if nprops >= 3 and kind == "funnel":
+        assert len(set(a["code"].tolist())) >= 3
+
+
+@pytest.mark.parametrize("conv", [_lib.DR_ALGORITHMS, _lib.DR_PROB_HASTINGS])
+@pytest.mark.parametrize("C", [1, 31, 4096 + 5, 70001])
+def test_tasks_equal_stages_with_philox_draws(conv, C):
+    d = 50
+    q0 = torch.as_tensor(_q0("funnel", C, d, 5), device=_dev())
+    a = algorithms.DRHMC(models.Funnel(d), device=_dev(), seed=9, chain_offset=123).engine
+    b = algorithms.DRHMC(models.Funnel(d), device=_dev(), seed=9, chain_offset=123).engine
+    ra = a.drhmc_step(q0, 12, 0.3, 3, 2.0, convention=conv)
+    rb = b.drhmc_sample(q0, 12, 0.3, 3, 2.0, 1, convention=conv, want_p=True)
+    _same(ra, rb, ("q", "p", "code", "avec", "counts", "ptries"))
+
+
+def test_tasks_match_the_oracle_directly():
+    """Not only equal to the staged kernels: the task kernel against oracle.samplers.drhmc_step itself."""
+    d, C, nleap, eps, nprops, f = 50, 200, 10, 0.35, 3, 2.0
+    om = omodels.Funnel(d)
+    q0 = _q0("funnel", C, d, 8)
+    P, U = replay.make_draws(77, 1, C, d, nprops)
+    e = algorithms.DRHMC(models.Funnel(d), device=_dev()).engine
+    out = e.drhmc_sample(torch.as_tensor(q0, device=_dev()), nleap, eps, nprops, f, 1, p=P[0], u=U[0], want_p=True)
+    ref = [samplers.drhmc_step(om, q0[c], nleap, eps, nprops, f, replay.Draws([P[0, c]], U[0, c])) for c in range(C)]
+    assert np.array_equal(out["code"].cpu().numpy(), [r[2] for r in ref])
+    assert np.array_equal(out["counts"].cpu().numpy(), [r[4] for r in ref])
+    assert np.allclose(out["q"].cpu().numpy(), np.array([r[0] for r in ref]), rtol=1e-10, atol=1e-11)
+    assert np.allclose(out["p"].cpu().numpy(), np.array([r[1] for r in ref]), rtol=1e-10, atol=1e-11)
+
+
+@pytest.mark.parametrize("kind,d,lpc", [("funnel", 50, 0), ("funnel", 10, 0), ("funnel", 50, 4), ("rosenbrock", 20, 0)])
+@pytest.mark.parametrize("conv", [_lib.DR_ALGORITHMS, _lib.DR_PROB_METROP])
+def test_k_transitions_in_one_launch_equal_k_single_calls(kind, d, lpc, conv, monkeypatch):
+    if lpc:
+        monkeypatch.setenv("HMCB_LPC", str(lpc))
+    else:
+        monkeypatch.delenv("HMCB_LPC", raising=False)
+    C, K, nleap, eps, nprops, f = 5000, 6, 7, (0.4 if kind == "funnel" else 0.08), 3, 2.0
+    dev = _dev()
+    q0 = torch.as_tensor(_q0(kind, C, d, 11), device=dev)
+    a = algorithms.DRHMC(_model(kind, d), device=dev, seed=21, chain_offset=7).engine
+    b = algorithms.DRHMC(_model(kind, d), device=dev, seed=21, chain_offset=7).engine
+    a.iteration = b.iteration = 40
+    q = q0
+    s1, s2 = torch.zeros_like(q0), torch.zeros_like(q0)
+    counts = torch.zeros((C, 3), dtype=torch.int32, device=dev)
+    nacc = torch.zeros(C, dtype=torch.int32, device=dev)
+    for k in range(K):
+        r = a.drhmc_step(q, nleap, eps, nprops, f, convention=conv)
+        q = r["q"]
+        a.moments_accumulate(q, s1, s2)
+        counts += r["counts"]
+        nacc += (r["code"] >= (0 if conv else 1)).int()
+    t1, t2 = torch.zeros_like(q0), torch.zeros_like(q0)
+    macc = torch.zeros(C, dtype=torch.int32, device=dev)
+    rb = b.drhmc_sample(q0, nleap, eps, nprops, f, K, msum=t1, msumsq=t2, n_accept=macc, convention=conv, want_p=True)
+    assert b.iteration == a.iteration == 40 + K
+    assert torch.equal(rb["q"], q) and torch.equal(rb["code"], r["code"]) and torch.equal(rb["avec"], r["avec"])
+    assert torch.equal(rb["p"], r["p"])
+    assert torch.equal(rb["counts"], counts) and torch.equal(macc, nacc)
+    assert torch.equal(t1, s1) and torch.equal(t2, s2)
+    assert (q != q0).any(dim=1).float().mean().item() > 0.5
+
+
+def test_in_place_and_repeated_launches():
+    """q_out == q_in, and the scratch of one launch does not leak into the next."""
+    d, C = 50, 9000
+    dev = _dev()
+    q0 = torch.as_tensor(_q0("funnel", C, d, 13), device=dev)
+    a = algorithms.DRHMC(models.Funnel(d), device=dev, seed=1).engine
+    b = algorithms.DRHMC(models.Funnel(d), device=dev, seed=1).engine
+    ref = a.drhmc_sample(q0, 9, 0.3, 3, 2.0, 4)
+    ref2 = a.drhmc_sample(ref["q"], 9, 0.3, 3, 2.0, 3)
+    q = q0.clone()
+    b.drhmc_sample(q, 9, 0.3, 3, 2.0, 4, q_out=q)
+    assert torch.equal(q, ref["q"])
+    out = b.drhmc_sample(q, 9, 0.3, 3, 2.0, 3, q_out=q)
+    assert torch.equal(q, ref2["q"]) and torch.equal(out["counts"], ref2["counts"])

@@ -147,3 +147,41 @@ def test_leapfrog_Vgq_and_V_vandg_standalone():
             for a, b in zip(out, ref):
                 assert np.allclose(np.asarray(a[c], dtype=float), np.asarray(b, dtype=float), rtol=1e-10, atol=1e-11)
     assert np.array_equal(s.unit_norm_KE(p0), 0.5 * (p0 ** 2).sum(axis=1)) or np.allclose(s.unit_norm_KE(p0), 0.5 * (p0 ** 2).sum(axis=1), rtol=1e-14)
+
+
+def test_gaussian_partial_refresh_reaches_the_generic_kernel(monkeypatch):
+    """hmcb_hmc_step with rng->p_prev on the f64 dense Gaussian: the tensor-path kernel only draws a full refresh,
+    so the call must be served by the generic kernel -- same result as with HMCB_GAUSS_GENERIC=1, and the momentum
+    really is alpha*p_prev + sqrt(1-alpha^2)*draw."""
+    import ctypes as C
+    from hmc_b200 import _lib
+    d, n, alpha = 20, 257, 0.8
+    dev = torch.device("cuda:0")
+    s = algorithms.HMC(models.CorrGaussian.ar1(d), device=dev, seed=5)
+    e = s.engine
+    m = e._ensure()
+    g = torch.Generator().manual_seed(0)
+    q = torch.randn(n, d, generator=g, dtype=torch.float64).to(dev)
+    pv = torch.randn(n, d, generator=g, dtype=torch.float64).to(dev)
+    res = []
+    for generic in ("", "1"):
+        if generic:
+            monkeypatch.setenv("HMCB_GAUSS_GENERIC", "1")
+        else:
+            monkeypatch.delenv("HMCB_GAUSS_GENERIC", raising=False)
+        qo, p0 = torch.empty_like(q), torch.empty_like(q)
+        so = _lib.StepOut()
+        so.p0_out = _lib.ptr(p0)
+        r, keep = e._rng(None, None, 1, n, p_prev=pv, alpha=alpha)
+        _lib.check(e.lib.hmcb_hmc_step(C.byref(m), C.byref(e._chains(q, qo)), C.byref(r), 5, 0.1, _lib.RULE_ALG,
+                                       C.byref(so), e._stream()))
+        # the same call with a full refresh gives the plain draw
+        z, so2 = torch.empty_like(q), _lib.StepOut()
+        so2.p0_out = _lib.ptr(z)
+        r2, _ = e._rng(None, None, 1, n)
+        _lib.check(e.lib.hmcb_hmc_step(C.byref(m), C.byref(e._chains(q, torch.empty_like(q))), C.byref(r2), 5, 0.1,
+                                       _lib.RULE_ALG, C.byref(so2), e._stream()))
+        torch.cuda.synchronize()
+        assert torch.equal(p0, alpha * pv + np.sqrt(1 - alpha ** 2) * z)
+        res.append((qo, p0))
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])

@@ -179,3 +179,22 @@ def test_get_stepsize_standalone_vs_oracle():
         want = steps[isx] + (steps[isx + 1] - steps[isx]) * U[c, 1]
         assert np.isclose(ss[c], want, rtol=1e-12) and np.isclose(prob[c], pp[isx + 1], rtol=1e-9)
         assert np.isclose(pe[c], pp[np.where(steps > 0.1)[0][0]], rtol=1e-9)
+
+
+def test_mala_cached_potential_without_cached_gradient():
+    """V_q and V_gq are cached independently in the reference (src/mala.py:49-52): a step given V_q but not V_gq must
+    use that V_q (and evaluate the gradient itself) -- the result equals the step given both, or neither."""
+    d, C = 10, 33
+    pm, om = models.Funnel(d), omodels.Funnel(d)
+    q0 = np.random.default_rng(3).uniform(-1, 1, (C, d))
+    P, U = replay.make_draws(8, 1, C, d, 1)
+    s = mala.MALA(pm, device=_dev())
+    V = s.V(q0)
+    full = s.step(q0, 0.05, V, s.V_g(q0), z=P[0], u=U[0])
+    only_v = s.step(q0, 0.05, V, None, z=P[0], u=U[0])
+    none = s.step(q0, 0.05, None, None, z=P[0], u=U[0])
+    for a, b, c in zip(full, only_v, none):
+        assert np.array_equal(a, b) and np.array_equal(a, c)
+    ref = [samplers.mala_step(om, q0[c], 0.05, replay.Draws([P[0, c]], U[0, c]), float(V[c]), None) for c in range(C)]
+    assert np.array_equal(only_v[1], [r[1] for r in ref])
+    _close(only_v[0], np.array([r[0] for r in ref]))
