@@ -255,67 +255,6 @@ static int drhmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* 
   return rc;
 }
 
-// ------------------------------------------------------------------ DR as tasks (dr_tasks.cuh)
-struct TaskLayout {
-  size_t off_ctrl, off_rings, off_iter, off_sti, off_stf, off_frames, total;
-};
-
-static void task_layout(const hmcb_model* m, int64_t n_chains, int nprops, TaskLayout& L) {
-  const size_t ts = m->dtype == HMCB_F64 ? 8 : 4;
-  const size_t np = (size_t)nprops;
-  size_t off = 0;
-  L.off_ctrl = off;   off = align_up(off + (2 + 2 * (np + 1)) * kCtrlStride * sizeof(int32_t), 256);
-  L.off_rings = off;  off = align_up(off + (np + 1) * (size_t)n_chains * sizeof(int32_t), 256);
-  L.off_iter = off;   off = align_up(off + (size_t)n_chains * sizeof(int32_t), 256);
-  L.off_sti = off;    off = align_up(off + (size_t)n_chains * (6 + 2 * np) * sizeof(int32_t), 256);
-  L.off_stf = off;    off = align_up(off + (size_t)n_chains * (2 * np + 2 * np * np) * ts, 256);
-  L.off_frames = off; off = align_up(off + (size_t)n_chains * (2 * np - 1) * (size_t)m->d * ts, 256);
-  L.total = off;
-}
-
-struct SampleIo {   // hmcb_sample_io with defaults for the single-transition call
-  int K;
-  void* msum;
-  void* msumsq;
-  int32_t* n_accept;
-};
-
-template <typename T>
-static int drhmc_tasks_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r, int n_leap,
-                         double eps, int nprops, double stepfactor, int conv, const SampleIo& io, const hmcb_step_out* o,
-                         void* ws, const TaskLayout& L, cudaStream_t st) {
-  TaskArgs<T> A;
-  memset(&A, 0, sizeof(A));
-  TransArgs<T>& a = A.t;
-  fill_args(a, m, c, r, o);
-  a.nprops = nprops;
-  a.dr_conv = conv != HMCB_DR_ALGORITHMS;
-  a.dr_prob = conv == HMCB_DR_PROB_METROP ? 1 : (conv == HMCB_DR_PROB_HASTINGS ? 2 : 0);
-  if (!a.dr_prob) a.ptries_out = nullptr;
-  for (int j = 0; j < nprops; ++j) {
-    const double fac = pow(stepfactor, (double)j);     // src/algorithms.py:510-511
-    a.L[j] = (int32_t)(n_leap * fac);
-    a.eps[j] = (T)(eps / fac);
-  }
-  A.K = io.K;
-  A.msum = (T*)io.msum;
-  A.msumsq = (T*)io.msumsq;
-  A.n_accept = io.n_accept;
-  char* w = (char*)ws;
-  A.ctrl = (int32_t*)(w + L.off_ctrl);
-  A.rings = (int32_t*)(w + L.off_rings);
-  A.ring_cap = (int32_t)c->n_chains;
-  A.iter = (int32_t*)(w + L.off_iter);
-  A.st_i = (int32_t*)(w + L.off_sti);
-  A.st_f = (T*)(w + L.off_stf);
-  A.frames = (T*)(w + L.off_frames);
-  HMCB_CUDA(cudaMemsetAsync(A.ctrl, 0, L.off_rings - L.off_ctrl, st));
-  // rings start empty (-1); ring nprops (chains entering a later transition) is only used with K > 1
-  HMCB_CUDA(cudaMemsetAsync(A.rings, 0xFF, (size_t)(nprops + (io.K > 1 ? 1 : 0)) * c->n_chains * sizeof(int32_t), st));
-  if (io.K > 1) HMCB_CUDA(cudaMemsetAsync(A.iter, 0, (size_t)c->n_chains * sizeof(int32_t), st));
-  return e->fn(*m, OP_DRTASK, &A, st);
-}
-
 template <typename T>
 static int mala_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r, double eps,
                        int n_steps, const hmcb_mala_io* io, cudaStream_t st) {
@@ -415,16 +354,7 @@ static int adwalk_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains*
 // global chain id).  The helper streams belong to the library (created once per device, outside
 // any stream capture); they fork from and join back into the caller's stream through events, so
 // from the caller's side all work is still ordered on the stream it passed.
-constexpr int kMaxSplit = 4;
-
-// hmcb_drhmc_step runs the transition as tasks in one persistent kernel (dr_tasks.cuh) when HMCB_DR_TASKS=1 is set;
-// per-stage events (profile) only make sense for the staged form
-static bool dr_use_tasks(int64_t n_chains, const hmcb_profile* prof) {
-  (void)n_chains;
-  if (prof) return false;
-  const char* e = getenv("HMCB_DR_TASKS");
-  return e && atoi(e) != 0;
-}
+constexpr int kMaxSplit = 8;
 
 static int dr_split_for(int64_t n_chains, const hmcb_profile* prof) {
   if (prof) return 1;                       // per-stage events want the stages one after another
@@ -443,6 +373,7 @@ struct HelperStreams {
   cudaEvent_t fork, join[kMaxSplit - 1];
 };
 static std::mutex g_helper_mu;
+static std::mutex g_seq_mu;   // serialises the enqueueing of calls that use the per-device fork/join events
 static HelperStreams g_helpers[64];
 
 static int helper_streams(HelperStreams** out) {
@@ -634,56 +565,7 @@ size_t hmcb_drhmc_workspace_bytes(const hmcb_model* model, int64_t n_chains, int
     if (dr_layout(e, model, split_bound(n_chains, S, i + 1) - split_bound(n_chains, S, i), nprops, L)) return 0;
     total += L.total;
   }
-  if (dr_use_tasks(n_chains, nullptr)) {
-    TaskLayout TL;
-    task_layout(model, n_chains, nprops, TL);
-    if (TL.total > total) total = TL.total;
-  }
   return total;
-}
-
-size_t hmcb_drhmc_sample_workspace_bytes(const hmcb_model* model, int64_t n_chains, int32_t nprops) {
-  if (check_model(model)) return 0;
-  if (n_chains < 1 || nprops < 1 || nprops > kMaxProps) {
-    set_error("workspace query: n_chains=%lld nprops=%d out of range (nprops <= %d)", (long long)n_chains, nprops, kMaxProps);
-    return 0;
-  }
-  TaskLayout TL;
-  task_layout(model, n_chains, nprops, TL);
-  return TL.total;
-}
-
-int hmcb_drhmc_sample(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
-                      double step_size, int32_t nprops, double stepfactor, int32_t convention, const hmcb_sample_io* io,
-                      const hmcb_step_out* out, void* workspace, size_t workspace_bytes, void* stream) {
-  int rc;
-  if ((rc = check_model(model))) return rc;
-  if ((rc = check_chains(chains))) return rc;
-  HMCB_CHECK_ARG(rng != nullptr && io != nullptr, "rng/io is NULL");
-  HMCB_CHECK_ARG(nprops >= 1 && nprops <= kMaxProps, "nprops=%d must be in 1..%d", nprops, kMaxProps);
-  HMCB_CHECK_ARG(stepfactor > 0, "stepfactor must be > 0");
-  HMCB_CHECK_ARG(convention >= HMCB_DR_ALGORITHMS && convention <= HMCB_DR_PROB_HASTINGS, "unknown DR convention %d", convention);
-  HMCB_CHECK_ARG(n_leap >= 0, "n_leap must be >= 0");
-  HMCB_CHECK_ARG(io->n_transitions >= 1, "n_transitions must be >= 1");
-  HMCB_CHECK_ARG(io->n_transitions == 1 || (!rng->p_inject && !rng->u_inject && !rng->p_prev),
-                 "injected draws and a partial momentum refresh are defined for n_transitions == 1 only");
-  HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= dr_uniforms(nprops, convention),
-                 "u_inject needs u_stride >= %d for nprops=%d under convention %d", dr_uniforms(nprops, convention), nprops, convention);
-  HMCB_CHECK_ARG((io->moment_sum == nullptr) == (io->moment_sumsq == nullptr), "give both moment_sum and moment_sumsq or neither");
-  if (chains->n_chains == 0) return 0;
-  const Entry* e = choose_entry(*model);
-  if (!e) return HMCB_E_UNSUPPORTED;
-  TaskLayout TL;
-  task_layout(model, chains->n_chains, nprops, TL);
-  if (!workspace || workspace_bytes < TL.total) {
-    set_error("drhmc sample workspace too small: have %zu bytes, need %zu", workspace ? workspace_bytes : (size_t)0, TL.total);
-    return HMCB_E_WORKSPACE;
-  }
-  const SampleIo sio{io->n_transitions, io->moment_sum, io->moment_sumsq, io->n_accept};
-  cudaStream_t st = (cudaStream_t)stream;
-  if (model->dtype == HMCB_F64)
-    return drhmc_tasks_t<double>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, convention, sio, out, workspace, TL, st);
-  return drhmc_tasks_t<float>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, convention, sio, out, workspace, TL, st);
 }
 
 int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
@@ -702,20 +584,6 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
   if (chains->n_chains == 0) return 0;
   const Entry* e = choose_entry(*model);
   if (!e) return HMCB_E_UNSUPPORTED;
-  if (dr_use_tasks(chains->n_chains, profile)) {
-    TaskLayout TL;
-    task_layout(model, chains->n_chains, nprops, TL);
-    if (!workspace || workspace_bytes < TL.total) {
-      set_error("drhmc workspace too small: have %zu bytes, need %zu", workspace ? workspace_bytes : (size_t)0, TL.total);
-      return HMCB_E_WORKSPACE;
-    }
-    const SampleIo sio{1, nullptr, nullptr, nullptr};
-    if (model->dtype == HMCB_F64)
-      return drhmc_tasks_t<double>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, convention, sio, out,
-                                   workspace, TL, (cudaStream_t)stream);
-    return drhmc_tasks_t<float>(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, convention, sio, out,
-                                workspace, TL, (cudaStream_t)stream);
-  }
   // the workspace is always sized for the un-profiled call (hmcb_drhmc_workspace_bytes), which is the larger one
   const int S = dr_split_for(chains->n_chains, profile);
   DrLayout L[kMaxSplit];
@@ -741,8 +609,7 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
   if ((rc = helper_streams(&h))) return rc;
   // the fork/join events are shared by every call on this device: enqueue the whole fork - launch - join sequence
   // of one call before another host thread's (only the enqueueing is serialised; the work itself is asynchronous)
-  static std::mutex seq_mu;
-  std::lock_guard<std::mutex> seq_lock(seq_mu);
+  std::lock_guard<std::mutex> seq_lock(g_seq_mu);
   HMCB_CUDA(cudaEventRecord(h->fork, st));
   char* w = (char*)workspace;
   rc = 0;
@@ -766,6 +633,128 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
       if (ce != cudaSuccess && rc == 0) rc = cuda_fail(ce, "join of the helper stream");
     }
     w += L[i].total;
+  }
+  return rc;
+}
+
+// ------------------------------------------------------------------ K transitions per call, pipelined over chain ranges
+// ranges of a sample call: enough that the stage kernels of different ranges and transitions always have
+// something to fill each other's tails with, few enough that a range's first stage still covers the GPU
+static int sample_split_for(int64_t n_chains) {
+  int s = n_chains >= (1 << 17) ? 4 : (n_chains >= (1 << 14) ? 2 : 1);
+  if (const char* e = getenv("HMCB_SAMPLE_SPLIT")) {
+    const int v = atoi(e);
+    if (v >= 1 && v <= kMaxSplit) s = v;
+  }
+  if ((int64_t)s > n_chains) s = 1;
+  return s;
+}
+
+static int sample_layouts(const Entry* e, const hmcb_model* m, int64_t n_chains, int nprops, int S, DrLayout* L, size_t* off_counts,
+                          size_t& total) {
+  total = 0;
+  for (int i = 0; i < S; ++i) {
+    const int64_t n = split_bound(n_chains, S, i + 1) - split_bound(n_chains, S, i);
+    int rc = dr_layout(e, m, n, nprops, L[i]);
+    if (rc) return rc;
+    off_counts[i] = total + L[i].total;                              // this range's per-transition counters
+    total = off_counts[i] + align_up((size_t)n * 3 * sizeof(int32_t), 256);
+  }
+  return 0;
+}
+
+size_t hmcb_drhmc_sample_workspace_bytes(const hmcb_model* model, int64_t n_chains, int32_t nprops) {
+  if (check_model(model)) return 0;
+  if (n_chains < 1 || nprops < 1 || nprops > kMaxProps) {
+    set_error("workspace query: n_chains=%lld nprops=%d out of range (nprops <= %d)", (long long)n_chains, nprops, kMaxProps);
+    return 0;
+  }
+  const Entry* e = choose_entry(*model);
+  if (!e) return 0;
+  DrLayout L[kMaxSplit];
+  size_t offc[kMaxSplit], total = 0;
+  if (sample_layouts(e, model, n_chains, nprops, sample_split_for(n_chains), L, offc, total)) return 0;
+  return total;
+}
+
+int hmcb_drhmc_sample(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
+                      double step_size, int32_t nprops, double stepfactor, int32_t convention, const hmcb_sample_io* io,
+                      const hmcb_step_out* out, void* workspace, size_t workspace_bytes, void* stream) {
+  int rc;
+  if ((rc = check_model(model))) return rc;
+  if ((rc = check_chains(chains))) return rc;
+  HMCB_CHECK_ARG(rng != nullptr && io != nullptr, "rng/io is NULL");
+  HMCB_CHECK_ARG(nprops >= 1 && nprops <= kMaxProps, "nprops=%d must be in 1..%d", nprops, kMaxProps);
+  HMCB_CHECK_ARG(stepfactor > 0, "stepfactor must be > 0");
+  HMCB_CHECK_ARG(convention >= HMCB_DR_ALGORITHMS && convention <= HMCB_DR_PROB_HASTINGS, "unknown DR convention %d", convention);
+  HMCB_CHECK_ARG(n_leap >= 0, "n_leap must be >= 0");
+  const int K = io->n_transitions;
+  HMCB_CHECK_ARG(K >= 1, "n_transitions must be >= 1");
+  HMCB_CHECK_ARG(K == 1 || (!rng->p_inject && !rng->u_inject && !rng->p_prev),
+                 "injected draws and a partial momentum refresh are defined for n_transitions == 1 only");
+  HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= dr_uniforms(nprops, convention),
+                 "u_inject needs u_stride >= %d for nprops=%d under convention %d", dr_uniforms(nprops, convention), nprops, convention);
+  HMCB_CHECK_ARG((io->moment_sum == nullptr) == (io->moment_sumsq == nullptr), "give both moment_sum and moment_sumsq or neither");
+  HMCB_CHECK_ARG(!io->n_accept || (out && out->code), "n_accept needs out->code");
+  if (chains->n_chains == 0) return 0;
+  const Entry* e = choose_entry(*model);
+  if (!e) return HMCB_E_UNSUPPORTED;
+  const int S = sample_split_for(chains->n_chains);
+  DrLayout L[kMaxSplit];
+  size_t offc[kMaxSplit], need = 0;
+  if ((rc = sample_layouts(e, model, chains->n_chains, nprops, S, L, offc, need))) return rc;
+  if (!workspace || workspace_bytes < need) {
+    set_error("drhmc sample workspace too small: have %zu bytes, need %zu", workspace ? workspace_bytes : (size_t)0, need);
+    return HMCB_E_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  HelperStreams* h = nullptr;
+  std::unique_lock<std::mutex> seq_lock(g_seq_mu, std::defer_lock);
+  if (S > 1) {
+    if ((rc = helper_streams(&h))) return rc;
+    seq_lock.lock();   // fork/join events are shared per device: one call's enqueueing at a time
+    HMCB_CUDA(cudaEventRecord(h->fork, st));
+  }
+  const size_t ts = model->dtype == HMCB_F64 ? 8 : 4;
+  const int min_accept = convention == HMCB_DR_ALGORITHMS ? 1 : 0;
+  // transition k of every range is enqueued before transition k+1 of any: all streams have work from the start
+  rc = 0;
+  for (int i = 1; i < S && rc == 0; ++i) {
+    cudaError_t ce = cudaStreamWaitEvent(h->s[i - 1], h->fork, 0);
+    if (ce != cudaSuccess) rc = cuda_fail(ce, "cudaStreamWaitEvent(helper, fork)");
+  }
+  int forked = rc == 0 ? S : 1;
+  for (int k = 0; k < K && rc == 0; ++k) {
+    for (int i = 0; i < S && rc == 0; ++i) {
+      const int64_t lo = split_bound(chains->n_chains, S, i), hi = split_bound(chains->n_chains, S, i + 1);
+      hmcb_chains cs;
+      hmcb_rng rs;
+      hmcb_step_out os;
+      sub_range(model, chains, rng, out, nprops, lo, hi, cs, rs, os);
+      if (k > 0) cs.q_in = cs.q_out;                   // later transitions run in place on the new state
+      rs.iteration = rng->iteration + (uint64_t)k;
+      int32_t* counts_k = (int32_t*)((char*)workspace + offc[i]);
+      int32_t* counts_tot = os.counts;
+      if (K > 1 && counts_tot) os.counts = counts_k;
+      cudaStream_t on = i == 0 ? st : h->s[i - 1];
+      void* ws = (char*)workspace + (offc[i] - L[i].total);
+      if (model->dtype == HMCB_F64)
+        rc = drhmc_step_t<double>(e, model, &cs, &rs, n_leap, step_size, nprops, stepfactor, convention, &os, ws, L[i], nullptr, on);
+      else
+        rc = drhmc_step_t<float>(e, model, &cs, &rs, n_leap, step_size, nprops, stepfactor, convention, &os, ws, L[i], nullptr, on);
+      if (rc) break;
+      void* msum = io->moment_sum ? (char*)io->moment_sum + (size_t)lo * model->d * ts : nullptr;
+      void* msq = io->moment_sumsq ? (char*)io->moment_sumsq + (size_t)lo * model->d * ts : nullptr;
+      rc = launch_post_transition(model->dtype, hi - lo, model->d, cs.q_out, cs.stride_chain, cs.stride_dim, msum, msq, counts_k,
+                                  (K > 1) ? counts_tot : nullptr, k == 0, os.code, min_accept,
+                                  io->n_accept ? io->n_accept + lo : nullptr, on);
+    }
+  }
+  for (int i = 1; i < forked; ++i) {
+    // a forked helper stream is always joined back, also after an error
+    cudaError_t ce = cudaEventRecord(h->join[i - 1], h->s[i - 1]);
+    if (ce == cudaSuccess) ce = cudaStreamWaitEvent(st, h->join[i - 1], 0);
+    if (ce != cudaSuccess && rc == 0) rc = cuda_fail(ce, "join of the helper stream");
   }
   return rc;
 }

@@ -7,14 +7,13 @@
 #pragma once
 #include <vector>
 
-#include "dr_tasks.cuh"
 #include "extra_kernels.cuh"
 #include "transition_ws.cuh"
 
 namespace hmcb {
 
 enum Op { OP_HMC = 0, OP_DR0 = 1, OP_DRN = 2, OP_LEAPFROG = 3, OP_LOGPGRAD = 4, OP_QUERY = 5, OP_MALA = 6, OP_ADHMC = 7,
-          OP_QUERY_AD = 8, OP_GHMC = 9, OP_ADWALK = 10, OP_QUERY_WALK = 11, OP_DRTASK = 12 };
+          OP_QUERY_AD = 8, OP_GHMC = 9, OP_ADWALK = 10, OP_QUERY_WALK = 11 };
 constexpr int kGhmcMaxEpl = 32;  // GHMC keeps q, p and the gradient: 3*EPL values per lane
 constexpr int kMalaMaxEpl = 28;  // MALA keeps q, grad, q1, grad1 in registers: 4*EPL values per lane
 
@@ -112,6 +111,11 @@ constexpr int min_blocks_for() {
 }
 
 int max_optin_smem();  // per-block opt-in shared memory limit of the current device
+
+// moments.cu: the per-transition bookkeeping of a sample loop (running moments, summed work counters, accept counts)
+int launch_post_transition(int32_t dtype, int64_t n_chains, int32_t d, const void* q, int64_t sc, int64_t sd, void* sum,
+                           void* sumsq, const int32_t* counts_k, int32_t* counts_tot, int first, const int32_t* code,
+                           int min_accept_code, int32_t* n_accept, cudaStream_t st);
 
 // gauss_dmma.cu: dense-Gaussian HMC transition on the FP64 tensor path; returns 1 when it does not apply
 int gauss_dmma_hmc(const hmcb_model& hm, const TransArgs<double>& a, cudaStream_t st);
@@ -212,14 +216,6 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
       // the list length lives on the device: launch the persistent grid the frames were sized for
       const int grid = (int)(a.ws.frame_threads / THREADS);
       k<<<grid, THREADS, smem, st>>>(model, a);
-      break;
-    }
-    case OP_DRTASK: {
-      auto k = k_dr_tasks<Model, T, EPL, LPC, UNITM, THREADS, MINB>;
-      if ((rc = prep(k, max_blocks))) return rc;
-      TaskArgs<T>& a = *(TaskArgs<T>*)args;
-      // persistent and fully resident: warps wait on each other's ring entries
-      k<<<grid_for(a.t.n_chains, max_blocks), THREADS, smem, st>>>(model, a);
       break;
     }
     case OP_LEAPFROG:

@@ -21,6 +21,55 @@ __global__ void __launch_bounds__(256) k_moments_accumulate(const T* __restrict_
   }
 }
 
+// What a sample loop does with one transition's outputs (hmcb_drhmc_sample): running moments as above, the
+// transition's work counters added to the running totals (the reference sums state.counts afterwards,
+// scripts_old/tests/test_drhmc_funnel.py:258), accepted transitions counted.  One launch per transition and
+// chain range; HBM-bound, it overlaps the FP64-bound stage kernels of other ranges.
+template <typename T>
+__global__ void __launch_bounds__(256) k_post_transition(const T* __restrict__ q, int64_t sc, int64_t sd, int d, int64_t n_chains,
+                                                         T* __restrict__ sum, T* __restrict__ sumsq,
+                                                         const int32_t* __restrict__ counts_k, int32_t* __restrict__ counts_tot,
+                                                         int first, const int32_t* __restrict__ code, int min_accept_code,
+                                                         int32_t* __restrict__ n_accept) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (sum) {
+    const int64_t n = n_chains * d;
+    for (int64_t i = i0; i < n; i += stride) {
+      const int64_t c = i / d;
+      const int k = (int)(i - c * d);
+      const T x = q[c * sc + k * sd];
+      sum[i] += x;
+      sumsq[i] = fma(x, x, sumsq[i]);
+    }
+  }
+  if (counts_tot) {
+    for (int64_t i = i0; i < 3 * n_chains; i += stride) counts_tot[i] = first ? counts_k[i] : counts_tot[i] + counts_k[i];
+  }
+  if (n_accept) {
+    for (int64_t i = i0; i < n_chains; i += stride) n_accept[i] += (code[i] >= min_accept_code) ? 1 : 0;
+  }
+}
+
+int launch_post_transition(int32_t dtype, int64_t n_chains, int32_t d, const void* q, int64_t sc, int64_t sd, void* sum,
+                           void* sumsq, const int32_t* counts_k, int32_t* counts_tot, int first, const int32_t* code,
+                           int min_accept_code, int32_t* n_accept, cudaStream_t st) {
+  if (!sum && !counts_tot && !n_accept) return 0;
+  const int64_t n = n_chains * (sum ? d : 3);
+  int64_t blocks = (n + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  if (dtype == HMCB_F64)
+    k_post_transition<double><<<(int)blocks, 256, 0, st>>>((const double*)q, sc, sd, d, n_chains, (double*)sum, (double*)sumsq,
+                                                           counts_k, counts_tot, first, code, min_accept_code, n_accept);
+  else
+    k_post_transition<float><<<(int)blocks, 256, 0, st>>>((const float*)q, sc, sd, d, n_chains, (float*)sum, (float*)sumsq,
+                                                          counts_k, counts_tot, first, code, min_accept_code, n_accept);
+  HMCB_CUDA(cudaPeekAtLastError());
+  return 0;
+}
+
 // out[0*d+k] = sum_c m_ck, out[1*d+k] = sum_c m_ck^2, out[2*d+k] = sum_c s2_ck (ddof=1),
 // out[3*d+k] = sum_c (m_ck - mu_k)^2, with m, s2 the per-chain mean and variance over n_samples.
 // Thread t of a block owns dimension k = kbase + t % dw and row offset t / dw, so a

@@ -168,19 +168,23 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
                     const hmcb_step_out* out, void* workspace, size_t workspace_bytes,
                     const hmcb_profile* profile /* may be NULL */, void* stream);
 
-/* K delayed-rejection transitions of every chain in ONE launch: the loop of DRHMC.sample
+/* K delayed-rejection transitions of every chain in ONE call: the loop of DRHMC.sample
  * (src/algorithms.py:542-552; scripts_old/funnel/funnelmpi_multistep.py runs the same loop over
  * PyHMC_multistep.multi_step) with the chain state kept on the device.  Each transition is
- * hmcb_drhmc_step's, bit for bit (transition k of a chain draws with iteration rng->iteration + k);
- * chains advance independently inside one persistent kernel that schedules single leapfrog
- * trajectories (hmc_b200/csrc/dr_tasks.cuh), so nothing waits for the slowest chain between
- * transitions.  The reference keeps every sample (state.samples, :548); at 2^20 chains that does
- * not fit, so the running moments the diagnostics need are folded in instead: after every
- * transition moment_sum += q, moment_sumsq += q*q (contiguous [C,d], model dtype; as
- * hmcb_moments_accumulate).  out: code / avec / ptries / p_out / p0_out of the LAST transition,
- * counts summed over the K transitions; n_accept[c] += transitions accepted at any stage.
- * Injected draws and p_prev need n_transitions == 1.  Workspace: hmcb_drhmc_sample_workspace_bytes()
- * (per-chain scratch: (2 nprops - 1) d + O(nprops^2) values per chain). */
+ * hmcb_drhmc_step's, bit for bit (transition k of a chain draws with iteration rng->iteration + k).
+ * Chains are independent, so the batch is cut into up to 4 contiguous chain ranges, each running
+ * its K transitions back to back on a stream of its own (the caller's and helper streams the
+ * library owns, forked from and joined into `stream`): the thin last round of one range's stage
+ * kernel is filled by another range's kernels -- of the same or of a later transition -- so the
+ * only tail left is the one at the very end of the call.  The reference keeps every sample
+ * (state.samples, :548); at 2^20 chains that does not fit, so the running moments the diagnostics
+ * need are folded in instead: after every transition moment_sum += q, moment_sumsq += q*q
+ * (contiguous [C,d], model dtype; as hmcb_moments_accumulate).  out: code / avec / ptries / p_out /
+ * p0_out of the LAST transition, counts summed over the K transitions; n_accept[c] += transitions
+ * accepted at any stage (needs out->code).  Injected draws and p_prev need n_transitions == 1.
+ * Workspace: hmcb_drhmc_sample_workspace_bytes().  Make the first call per device outside stream
+ * capture (helper streams are created then); HMCB_SAMPLE_SPLIT=n in the environment sets the
+ * number of ranges (1..8). */
 typedef struct hmcb_sample_io {
   int32_t n_transitions;      /* K >= 1 */
   void* moment_sum;           /* [C,d] or NULL (both or neither) */

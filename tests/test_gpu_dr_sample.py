@@ -1,10 +1,10 @@
-"""Delayed rejection as per-trajectory tasks in one persistent kernel (csrc/dr_tasks.cuh,
-hmcb_drhmc_sample) against the staged kernels (hmcb_drhmc_step, one kernel per stage), which the
-oracle and golden tests pin to algorithms.DRHMC.step / get_num (src/algorithms.py:474-530) and
-PyHMC_multistep / the probabilistic classes: every per-chain output must be IDENTICAL, bit for
-bit, for every convention, kernel shape and number of stages, with replayed and with Philox draws;
-K transitions in one launch must equal K single calls; and the folded running moments must equal
-hmcb_moments_accumulate's."""
+"""K delayed-rejection transitions per call (hmcb_drhmc_sample: the stage kernels of several chain
+ranges pipelined over streams, running moments and summed counters folded in) against single
+hmcb_drhmc_step calls, which the oracle and golden tests pin to algorithms.DRHMC.step / get_num
+(src/algorithms.py:474-530) and PyHMC_multistep / the probabilistic classes: every per-chain output
+must be IDENTICAL, bit for bit, for every convention, kernel shape and number of stages, with
+replayed and with Philox draws; K transitions in one call must equal K single calls; and the folded
+running moments must equal hmcb_moments_accumulate's."""
 import numpy as np
 import pytest
 import torch
@@ -47,7 +47,7 @@ def _same(a, b, keys):
 @pytest.mark.parametrize("nprops,f", [(1, 2.0), (2, 2.0), (3, 2.0), (4, 1.5), (5, 1.3)])
 @pytest.mark.parametrize("conv", [_lib.DR_ALGORITHMS, _lib.DR_MULTISTEP, _lib.DR_PROB_METROP, _lib.DR_PROB_HASTINGS])
 @pytest.mark.parametrize("lpc", [0, 8])
-def test_tasks_equal_stages_with_replayed_draws(kind, d, nleap, eps, nprops, f, conv, lpc, monkeypatch):
+def test_sample_call_equals_step_call_with_replayed_draws(kind, d, nleap, eps, nprops, f, conv, lpc, monkeypatch):
     if lpc:
         monkeypatch.setenv("HMCB_LPC", str(lpc))
     else:
@@ -64,8 +64,8 @@ def test_tasks_equal_stages_with_replayed_draws(kind, d, nleap, eps, nprops, f, 
 
 
 @pytest.mark.parametrize("conv", [_lib.DR_ALGORITHMS, _lib.DR_PROB_HASTINGS])
-@pytest.mark.parametrize("C", [1, 31, 4096 + 5, 70001])
-def test_tasks_equal_stages_with_philox_draws(conv, C):
+@pytest.mark.parametrize("C", [1, 31, 4096 + 5, 70001, 140003])
+def test_sample_call_equals_step_call_with_philox_draws(conv, C):
     d = 50
     q0 = torch.as_tensor(_q0("funnel", C, d, 5), device=_dev())
     a = algorithms.DRHMC(models.Funnel(d), device=_dev(), seed=9, chain_offset=123).engine
@@ -75,8 +75,8 @@ def test_tasks_equal_stages_with_philox_draws(conv, C):
     _same(ra, rb, ("q", "p", "code", "avec", "counts", "ptries"))
 
 
-def test_tasks_match_the_oracle_directly():
-    """Not only equal to the staged kernels: the task kernel against oracle.samplers.drhmc_step itself."""
+def test_sample_call_matches_the_oracle_directly():
+    """Not only equal to hmcb_drhmc_step: the sample call against oracle.samplers.drhmc_step itself."""
     d, C, nleap, eps, nprops, f = 50, 200, 10, 0.35, 3, 2.0
     om = omodels.Funnel(d)
     q0 = _q0("funnel", C, d, 8)
@@ -92,7 +92,7 @@ def test_tasks_match_the_oracle_directly():
 
 @pytest.mark.parametrize("kind,d,lpc", [("funnel", 50, 0), ("funnel", 10, 0), ("funnel", 50, 4), ("rosenbrock", 20, 0)])
 @pytest.mark.parametrize("conv", [_lib.DR_ALGORITHMS, _lib.DR_PROB_METROP])
-def test_k_transitions_in_one_launch_equal_k_single_calls(kind, d, lpc, conv, monkeypatch):
+def test_k_transitions_in_one_call_equal_k_single_calls(kind, d, lpc, conv, monkeypatch):
     if lpc:
         monkeypatch.setenv("HMCB_LPC", str(lpc))
     else:
@@ -125,7 +125,7 @@ def test_k_transitions_in_one_launch_equal_k_single_calls(kind, d, lpc, conv, mo
 
 
 def test_in_place_and_repeated_launches():
-    """q_out == q_in, and the scratch of one launch does not leak into the next."""
+    """q_out == q_in, and the scratch of one call does not leak into the next."""
     d, C = 50, 9000
     dev = _dev()
     q0 = torch.as_tensor(_q0("funnel", C, d, 13), device=dev)

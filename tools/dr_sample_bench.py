@@ -1,5 +1,6 @@
 #!/usr/bin/env python
-"""Staged DR step (one kernel per stage) against the task kernel (dr_tasks.cuh) on the headline workload:
+"""One hmcb_drhmc_step call per transition against hmcb_drhmc_sample (K transitions per call, chain ranges pipelined over
+streams) on the headline workload:
 funnel d=50, nleap=150, eps=0.2, nprops=3, f=2.  Prints ms per transition and the fraction of the FP64 peak
 (gradient evaluations x 350 flop / time / measured DFMA peak) for each form and chain count."""
 import argparse
@@ -86,9 +87,9 @@ def main():
             eng.drhmc_sample(state["q"], a.nleap, a.eps, 3, 2.0, K, msum=s1, msumsq=s2, q_out=nxt, want_avec=False,
                              code_out=code, counts_out=counts[0])
 
-        for name, fn in (("staged, one call per transition (+ moments kernel)", staged),
-                         ("tasks, one call per transition (moments folded)", tasks_k1),
-                         ("tasks, %d transitions per launch (moments folded)" % K, tasks_fused)):
+        for name, fn in (("step call per transition (+ moments kernel)", staged),
+                         ("sample call, 1 transition per call (moments folded)", tasks_k1),
+                         ("sample call, %d transitions per call (moments folded)" % K, tasks_fused)):
             ms = timed(fn)
             if fn is tasks_fused:
                 grads = float(counts[0, :, 1].sum(dtype=torch.float64))
@@ -100,7 +101,7 @@ def main():
                          "fp64_peak_tflops": peak})
             print(json.dumps(rows[-1]), flush=True)
     os.makedirs("gpurun_out", exist_ok=True)
-    json.dump(rows, open("gpurun_out/dr_tasks_bench.json", "w"), indent=1)
+    json.dump(rows, open("gpurun_out/dr_sample_bench.json", "w"), indent=1)
 
 
 if __name__ == "__main__":
