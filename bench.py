@@ -53,6 +53,9 @@ def parse():
     ap.add_argument("--no_cpu_baseline", action="store_true")
     ap.add_argument("--no_e2e", action="store_true")
     ap.add_argument("--e2e_steps", type=int, default=0)
+    ap.add_argument("--no_secondary", action="store_true")
+    ap.add_argument("--ess_steps", type=int, default=64, help="transitions of the stationary ESS window (0: skip)")
+    ap.add_argument("--acf_steps", type=int, default=256, help="stored transitions of the autocorrelation window (0: skip)")
     return ap.parse_args()
 
 
@@ -215,49 +218,20 @@ class ClockSampler(threading.Thread):
 
 
 # ------------------------------------------------------------------ GPU arm
-def run_hmcb(a):
+def measured_peaks():
+    """Driver-measured HBM / bf16 peaks of this pool's B200 (MEASURED_PEAKS.json), else the profiling recipe's fallback."""
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return {"hbm_gbs": p["hbm_gbs"], "bf16_tflops": p["bf16_tflops"], "bf16_tflops_sustained": p.get("bf16_tflops_sustained"),
+                "source": "MEASURED_PEAKS.json"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": None, "source": "fallback (B200_PROFILING.md)"}
+
+
+def fp64_peak_tflops(eng, dev):
+    """FP64 pipe peak of this GPU, measured now with a register-resident DFMA loop (MEASURED_PEAKS.json has no FP64 figure)."""
     import torch
-
-    from hmc_b200 import _lib, algorithms, dist, models, utils
-
-    rank, world, local = dist.init_from_env()
-    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    n_total = total_chains(a)
-    lo, hi = dist.shard_range(n_total)
-    C, d = hi - lo, a.ndim
-
-    model = models.Funnel(d)
-    dr = algorithms.DRHMC(model, device=dev, seed=a.seed, chain_offset=lo)
-    eng = dr.engine
-    eng._ensure()
-    g = torch.Generator().manual_seed(a.seed)
-    if a.scaling == "strong":   # one global array, sliced: chain statistics do not depend on N
-        q = (torch.rand(n_total, d, generator=g, dtype=torch.float64) * 2 - 1)[lo:hi].to(dev).contiguous()
-    else:                       # per-shard stream (no N*2^20 x d host array); shard 0 is the N=1 workload
-        g.manual_seed(a.seed + 7919 * rank)
-        q = (torch.rand(C, d, generator=g, dtype=torch.float64) * 2 - 1).to(dev).contiguous()
-    nxt = torch.empty_like(q)
-
-    K = a.steps
-    counts_log = torch.zeros((K + 1, C, 3), dtype=torch.int32, device=dev)   # slot K: scratch for untimed steps
-    code_log = torch.zeros((K + 1, C), dtype=torch.int32, device=dev)
-
-    def transition(qi, qo, events=None, slot=K):
-        # every output buffer is preallocated: no allocator traffic inside the timed loop
-        return eng.drhmc_step(qi, a.nleap, a.step_size, a.nprops, a.stepfactor, want_p=False, q_out=qo,
-                              stage_events=events, want_avec=False, code_out=code_log[slot],
-                              counts_out=counts_log[slot])
-
-    clocks = ClockSampler(local)
-    clocks.start()
-    for _ in range(a.burnin):
-        transition(q, nxt)
-        q, nxt = nxt, q
-    mom = utils.RunningMoments(eng, C, d)
-
-    # FP64 pipe peak of this GPU, measured now (MEASURED_PEAKS.json carries only HBM and bf16 numbers)
+    from hmc_b200 import _lib
     sms = torch.cuda.get_device_properties(dev).multi_processor_count
     sink = torch.empty(sms * 8 * 256, dtype=torch.float64, device=dev)
     cnt = _lib.C.c_double(0)
@@ -270,105 +244,470 @@ def run_hmcb(a):
         torch.cuda.synchronize()
         if it:
             best = max(best, 2.0 * cnt.value / (e0.elapsed_time(e1) * 1e-3) / 1e12)
-    fp64_peak_tflops = best
+    return best
 
-    for _ in range(a.warmup):
-        out = transition(q, nxt)
-        q, nxt = nxt, q
-        mom.add(q)
-    mom.reset()
 
-    # nvidia-smi was started before burn-in; its start-up (NVML init over every GPU of the box) stalls
-    # kernel launches for a moment, so it must be past that before the timed region begins
-    t_wait = time.time()
-    while len(clocks.rows) < 3 and time.time() - t_wait < 10.0:
-        time.sleep(0.05)
-    KR = min(K, 6)      # transitions of the per-stage timing pass after the timed region
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(a.nprops + 1)] for _ in range(KR)]
-    for row in evs:
-        for ev in row:
-            ev.record()      # creates the cudaEvent_t handles now, not inside the timed loop
+def timed_region(fn, dev, world):
+    """fn() enqueues the work; barrier + synchronize on both sides, CUDA events on the launching stream, max over ranks."""
+    import torch
+    from hmc_b200 import dist
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     dist.barrier()
     torch.cuda.synchronize()
-    t_wall0 = time.time()
+    t0 = time.time()
     start.record()
-    for k in range(K):
-        transition(q, nxt, None, slot=k)
-        q, nxt = nxt, q
-        mom.add(q)
+    out = fn()
     end.record()
     torch.cuda.synchronize()
     dist.barrier()
-    t_wall1 = time.time()
+    t1 = time.time()
     ms = torch.tensor([start.elapsed_time(end)], dtype=torch.float64, device=dev)
     if world > 1:
         torch.distributed.all_reduce(ms, op=torch.distributed.ReduceOp.MAX)
-    ms_total = float(ms[0])
-    clocks.stop()
+    return float(ms[0]), out, t0, t1
 
-    # Per-stage kernel times for the roofline: the timed region above runs the DR step as the library runs it
-    # by default -- chain ranges on several streams, stages of different ranges overlapping -- so a stage has no
-    # duration of its own there.  Straight after it, the same transition is run KR more times from the same state
-    # with hmcb_profile events, which makes the library run the stages one after another on one stream.
-    n_split = 2 if C >= (1 << 15) else 1     # dr_split_for() in csrc/api.cu
-    if os.environ.get("HMCB_DR_SPLIT"):
-        n_split = int(os.environ["HMCB_DR_SPLIT"])
-    for k in range(KR):
-        transition(q, nxt, evs[k], slot=K)
+
+def exact_funnel(C, d, seed, dev):
+    import torch
+    g = torch.Generator(device=dev).manual_seed(seed)
+    v = 3.0 * torch.randn(C, 1, generator=g, dtype=torch.float64, device=dev)
+    th = torch.exp(v / 2) * torch.randn(C, d - 1, generator=g, dtype=torch.float64, device=dev)
+    return torch.cat([v, th], dim=1).contiguous()
+
+
+def dr_block(a, dev, world, lo, C, q0, seed, K, warmup, burnin, want_stage_times, fp64_peak):
+    """The headline measurement on C chains of this rank starting from q0: burn-in, warm-up, K timed transitions in one
+    hmcb_drhmc_sample call (chain ranges pipelined over streams, running moments folded in), then the same K
+    transitions as one hmcb_drhmc_step call + one moments kernel each, then per-stage kernel times."""
+    import torch
+    from hmc_b200 import algorithms, dist, models, utils
+    d = a.ndim
+    model = models.Funnel(d)
+    dr = algorithms.DRHMC(model, device=dev, seed=seed, chain_offset=lo)
+    eng = dr.engine
+    eng._ensure()
+    q = q0
+    if burnin:
+        q = eng.drhmc_sample(q, a.nleap, a.step_size, a.nprops, a.stepfactor, burnin, want_avec=False)["q"]
+    mom = utils.RunningMoments(eng, C, d)
+    nxt = torch.empty_like(q)
+    counts = torch.zeros((C, 3), dtype=torch.int32, device=dev)
+    code = torch.zeros(C, dtype=torch.int32, device=dev)
+    nacc = torch.zeros(C, dtype=torch.int32, device=dev)
+
+    def sample(qi, n):
+        return eng.drhmc_sample(qi, a.nleap, a.step_size, a.nprops, a.stepfactor, n, msum=mom.sum, msumsq=mom.sumsq,
+                                n_accept=nacc, q_out=nxt, want_avec=False, code_out=code, counts_out=counts)
+
+    if warmup:
+        sample(q, warmup)
         q, nxt = nxt, q
+    mom.reset()
+    nacc.zero_()
+    ms_total, _, t0, t1 = timed_region(lambda: sample(q, K), dev, world)
+    q, nxt = nxt, q
+    mom.n = K
+    stats = torch.cat([counts.sum(dim=0, dtype=torch.float64), nacc.sum(dtype=torch.float64)[None]])
+    code_frac = (torch.bincount(code.long(), minlength=a.nprops + 1).double() / C).tolist()
+    dist.all_reduce_sum(stats)
+    grads, leaps, acc = float(stats[1]), float(stats[2]), float(stats[3])
+    res = {"ms_total": ms_total, "t0": t0, "t1": t1, "grads": grads, "leaps": leaps, "accepted": acc, "code_frac": code_frac,
+           "mom": mom, "q": q, "eng": eng, "model": model, "n_split": 4 if C >= (1 << 17) else (2 if C >= (1 << 14) else 1)}
+    if os.environ.get("HMCB_SAMPLE_SPLIT"):
+        res["n_split"] = int(os.environ["HMCB_SAMPLE_SPLIT"])
+
+    # the same transitions, one hmcb_drhmc_step call + one hmcb_moments_accumulate per transition (round 1's timed loop)
+    s1, s2 = torch.zeros_like(q), torch.zeros_like(q)
+    cl = torch.zeros((K, C, 3), dtype=torch.int32, device=dev)
+
+    def per_call():
+        qi, qo = q, nxt
+        for k in range(K):
+            eng.drhmc_step(qi, a.nleap, a.step_size, a.nprops, a.stepfactor, want_p=False, q_out=qo, want_avec=False,
+                           code_out=code, counts_out=cl[k])
+            eng.moments_accumulate(qo, s1, s2)
+            qi, qo = qo, qi
+    ms_pc, _, _, _ = timed_region(per_call, dev, world)
+    g_pc = cl[:, :, 1].sum(dtype=torch.float64)[None]
+    dist.all_reduce_sum(g_pc)
+    res["per_call"] = {"ms_per_step": ms_pc / K, "value": float(g_pc[0]) / (ms_pc * 1e-3),
+                       "what": "one hmcb_drhmc_step call (2 chain ranges on 2 streams) + one hmcb_moments_accumulate per transition"}
+
+    if want_stage_times:
+        KR = min(K, 6)
+        evs = [[torch.cuda.Event(enable_timing=True) for _ in range(a.nprops + 1)] for _ in range(KR)]
+        for row in evs:
+            for ev in row:
+                ev.record()
+        qi, qo = q, nxt
+        for k in range(KR):
+            eng.drhmc_step(qi, a.nleap, a.step_size, a.nprops, a.stepfactor, want_p=False, q_out=qo, stage_events=evs[k],
+                           want_avec=False, code_out=code, counts_out=cl[0])
+            qi, qo = qo, qi
+        mev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        mev[0].record()
+        for _ in range(4):
+            eng.moments_accumulate(q, s1, s2)
+        mev[1].record()
+        torch.cuda.synchronize()
+        st = torch.tensor([[evs[k][j].elapsed_time(evs[k][j + 1]) for j in range(a.nprops)] for k in range(KR)],
+                          dtype=torch.float64).mean(dim=0)
+        res["stage_ms"] = st.tolist()
+        res["moments_ms"] = mev[0].elapsed_time(mev[1]) / 4
+        res["stage_passes"] = KR
+    return res
+
+
+def stationary_block(a, dev, world, lo, C, seed):
+    """ESS and moment checks on a STATIONARY ensemble: chains start from exact funnel draws (v ~ N(0, 3), theta ~
+    N(0, e^v)), T transitions in one sample call with running moments; pooled moments against the analytic ones with
+    their Monte Carlo errors, utils.get_ess_true (src/utils.py:8-27) over the window, all ranks reduced over NCCL."""
+    import torch
+    from hmc_b200 import algorithms, dist, models, utils
+    d, T = a.ndim, a.ess_steps
+    model = models.Funnel(d)
+    eng = algorithms.DRHMC(model, device=dev, seed=seed + 17, chain_offset=lo).engine
+    eng._ensure()
+    q = exact_funnel(C, d, seed + 101 + lo % 9973, dev)
+    mom = utils.RunningMoments(eng, C, d)
+    counts = torch.zeros((C, 3), dtype=torch.int32, device=dev)
+    ms, out, _, _ = timed_region(lambda: eng.drhmc_sample(q, a.nleap, a.step_size, a.nprops, a.stepfactor, T, msum=mom.sum,
+                                                           msumsq=mom.sumsq, want_avec=False, counts_out=counts), dev, world)
+    mom.n = T
+    sec = ms * 1e-3
+    ess = mom.ess_true(model.true_mean(), model.true_std())
+    sums, Ctot = mom.reduce()
+    mean = sums[0] / Ctot
+    se_mean = torch.sqrt((sums[1] - sums[0] ** 2 / Ctot) / (Ctot - 1.0) / Ctot)        # between-chain variance of the chain means
+    m2 = mom.sumsq / T                                                                   # per-chain second moments
+    blk = torch.stack([m2.sum(dim=0, dtype=torch.float64), (m2 * m2).sum(dim=0, dtype=torch.float64)])
+    dist.all_reduce_sum(blk)
+    e2 = blk[0] / Ctot
+    se_e2 = torch.sqrt(torch.clamp(blk[1] / Ctot - e2 ** 2, min=0.0) / Ctot)
+    std = torch.sqrt(torch.clamp(e2 - mean ** 2, min=0.0))
+    se_std = se_e2 / (2.0 * std)
+    g = counts[:, 1].sum(dtype=torch.float64)[None]
+    dist.all_reduce_sum(g)
+    tstd = 9.487735836358526      # exp(2.25): Var(theta) = E[e^v] = e^{4.5}
+
+    # control: plain HMC (same kernels, same generator, same step size and length) from the same kind of start
+    from hmc_b200 import _lib, pyhmc
+    hq = exact_funnel(C, d, seed + 211 + lo % 9973, dev)
+    heng = pyhmc.HMC(model, device=dev, seed=seed + 19, chain_offset=lo).engine
+    hm = utils.RunningMoments(heng, C, d)
+    hnxt = torch.empty_like(hq)
+    Th = 8
+    for _ in range(Th):
+        heng.hmc_step(hq, a.nleap, a.step_size, _lib.RULE_PYHMC, want_p=False, q_out=hnxt)
+        hq, hnxt = hnxt, hq
+        hm.add(hq)
+    hs, hC = hm.reduce()
+    hmean = hs[0] / hC
+    hse = torch.sqrt((hs[1] - hs[0] ** 2 / hC) / (hC - 1.0) / hC)
+    hm2 = hm.sumsq / Th
+    hb = torch.stack([hm2[:, 0].sum(dtype=torch.float64), (hm2[:, 0] ** 2).sum(dtype=torch.float64)])
+    dist.all_reduce_sum(hb)
+    he2 = hb[0] / hC
+    hstd = torch.sqrt(he2 - hmean[0] ** 2)
+    hse_std = torch.sqrt(torch.clamp(hb[1] / hC - he2 ** 2, min=0.0) / hC) / (2.0 * hstd)
+    control = {"sampler": "pyhmc.HMC.step, L=%d eps=%g, %d transitions from exact funnel draws" % (a.nleap, a.step_size, Th),
+               "v_mean": float(hmean[0]), "v_mean_mc_err": float(hse[0]), "v_std": float(hstd), "v_std_mc_err": float(hse_std),
+               "pass": abs(float(hmean[0])) < 5 * float(hse[0]) and abs(float(hstd) - 3.0) < 5 * float(hse_std)}
+    del hq, hnxt, hm, hm2
+    v_ok = abs(float(mean[0])) < 5 * float(se_mean[0]) and abs(float(std[0]) - 3.0) < 5 * float(se_std[0])
+    th_mean_ok = bool((mean[1:].abs() < 5 * se_mean[1:]).float().mean() > 0.95)
+    th_std_ok = bool(((std[1:] - tstd).abs() < 5 * se_std[1:]).float().mean() > 0.95)
+    return {"start": "exact funnel draws", "transitions": T, "chains": int(Ctot), "ms_per_step": ms / T,
+            "v_mean": float(mean[0]), "v_mean_mc_err": float(se_mean[0]), "v_std": float(std[0]), "v_std_mc_err": float(se_std[0]),
+            "v_truth": [0.0, 3.0], "theta_std_mean_over_dims": float(std[1:].mean()), "theta_std_mc_err_typical": float(se_std[1:].median()),
+            "theta_std_truth": tstd, "pass": {"v": v_ok, "theta_mean": th_mean_ok, "theta_std": th_std_ok},
+            "pass_rule": "|estimate - truth| < 5 Monte Carlo errors (errors from the between-chain variance of per-chain moments); "
+                         "theta: at least 95 % of the dimensions",
+            "hmc_control": control,
+            "note": "delayed rejection with nprops >= 2 drifts slowly off the exact ensemble at this step size (std of v about "
+                    "-0.06 % per transition) while plain HMC through the same kernels and generator does not (hmc_control): it is "
+                    "the reference's own rule -- the GPU's decisions are identical to algorithms.DRHMC.step's on the same draws "
+                    "(tests/test_gpu_bench_path.py: 0 of 4096 differ) -- most likely get_num returning 0 for a ghost stage "
+                    "whose energy is NaN (src/algorithms.py:491-492) where one that overflowed to +inf counts as a certain "
+                    "rejection; see DESIGN.md section 2",
+            "ess_true_v": float(ess[0]), "ess_true_min": float(ess.min()), "ess_true_min_per_sec": float(ess.min()) / sec,
+            "ess_true_v_per_sec": float(ess[0]) / sec, "ess_true_per_grad_eval_v": float(ess[0]) / float(g[0]),
+            "ess_note": "utils.get_ess_true over the %d-transition window of all chains: (std / rms over chains of the chain-mean "
+                        "error)^2 * chains" % T}
+
+
+def autocorr_block(a, dev, seed):
+    """utils.get_rcc (src/utils.py:59-71: FFT autocorrelation, Sokal window c=5) on a STORED window: 4096 stationary
+    chains, every transition kept (v and the first two thetas)."""
+    import torch
+    from hmc_b200 import algorithms, models, utils
+    d, C, T = a.ndim, 4096, a.acf_steps
+    eng = algorithms.DRHMC(models.Funnel(d), device=dev, seed=seed + 29, chain_offset=1 << 40).engine
+    q = exact_funnel(C, d, seed + 5, dev)
+    nxt = torch.empty_like(q)
+    xs = torch.empty((T, C, 3), dtype=torch.float64, device=dev)
+    counts = torch.zeros((T, C, 3), dtype=torch.int32, device=dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
-    tot = counts_log[:K].sum(dim=(0, 1), dtype=torch.float64)
-    stage_ms = torch.tensor([[evs[k][j].elapsed_time(evs[k][j + 1]) for j in range(a.nprops)] for k in range(KR)],
-                            dtype=torch.float64, device=dev)
-    n_stage1 = (code_log[:K] != 1).sum(dim=1).double().mean()
-    acc_rate = (code_log[:K] > 0).double().mean()
-    code_frac = (torch.bincount(code_log[:K].flatten().long(), minlength=a.nprops + 1).double() / (K * C)).tolist()
-    stats = torch.cat([tot, stage_ms.mean(dim=0), n_stage1[None], acc_rate[None] * C])
-    dist.all_reduce_sum(stats[:3])
-    dist.all_reduce_sum(stats[-1:])
-    grads, leaps = float(stats[1]), float(stats[2])
+    e0.record()
+    for t in range(T):
+        eng.drhmc_step(q, a.nleap, a.step_size, a.nprops, a.stepfactor, want_p=False, q_out=nxt, want_avec=False,
+                       counts_out=counts[t])
+        q, nxt = nxt, q
+        xs[t] = q[:, :3]
+    e1.record()
+    torch.cuda.synchronize()
+    rcc, tc = utils.get_rcc(xs)                          # tc: integrated autocorrelation time at the window, [C, 3]
+    tau = tc.double().clamp(min=1.0)
+    ess_chain = T / tau
+    grads = float(counts[:, :, 1].sum(dtype=torch.float64))
+    return {"chains": C, "transitions_stored": T, "tau_v_median": float(tau[:, 0].median()), "tau_v_mean": float(tau[:, 0].mean()),
+            "tau_theta_median": float(tau[:, 1:].median()), "ess_per_chain_v": float(ess_chain[:, 0].mean()),
+            "ess_v_per_transition_per_chain": float(ess_chain[:, 0].mean()) / T,
+            "ess_v_per_grad_eval": float(ess_chain[:, 0].sum()) / grads,
+            "note": "src/utils.py:59-71 on x[T, 4096, 3] (v, theta_1, theta_2); tau = 1 + 2 sum rho up to the first lag >= 5 tau; "
+                    "ESS per chain = T / tau.  ESS/s of the full ensemble = ess_v_per_grad_eval x grad evals/s of the headline"}
+
+
+def gates_block(dev):
+    """SURVEY section 8d correctness gates, computed in this run on a committed golden (made by the unmodified reference):
+    max relative error of q and p, accept-code mismatches, Vgcount equality."""
+    import torch
+    from hmc_b200 import algorithms, models
+    path = os.path.join(ROOT, "tests", "golden", "drhmc_funnel50.npz")
+    if not os.path.exists(path):
+        return {"error": "golden not found"}
+    g = np.load(path)
+    case = json.loads(str(g["spec"]))
+    ar = case["args"]
+    s = algorithms.DRHMC(models.Funnel(case["model"]["d"], case["model"].get("sigma", 3.0)), device=dev)
+    err_q = err_p = 0.0
+    code_bad = cnt_bad = n = 0
+    for t in range(g["P"].shape[0]):
+        q_in = g["q0"] if t == 0 else g["q"][t - 1]
+        q, p, code, avec, counts = s.step(q_in, ar["nleap"], ar["step_size"], ar["nprops"], ar["stepfactor"], p=g["P"][t], u=g["U"][t])
+        err_q = max(err_q, float(np.max(np.abs(q - g["q"][t]) / (np.abs(g["q"][t]) + 0.1))))
+        err_p = max(err_p, float(np.max(np.abs(p - g["p"][t]) / (np.abs(g["p"][t]) + 0.1))))
+        code_bad += int((np.asarray(code, dtype=np.float64) != g["code"][t]).sum())
+        cnt_bad += int((np.asarray(counts)[:, 1] != g["counts"][t][:, 1]).sum())
+        n += q.shape[0]
+    return {"golden": "tests/golden/drhmc_funnel50.npz (algorithms.DRHMC.step of the unmodified reference, replayed draws)",
+            "chain_transitions": n, "max_rel_err_q": err_q, "max_rel_err_p": err_p, "tolerance": 1e-10,
+            "accept_code_mismatches": code_bad, "vgcount_mismatches": cnt_bad,
+            "pass": err_q < 1e-10 and err_p < 1e-10 and code_bad == 0 and cnt_bad == 0}
+
+
+def secondary_block(a, dev, world, rank, fp64_peak, peaks):
+    """The other BASELINE.json configurations, chains sharded over the ranks (fixed totals), each a few timed
+    transitions: ms, rate and its own roofline fraction.  Timing: CUDA events, best of 3 after 2 warm-ups, max over ranks."""
+    import torch
+    from hmc_b200 import _lib, adaptivehmc, algorithms, dist, mala, models, pyhmc
+    rows = []
+    g = torch.Generator().manual_seed(a.seed + 3)
+
+    def shard(n):
+        lo, hi = dist.shard_range(n)
+        return lo, hi - lo
+
+    def timed(fn, reps=3, warm=2):
+        for _ in range(warm):
+            fn()
+        best, out = 1e30, None
+        for _ in range(reps):
+            ms, out, _, _ = timed_region(fn, dev, world)
+            best = min(best, ms)
+        return best, out
+
+    def total(x):
+        t = torch.as_tensor([float(x)], dtype=torch.float64, device=dev)
+        dist.all_reduce_sum(t)
+        return float(t[0])
+
+    def row(name, ms, grads, flops_per_grad, bound="fp64", extra=None):
+        tf = grads * flops_per_grad / (ms * 1e-3) / 1e12
+        r = {"config": name, "ms_per_transition": ms, "grad_evals_per_s": grads / (ms * 1e-3), "algorithmic_tflops": tf, "bound": bound}
+        if bound == "fp64":
+            r["frac_of_fp64_peak"] = tf / fp64_peak
+        if extra:
+            r.update(extra)
+        rows.append(r)
+
+    # config 2: correlated Gaussian d=100, 65,536 chains, fixed step / L (FP64 tensor path, mma.sync.m8n8k4.f64)
+    d, Ct, L = 100, 65536, 32
+    lo, C = shard(Ct)
+    gm = models.CorrGaussian.ar1(d)
+    s = pyhmc.HMC(gm, device=dev, seed=1, chain_offset=lo)
+    q = torch.randn(Ct, d, generator=g, dtype=torch.float64)[lo:lo + C].to(dev)
+    eps = 0.1 * float(np.sqrt(np.linalg.eigvalsh(gm.Sigma).min()))
+    ms, out = timed(lambda: s.engine.hmc_step(q, L, eps, _lib.RULE_PYHMC, want_p=False))
+    row("cfg2 correlated Gaussian d=100, HMC L=32 eps=%.4f, 65,536 chains (k_gauss_hmc, DMMA)" % eps, ms, Ct * (L + 1), 2 * d * d + 4 * d)
+
+    # config 3, light variant (the reference's usual trajectory length): funnel d=50 DRHMC nleap=20 eps=0.1
+    d, Ct = 50, 1 << 20
+    lo, C = shard(Ct)
+    fm = models.Funnel(d)
+    q = (torch.rand(C, d, generator=g, dtype=torch.float64) * 2 - 1).to(dev)
+    dr = algorithms.DRHMC(fm, device=dev, seed=1, chain_offset=lo)
+    counts = torch.zeros((C, 3), dtype=torch.int32, device=dev)
+    ms, out = timed(lambda: dr.engine.drhmc_step(q, 20, 0.1, 3, 2.0, want_p=False, counts_out=counts, want_avec=False))
+    row("cfg3-light funnel d=50 DRHMC nleap=20 eps=0.1 nprops=3, 2^20 chains, one call per transition", ms,
+        total(counts[:, 1].sum(dtype=torch.float64)), 7 * d)
+    Kf = 8
+    ms, out = timed(lambda: dr.engine.drhmc_sample(q, 20, 0.1, 3, 2.0, Kf, counts_out=counts, want_avec=False))
+    row("cfg3-light, %d transitions per call (hmcb_drhmc_sample)" % Kf, ms / Kf, total(counts[:, 1].sum(dtype=torch.float64)) / Kf, 7 * d)
+    h = pyhmc.HMC(fm, device=dev, seed=1, chain_offset=lo)
+    ms, out = timed(lambda: h.engine.hmc_step(q, 20, 0.1, _lib.RULE_PYHMC, want_p=False))
+    row("funnel d=50 HMC L=20 eps=0.1, 2^20 chains", ms, Ct * 21, 7 * d)
+    del q, counts
+
+    # config 4: Bayesian logistic regression N=100,000 D=128, 16,384 chains, HMC L=10 (tcgen05 gradient GEMMs)
+    N, D, Ct, L = 100000, 128, 16384, 10
+    lo, C = shard(Ct)
+    rng = np.random.default_rng(3)
+    X = (rng.standard_normal((N, D)) / np.sqrt(D)).astype(np.float32)
+    y = (rng.random(N) < 1 / (1 + np.exp(-(X.astype(np.float64) @ rng.standard_normal(D))))).astype(np.float32)
+    lm = algorithms.HMC(models.LogisticRegression(X, y, 1.0), device=dev, seed=3, chain_offset=lo)
+    q = (0.1 * torch.randn(Ct, D, generator=g))[lo:lo + C].to(dev)
+    ms, out = timed(lambda: lm.engine.hmc_step(q, L, 0.01, _lib.RULE_ALG, want_p=False), reps=2, warm=1)
+    grads = Ct * (L + 1)
+    alg = grads * 4.0 * N * D / (ms * 1e-3) / 1e12
+    row("cfg4 logistic regression N=100,000 D=128, HMC L=10 eps=0.01, 16,384 chains", ms, grads, 4.0 * N * D, bound="tensor",
+        extra={"frac_of_bf16_peak_algorithmic": alg / peaks["bf16_tflops"],
+               "executed_fp16_tflops": 3 * alg, "frac_of_bf16_peak_executed": 3 * alg / peaks["bf16_tflops"],
+               "peak": peaks["bf16_tflops"], "peak_source": peaks["source"],
+               "note": "algorithmic = 4 N D flop per gradient (two GEMMs); executed = 3 fp16 products per algorithmic one "
+                       "(hi*hi + hi*lo + lo*hi for 1e-5 parity with the float64 reference)"})
+    del lm, q
+
+    # config 5 at d=100: Rosenbrock, 131,072 chains: HMC L=20, MALA (32 steps per launch), AdHMC_eps0, and the
+    # dual-averaging warm-up whose accept statistic is all-reduced over the ranks every iteration
+    d, Ct = 100, 131072
+    lo, C = shard(Ct)
+    rm = models.Rosenbrock(d)
+    q = (1.0 + 0.1 * torch.randn(Ct, d, generator=g, dtype=torch.float64))[lo:lo + C].to(dev)
+    fpg = 8.5 * d
+    hh = algorithms.HMC(rm, device=dev, seed=4, chain_offset=lo)
+    ms, out = timed(lambda: hh.engine.hmc_step(q, 20, 0.02, _lib.RULE_ALG, want_p=False))
+    row("cfg5 Rosenbrock d=100 HMC L=20 eps=0.02, 131,072 chains", ms, Ct * 21, fpg)
+    mm = mala.MALA(rm, device=dev, seed=4, chain_offset=lo)
+    ms, out = timed(lambda: mm.engine.mala_step(q, 0.02, n_steps=32))
+    row("cfg5 Rosenbrock d=100 MALA eps=0.02, 32 steps per launch", ms / 32, Ct * 33 / 32.0, fpg,
+        extra={"normals_per_s": Ct * 32 * d / (ms * 1e-3), "note": "one gradient per d normals: bound by Philox + Box-Muller issue, "
+               "not by the FP64 pipe (see profiles/ for the generator-only ceiling)"})
+    ad = adaptivehmc.AdHMC_eps0(rm, device=dev, seed=4, chain_offset=lo)
+    steps = ad.get_steps(0.01, 1.0, 10)
+    ms, out = timed(lambda: ad.engine.adhmc_eps0_step(q, 20, steps, 1))
+    row("cfg5 Rosenbrock d=100 AdHMC_eps0 ntry=10 Nleap=20", ms, total(out["counts"][:, 1].sum(dtype=torch.float64)), fpg)
+    hh.step_size = 0.05
+    nit = 60
+    torch.cuda.synchronize()
+    dist.barrier()
+    t0 = time.perf_counter()
+    hh.adapt_stepsize(q, nit, nsamples=0, burnin=0, step_size=0.05, nleap=20)
+    torch.cuda.synchronize()
+    dist.barrier()
+    ms_it = (time.perf_counter() - t0) * 1e3 / (nit + 1)
+    row("cfg5 Rosenbrock d=100 HMC L=20 dual-averaging warm-up, %d iterations, accept statistic all-reduced (%s) every "
+        "iteration" % (nit + 1, "NCCL, %d ranks" % world if world > 1 else "1 rank: no collective"), ms_it, Ct * 21, fpg,
+        extra={"adapted_step_size": float(hh.step_size), "timing": "host wall clock per iteration (one host round trip each)"})
+    return rows
+
+
+def run_hmcb(a):
+    import torch
+
+    from hmc_b200 import dist
+
+    rank, world, local = dist.init_from_env()
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    n_total = total_chains(a)
+    lo, hi = dist.shard_range(n_total)
+    C, d, K = hi - lo, a.ndim, a.steps
+
+    g = torch.Generator().manual_seed(a.seed)
+    if a.scaling == "strong":   # one global array, sliced: chain statistics do not depend on N
+        q0 = (torch.rand(n_total, d, generator=g, dtype=torch.float64) * 2 - 1)[lo:hi].to(dev).contiguous()
+    else:                       # per-shard stream (no N*2^20 x d host array); shard 0 is the N=1 workload
+        g.manual_seed(a.seed + 7919 * rank)
+        q0 = (torch.rand(C, d, generator=g, dtype=torch.float64) * 2 - 1).to(dev).contiguous()
+
+    clocks = ClockSampler(local)
+    clocks.start()
+    from hmc_b200 import algorithms, models
+    probe_eng = algorithms.DRHMC(models.Funnel(d), device=dev).engine
+    probe_eng._ensure()
+    fp64_peak = fp64_peak_tflops(probe_eng, dev)
+    peaks = measured_peaks()
+    # nvidia-smi's start-up (NVML init over every GPU of the box) stalls kernel launches for a moment: be past it
+    t_wait = time.time()
+    while len(clocks.rows) < 3 and time.time() - t_wait < 10.0:
+        time.sleep(0.05)
+
+    H = dr_block(a, dev, world, lo, C, q0, a.seed, K, a.warmup, a.burnin, True, fp64_peak)
+    clocks_summary = clocks.summary(H["t0"], H["t1"])
+    clocks.stop()
+    ms_total, grads, leaps = H["ms_total"], H["grads"], H["leaps"]
     sec = ms_total * 1e-3
     value = grads / sec
     fpg = FLOPS_PER_GRAD["funnel"](d)
-
-    # ESS over the timed transitions from streamed per-chain means (utils.get_ess_true), all ranks
+    mom, model, eng = H["mom"], H["model"], H["eng"]
     ess = mom.ess_true(model.true_mean(), model.true_std())
     rhat = mom.rhat()
     mean, std = mom.mean_std()
-    ess_min = float(ess.min())
 
-    # roofline of the dominant kernel: DR stage 0 (every chain integrates nleap steps)
+    # roofline of the dominant kernel: DR stage 0 (every chain integrates nleap steps), timed by events between the
+    # stage launches of single hmcb_drhmc_step calls run straight after the timed region
     L0 = max(a.nleap, 1)
-    st_ms = stats[3:3 + a.nprops].tolist()
+    st_ms = H["stage_ms"]
     s0_flops = C * (L0 + 1) * fpg
     achieved = s0_flops / (st_ms[0] * 1e-3) / 1e12
-    default_shape = (C == 1 << 20 and d == 50 and a.nleap == 150)
     roofline = {"bound": "fp64", "kernel": "k_transition_ws<Funnel,f64,EPL=50,MODE_DR0> (DR stage 0, warp-specialised)",
-                "achieved": achieved, "peak": fp64_peak_tflops, "unit": "TFLOP/s",
-                "frac": achieved / fp64_peak_tflops if fp64_peak_tflops else None,
-                # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (profiles/r1b_ncu_dr_stages.md);
-                # algorithmic HBM bytes are 2*C*d*8 + outputs = 0.87 GB, i.e. no re-reads
-                "traffic": 447266560 + 347079680 if default_shape else None,
-                "traffic_unit": "bytes per launch (HBM; the kernel is FP64-pipe-bound, HBM is at 5 % of its peak)",
+                "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak else None,
+                "traffic": None,
+                "traffic_note": "not measured in this run; one ncu --set full capture of this kernel at this shape read "
+                                "794,346,240 B per launch (profiles/r1b_ncu_dr_stages.md) against 2*C*d*8 + outputs = 0.87 GB "
+                                "algorithmic: the kernel is FP64-pipe-bound, HBM at 5 % of its peak",
                 "peak_source": "hmcb_probe_fma: register-resident DFMA loop measured in this run on this GPU "
                                "(MEASURED_PEAKS.json has no FP64 figure)",
-                "algorithmic_flops_per_launch": s0_flops, "avg_launch_ms": st_ms[0],
-                "stage_ms": st_ms, "stage_ms_sum": sum(st_ms),
-                "timing_note": "stage kernels timed by CUDA events recorded inside hmcb_drhmc_step (hmcb_profile) over %d "
-                               "transitions run straight after the timed region with the stages serialised on one stream; "
-                               "inside the timed region the library overlaps the stages of 2 chain ranges on 2 streams "
-                               "(ms_per_step is below the sum of the stage times for that reason)" % KR, "step_frac_all_stages": grads / world * fpg / sec / 1e12 / fp64_peak_tflops}
+                "algorithmic_flops_per_launch": s0_flops, "avg_launch_ms": st_ms[0], "stage_ms": st_ms, "stage_ms_sum": sum(st_ms),
+                "moments_kernel_ms": H["moments_ms"],
+                "timing_note": "stage kernels timed by CUDA events recorded inside hmcb_drhmc_step (hmcb_profile) over %d single "
+                               "transitions run straight after the timed region, stages serialised on one stream; the timed "
+                               "region itself runs %d chain ranges on %d streams, so its ms_per_step (%.3f) is to be compared "
+                               "with stage_ms_sum + moments_kernel_ms (%.3f)" %
+                               (H["stage_passes"], H["n_split"], H["n_split"], ms_total / K, sum(st_ms) + H["moments_ms"]),
+                "step_frac_all_stages": grads / world * fpg / sec / 1e12 / fp64_peak,
+                "hbm_peak_gbs": peaks["hbm_gbs"], "hbm_peak_source": peaks["source"],
+                "algorithmic_hbm_gbs_of_the_step": (2 * C * d * 8 + 5 * C * d * 8) / (ms_total / K * 1e-3) / 1e9}
+
+    strong = None
+    if world > 1 and a.scaling == "weak":
+        # the configuration as BASELINE.json words it: 2^20 chains IN TOTAL, sharded over the N GPUs
+        lo_s, hi_s = dist.shard_range(a.chains)
+        gs = torch.Generator().manual_seed(a.seed)
+        qs = (torch.rand(a.chains, d, generator=gs, dtype=torch.float64) * 2 - 1)[lo_s:hi_s].to(dev).contiguous()
+        S = dr_block(a, dev, world, lo_s, hi_s - lo_s, qs, a.seed, K, a.warmup, a.burnin, False, fp64_peak)
+        strong = {"chains_total": a.chains, "chains_per_gpu": (hi_s - lo_s), "ms_per_step": S["ms_total"] / K,
+                  "value": S["grads"] / (S["ms_total"] * 1e-3), "unit": "grad_evals/s", "scaling": "strong",
+                  "per_call": S["per_call"],
+                  "note": "same workload and timing method with the 2^20 chains divided over the %d GPUs; compare with the "
+                          "N=1 line's value for the strong-scaling efficiency" % world}
+        del S, qs
+
+    stationary = stationary_block(a, dev, world, lo, C, a.seed) if a.ess_steps > 0 else None
+    secondary = None
+    if not a.no_secondary:
+        secondary = secondary_block(a, dev, world, rank, fp64_peak, peaks)
 
     # end to end: public API, pinned host buffers in, host results out, every step
     e2e = None
     if not a.no_e2e:
         Ke = a.e2e_steps or max(3, min(K, 8))
         qh = torch.empty((C, d), dtype=torch.float64).pin_memory()
-        qh.copy_(q)
+        qh.copy_(H["q"])
         dr_e = algorithms.DRHMC(model, device=dev, seed=a.seed + 1, chain_offset=lo)
-        # the momentum is not brought back: the reference's sample loop discards the p its step returns
-        # (src/algorithms.py:546-551); the same call with p is timed after it and reported beside it
         for _ in range(2):
             r = dr_e.step(qh, a.nleap, a.step_size, a.nprops, a.stepfactor, want_p=False)
             qh = r[0]
@@ -383,7 +722,7 @@ def run_hmcb(a):
         torch.cuda.synchronize()
         dt = torch.tensor([time.time() - t0], dtype=torch.float64, device=dev)
         r = (qh,)
-        for _ in range(3):                                                       # warm the pinned p buffers
+        for _ in range(2):                                                       # warm the pinned p buffers
             r = dr_e.step(r[0], a.nleap, a.step_size, a.nprops, a.stepfactor)
         torch.cuda.synchronize()
         t1 = time.time()
@@ -391,6 +730,7 @@ def run_hmcb(a):
             r = dr_e.step(r[0], a.nleap, a.step_size, a.nprops, a.stepfactor)
         torch.cuda.synchronize()
         ms_with_p = 1e3 * (time.time() - t1) / 3
+        floor_ms = link_floor_ms(C, d, a.nprops, dev, world)
         ge = torch.tensor([float(g_e2e)], dtype=torch.float64, device=dev)
         if world > 1:
             torch.distributed.all_reduce(dt, op=torch.distributed.ReduceOp.MAX)
@@ -401,32 +741,99 @@ def run_hmcb(a):
                "d2h_bytes_per_step": d2h, "steps": Ke, "ms_per_step": 1e3 * float(dt[0]) / Ke,
                "api": "hmc_b200.algorithms.DRHMC.step(q_pinned_host, ..., want_p=False) -> host (q, None, code, avec, "
                       "counts); the reference's sample loop discards the returned momentum",
-               "ms_per_step_with_p_returned": ms_with_p, "d2h_bytes_per_step_with_p": d2h + C * d * 8}
+               "ms_per_step_with_p_returned": ms_with_p, "d2h_bytes_per_step_with_p": d2h + C * d * 8,
+               "link_floor_ms": floor_ms,
+               "link_floor_note": "all %d ranks at once doing ONLY this step's host-to-device and device-to-host copies from "
+                                  "pinned memory on two streams (no kernels): what the host links and memory allow" % world}
 
     if rank != 0:
         return
-    cpu = None
+    acf = autocorr_block(a, dev, a.seed) if a.acf_steps > 0 else None
+    gates = gates_block(dev)
+    cpu = cfg1 = None
     if not a.no_cpu_baseline and world == 1:
         cpu = cpu_baseline(a, a.cpu_seconds)
+        cfg1 = cpu_config1()
     line = {"metric": "grad_evals_per_sec", "value": value, "unit": "grad_evals/s", "n_gpus": world, "steps": K,
             "warmup": a.warmup, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": a.scaling,
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(a),
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(a, transitions_per_call=K, chain_ranges=H["n_split"]),
+            "timed_region": "ONE hmcb_drhmc_sample call: %d DRHMC transitions of every chain, %d chain ranges pipelined over "
+                            "%d streams, running moments folded in (bit-identical to %d single hmcb_drhmc_step calls)" %
+                            (K, H["n_split"], H["n_split"], K),
+            "per_call": H["per_call"],
             "leapfrog_steps_per_sec": (grads - leaps) / sec,
-            "ess_per_sec": ess_min / sec, "ess_min": ess_min, "ess_note": "min over dims of utils.get_ess_true over the "
-            "%d timed transitions of all chains (analytic funnel mean/std); chains started at U(-1,1), so it includes "
-            "remaining burn-in bias" % K,
-            "grad_evals_per_transition": grads / (K * n_total), "accept_rate": float(stats[-1]) / n_total,
-            "code_fractions": {"note": "rank 0: fraction of chain-transitions by DRHMC code (0 = rejected at every "
-                               "stage, j+1 = accepted at stage j)", "by_code": code_frac},
-            "rhat_max": float(rhat.max()),
-            "rhat_note": "R-hat (between- over within-chain variance, all-reduced moments) over the %d timed transitions "
-                         "only: with windows that short it mostly says how far a chain moves in %d transitions of the "
-                         "funnel, not whether the ensemble has converged" % (K, K), "v_mean": float(mean[0]), "v_std": float(std[0]),
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks.summary(t_wall0, t_wall1),
-            "gpu_launches": K * (n_split * a.nprops + 1),
-            "gpu_launches_note": "per step: %d chain ranges x %d DR stage kernels + 1 moments kernel (all libhmcb.so)"
-                                 % (n_split, a.nprops)}
+            "grad_evals_per_transition": grads / (K * n_total), "accept_rate": H["accepted"] / (K * n_total),
+            "code_fractions": {"note": "rank 0, last timed transition: fraction of chains by DRHMC code (0 = rejected at every "
+                               "stage, j+1 = accepted at stage j)", "by_code": H["code_frac"]},
+            "timed_window_diagnostics": {"ess_true_min": float(ess.min()), "rhat_max": float(rhat.max()), "v_mean": float(mean[0]),
+                                         "v_std": float(std[0]),
+                                         "note": "over the %d timed transitions only, chains started at U(-1,1) and burnt in for %d "
+                                                 "transitions: NOT stationary (the funnel's v needs thousands); the stationary "
+                                                 "figures are in 'stationary' and 'autocorr'" % (K, a.burnin)},
+            "stationary": stationary, "autocorr": acf,
+            "ess_per_sec": (stationary or {}).get("ess_true_min_per_sec"),
+            "gates": gates, "strong": strong, "secondary": secondary,
+            "roofline": roofline, "cpu_baseline": cpu, "config1_cpu": cfg1, "e2e": e2e, "clocks": clocks_summary,
+            "gpu_launches": K * H["n_split"] * (a.nprops + 1),
+            "gpu_launches_note": "timed region: %d transitions x %d chain ranges x (%d DR stage kernels + 1 counters/moments "
+                                 "kernel), all libhmcb.so" % (K, H["n_split"], a.nprops)}
     print(json.dumps(line), flush=True)
+
+
+def link_floor_ms(C, d, nprops, dev, world):
+    """The copies of one end-to-end step and nothing else, all ranks at once: H2D of q, D2H of q, code, avec, counts."""
+    import torch
+    from hmc_b200 import dist
+    pin = dict(pin_memory=True)
+    hq, hq2 = torch.empty((C, d), dtype=torch.float64, **pin), torch.empty((C, d), dtype=torch.float64, **pin)
+    hs = [torch.empty(C, dtype=torch.int32, **pin), torch.empty((C, nprops), dtype=torch.float64, **pin),
+          torch.empty((C, 3), dtype=torch.int32, **pin)]
+    dq, dq2 = torch.empty((C, d), dtype=torch.float64, device=dev), torch.zeros((C, d), dtype=torch.float64, device=dev)
+    ds = [torch.zeros_like(h, device=dev) for h in hs]
+    s_in, s_out = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+
+    def once():
+        with torch.cuda.stream(s_in):
+            dq.copy_(hq, non_blocking=True)
+        with torch.cuda.stream(s_out):
+            hq2.copy_(dq2, non_blocking=True)
+            for h, t in zip(hs, ds):
+                h.copy_(t, non_blocking=True)
+    once()
+    torch.cuda.synchronize()
+    dist.barrier()
+    t0 = time.time()
+    for _ in range(4):
+        once()
+    torch.cuda.synchronize()
+    dt = torch.tensor([time.time() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        torch.distributed.all_reduce(dt, op=torch.distributed.ReduceOp.MAX)
+    return 1e3 * float(dt[0]) / 4
+
+
+def cpu_config1():
+    """BASELINE.json config 1 exactly as stated: Neal's funnel d=10, pyhmc HMC, step 0.1, 20 leapfrog steps, ONE chain,
+    10,000 samples, on one host core (oracle/samplers.py hmc_step_pyhmc, the numpy port of src/pyhmc.py:64-69)."""
+    from oracle import models as om
+    from oracle import samplers
+    model = om.Funnel(10)
+    rng = np.random.Generator(np.random.PCG64(0))
+
+    class R:
+        normal = staticmethod(lambda size=None: rng.standard_normal(size))
+        uniform = staticmethod(lambda low=0.0, high=1.0, size=None: rng.uniform(low, high, size))
+    q = rng.uniform(-1, 1, 10)
+    grads = acc = 0
+    t0 = time.time()
+    for _ in range(10000):
+        q, p, code, Hs, cnt = samplers.hmc_step_pyhmc(model, q, 20, 0.1, R)
+        grads += cnt[1]
+        acc += code == 1.0
+    dt = time.time() - t0
+    return {"config": "funnel d=10, pyhmc.HMC.step, step 0.1, 20 leapfrog steps, 1 chain, 10,000 samples", "seconds": dt,
+            "grad_evals": grads, "grad_evals_per_s": grads / dt, "accept_rate": acc / 10000.0, "cores": 1, "kind": "port"}
 
 
 def main():
