@@ -527,7 +527,7 @@ def secondary_block(a, dev, world, rank, fp64_peak, peaks):
         tf = grads * flops_per_grad / (ms * 1e-3) / 1e12
         r = {"config": name, "ms_per_transition": ms, "grad_evals_per_s": grads / (ms * 1e-3), "algorithmic_tflops": tf, "bound": bound}
         if bound == "fp64":
-            r["frac_of_fp64_peak"] = tf / fp64_peak
+            r["frac_of_fp64_peak"] = tf / (fp64_peak * world)
         if extra:
             r.update(extra)
         rows.append(r)
@@ -572,8 +572,8 @@ def secondary_block(a, dev, world, rank, fp64_peak, peaks):
     grads = Ct * (L + 1)
     alg = grads * 4.0 * N * D / (ms * 1e-3) / 1e12
     row("cfg4 logistic regression N=100,000 D=128, HMC L=10 eps=0.01, 16,384 chains", ms, grads, 4.0 * N * D, bound="tensor",
-        extra={"frac_of_bf16_peak_algorithmic": alg / peaks["bf16_tflops"],
-               "executed_fp16_tflops": 3 * alg, "frac_of_bf16_peak_executed": 3 * alg / peaks["bf16_tflops"],
+        extra={"frac_of_bf16_peak_algorithmic": alg / (peaks["bf16_tflops"] * world),
+               "executed_fp16_tflops": 3 * alg, "frac_of_bf16_peak_executed": 3 * alg / (peaks["bf16_tflops"] * world),
                "peak": peaks["bf16_tflops"], "peak_source": peaks["source"],
                "note": "algorithmic = 4 N D flop per gradient (two GEMMs); executed = 3 fp16 products per algorithmic one "
                        "(hi*hi + hi*lo + lo*hi for 1e-5 parity with the float64 reference)"})
@@ -838,6 +838,12 @@ def cpu_config1():
 
 def main():
     a = parse()
+    # stdout carries exactly ONE line, the JSON: everything else any library prints there (NCCL's version banner ...)
+    # goes to stderr.  File descriptor 1 is pointed at stderr for the run; the JSON goes to the saved descriptor.
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(saved, "w")
     if a.impl == "reference":
         run_reference(a)
     else:
