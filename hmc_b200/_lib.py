@@ -92,6 +92,8 @@ SIGNATURES = {
     "hmcb_drhmc_sample": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
                                     C.c_int32, C.c_double, C.c_int32, C.POINTER(SampleIO), C.POINTER(StepOut),
                                     C.c_void_p, C.c_size_t, C.c_void_p]),
+    "hmcb_hmc_sample": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double, C.c_int32,
+                                  C.POINTER(SampleIO), C.POINTER(StepOut), C.c_void_p]),
     "hmcb_drhmc_step_static": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
                                          C.c_int32, C.c_double, C.c_int32, C.POINTER(StepOut), C.c_void_p]),
     "hmcb_moments_accumulate": (C.c_int, [C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_int64, C.c_int64,

@@ -507,6 +507,57 @@ int hmcb_hmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb
   return hmc_step_t<float>(e, model, chains, rng, n_leap, step_size, rule, out, st);
 }
 
+int hmcb_hmc_sample(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
+                    double step_size, int32_t rule, const hmcb_sample_io* io, const hmcb_step_out* out, void* stream) {
+  int rc;
+  if ((rc = check_model(model))) return rc;
+  if ((rc = check_chains(chains))) return rc;
+  HMCB_CHECK_ARG(rng != nullptr && io != nullptr, "rng/io is NULL");
+  HMCB_CHECK_ARG(rule == HMCB_RULE_PYHMC || rule == HMCB_RULE_ALG, "unknown accept rule %d", rule);
+  HMCB_CHECK_ARG(n_leap >= 0, "n_leap must be >= 0");
+  const int K = io->n_transitions;
+  HMCB_CHECK_ARG(K >= 1, "n_transitions must be >= 1");
+  HMCB_CHECK_ARG(K == 1 || (!rng->p_inject && !rng->u_inject && !rng->p_prev),
+                 "injected draws and a partial momentum refresh are defined for n_transitions == 1 only");
+  HMCB_CHECK_ARG((io->moment_sum == nullptr) == (io->moment_sumsq == nullptr), "give both moment_sum and moment_sumsq or neither");
+  HMCB_CHECK_ARG(!io->n_accept || (out && out->code), "n_accept needs out->code");
+  if (chains->n_chains == 0) return 0;
+  const Entry* e = choose_entry(*model);
+  if (!e) return HMCB_E_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  // the whole loop in one launch where the shape has the kernel for it and nothing needs the states in between
+  if (K > 1 && !io->moment_sum && model->dtype == HMCB_F64 && model->kind != HMCB_MODEL_GAUSSIAN) {
+    MultiHmcArgs<double> m;
+    fill_args(m.a, model, chains, rng, out);
+    m.a.rule = rule;
+    m.a.nprops = 1;
+    m.a.L[0] = n_leap;
+    m.a.eps[0] = step_size;
+    m.K = K;
+    m.n_accept = io->n_accept;
+    if ((rc = e->fn(*model, OP_HMC_MULTI, &m, st))) return rc;
+    if (m.applied) return 0;
+  }
+  // otherwise: K launches, later ones in place on the new state; counters are the same for every transition
+  for (int k = 0; k < K; ++k) {
+    hmcb_chains cs = *chains;
+    hmcb_rng rs = *rng;
+    if (k > 0) cs.q_in = cs.q_out;
+    rs.iteration = rng->iteration + (uint64_t)k;
+    if (model->dtype == HMCB_F64) rc = hmc_step_t<double>(e, model, &cs, &rs, n_leap, step_size, rule, out, st);
+    else rc = hmc_step_t<float>(e, model, &cs, &rs, n_leap, step_size, rule, out, st);
+    if (rc) return rc;
+    rc = launch_post_transition(model->dtype, chains->n_chains, model->d, cs.q_out, cs.stride_chain, cs.stride_dim, io->moment_sum,
+                                io->moment_sumsq, nullptr, nullptr, 0, out ? out->code : nullptr, 1, 1, io->n_accept, st);
+    if (rc) return rc;
+  }
+  if (K > 1 && out && out->counts) {
+    // Hcount, Vgcount, leapcount of one HMC transition are (2, n_leap + 1, 1) whatever happens (src/pyhmc.py:69)
+    rc = launch_scale_counts(out->counts, chains->n_chains, K, st);
+  }
+  return rc;
+}
+
 int hmcb_leapfrog(const hmcb_model* model, const hmcb_chains* chains, const void* p_in, void* p_out, int32_t n_leap,
                   double step_size, void* stream) {
   int rc;
@@ -746,7 +797,7 @@ int hmcb_drhmc_sample(const hmcb_model* model, const hmcb_chains* chains, const 
       void* msum = io->moment_sum ? (char*)io->moment_sum + (size_t)lo * model->d * ts : nullptr;
       void* msq = io->moment_sumsq ? (char*)io->moment_sumsq + (size_t)lo * model->d * ts : nullptr;
       rc = launch_post_transition(model->dtype, hi - lo, model->d, cs.q_out, cs.stride_chain, cs.stride_dim, msum, msq, counts_k,
-                                  (K > 1) ? counts_tot : nullptr, k == 0, os.code, min_accept,
+                                  (K > 1) ? counts_tot : nullptr, k == 0, os.code, min_accept, 1 << 30,
                                   io->n_accept ? io->n_accept + lo : nullptr, on);
     }
   }

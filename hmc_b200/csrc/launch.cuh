@@ -13,7 +13,7 @@
 namespace hmcb {
 
 enum Op { OP_HMC = 0, OP_DR0 = 1, OP_DRN = 2, OP_LEAPFROG = 3, OP_LOGPGRAD = 4, OP_QUERY = 5, OP_MALA = 6, OP_ADHMC = 7,
-          OP_QUERY_AD = 8, OP_GHMC = 9, OP_ADWALK = 10, OP_QUERY_WALK = 11 };
+          OP_QUERY_AD = 8, OP_GHMC = 9, OP_ADWALK = 10, OP_QUERY_WALK = 11, OP_HMC_MULTI = 12 };
 constexpr int kGhmcMaxEpl = 32;  // GHMC keeps q, p and the gradient: 3*EPL values per lane
 constexpr int kMalaMaxEpl = 28;  // MALA keeps q, grad, q1, grad1 in registers: 4*EPL values per lane
 
@@ -38,6 +38,15 @@ struct Registrar {
 
 // pick the compiled shape for this model; nullptr (+ error set) if none fits
 const Entry* choose_entry(const hmcb_model& hm, int max_epl = 1 << 30);
+
+// K HMC transitions in one launch (k_hmc_multi_ws); `applied` tells the caller whether this shape has that kernel
+template <typename T>
+struct MultiHmcArgs {
+  TransArgs<T> a;
+  int32_t K;
+  int32_t* n_accept;
+  int32_t applied;
+};
 
 // leapfrog-only / logp+grad kernels share the transition kernel's device code
 template <typename T>
@@ -115,7 +124,9 @@ int max_optin_smem();  // per-block opt-in shared memory limit of the current de
 // moments.cu: the per-transition bookkeeping of a sample loop (running moments, summed work counters, accept counts)
 int launch_post_transition(int32_t dtype, int64_t n_chains, int32_t d, const void* q, int64_t sc, int64_t sd, void* sum,
                            void* sumsq, const int32_t* counts_k, int32_t* counts_tot, int first, const int32_t* code,
-                           int min_accept_code, int32_t* n_accept, cudaStream_t st);
+                           int min_accept_code, int max_accept_code, int32_t* n_accept, cudaStream_t st);
+
+int launch_scale_counts(int32_t* counts, int64_t n_chains, int K, cudaStream_t st);
 
 // gauss_dmma.cu: dense-Gaussian HMC transition on the FP64 tensor path; returns 1 when it does not apply
 int gauss_dmma_hmc(const hmcb_model& hm, const TransArgs<double>& a, cudaStream_t st);
@@ -189,6 +200,25 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
         return 0;
       }
     }
+  }
+  if (op == OP_HMC_MULTI) {
+    MultiHmcArgs<T>& m = *(MultiHmcArgs<T>*)args;
+    m.applied = 0;
+    if constexpr (LPC == 1 && UNITM && sizeof(T) == 8 && EPL >= 20 && !GAUSS) {
+      const TransArgs<T>& a = m.a;
+      const size_t bytes = (size_t)EPL * kWsComputeThreads * (sizeof(T) + 2 * sizeof(float)) + 64;
+      if (!a.p_inject && !a.u_inject && !a.p_prev && !a.p0_out && !(a.rng_flags & HMCB_RNG_NORMAL_F64) && a.n_chains >= 4096 &&
+          bytes <= (size_t)max_optin_smem() && !getenv("HMCB_NO_WS")) {
+        auto k = k_hmc_multi_ws<Model, T, EPL>;
+        HMCB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        const int64_t need = (a.n_chains + kWsComputeThreads - 1) / kWsComputeThreads;
+        const int grid = (int)(need < sm_count() ? need : sm_count());
+        k<<<grid, kWsThreads, bytes, st>>>(model, a, m.K, m.n_accept);
+        HMCB_CUDA(cudaPeekAtLastError());
+        m.applied = 1;
+      }
+    }
+    return 0;
   }
   switch (op) {
     case OP_HMC: {

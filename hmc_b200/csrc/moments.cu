@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(256) k_post_transition(const T* __restrict__ q
                                                          T* __restrict__ sum, T* __restrict__ sumsq,
                                                          const int32_t* __restrict__ counts_k, int32_t* __restrict__ counts_tot,
                                                          int first, const int32_t* __restrict__ code, int min_accept_code,
-                                                         int32_t* __restrict__ n_accept) {
+                                                         int max_accept_code, int32_t* __restrict__ n_accept) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (sum) {
@@ -47,13 +47,13 @@ __global__ void __launch_bounds__(256) k_post_transition(const T* __restrict__ q
     for (int64_t i = i0; i < 3 * n_chains; i += stride) counts_tot[i] = first ? counts_k[i] : counts_tot[i] + counts_k[i];
   }
   if (n_accept) {
-    for (int64_t i = i0; i < n_chains; i += stride) n_accept[i] += (code[i] >= min_accept_code) ? 1 : 0;
+    for (int64_t i = i0; i < n_chains; i += stride) n_accept[i] += (code[i] >= min_accept_code && code[i] <= max_accept_code) ? 1 : 0;
   }
 }
 
 int launch_post_transition(int32_t dtype, int64_t n_chains, int32_t d, const void* q, int64_t sc, int64_t sd, void* sum,
                            void* sumsq, const int32_t* counts_k, int32_t* counts_tot, int first, const int32_t* code,
-                           int min_accept_code, int32_t* n_accept, cudaStream_t st) {
+                           int min_accept_code, int max_accept_code, int32_t* n_accept, cudaStream_t st) {
   if (!sum && !counts_tot && !n_accept) return 0;
   const int64_t n = n_chains * (sum ? d : 3);
   int64_t blocks = (n + 255) / 256;
@@ -62,10 +62,24 @@ int launch_post_transition(int32_t dtype, int64_t n_chains, int32_t d, const voi
   if (blocks < 1) blocks = 1;
   if (dtype == HMCB_F64)
     k_post_transition<double><<<(int)blocks, 256, 0, st>>>((const double*)q, sc, sd, d, n_chains, (double*)sum, (double*)sumsq,
-                                                           counts_k, counts_tot, first, code, min_accept_code, n_accept);
+                                                           counts_k, counts_tot, first, code, min_accept_code, max_accept_code, n_accept);
   else
     k_post_transition<float><<<(int)blocks, 256, 0, st>>>((const float*)q, sc, sd, d, n_chains, (float*)sum, (float*)sumsq,
-                                                          counts_k, counts_tot, first, code, min_accept_code, n_accept);
+                                                          counts_k, counts_tot, first, code, min_accept_code, max_accept_code, n_accept);
+  HMCB_CUDA(cudaPeekAtLastError());
+  return 0;
+}
+
+__global__ void __launch_bounds__(256) k_scale_counts(int32_t* __restrict__ counts, int64_t n, int K) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) counts[i] *= K;
+}
+
+int launch_scale_counts(int32_t* counts, int64_t n_chains, int K, cudaStream_t st) {
+  int64_t blocks = (3 * n_chains + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  k_scale_counts<<<(int)blocks, 256, 0, st>>>(counts, 3 * n_chains, K);
   HMCB_CUDA(cudaPeekAtLastError());
   return 0;
 }

@@ -92,4 +92,129 @@ __global__ void __launch_bounds__(kWsThreads, 1) k_transition_ws(const Model mod
   }
 }
 
+// ------------------------------------------------------------------ K HMC transitions per launch
+// The loop of HMC.sample (src/algorithms.py:244-250; scripts_old/funnel/funnelmpi.py:152-162) inside the
+// warp-specialised kernel: a chain's position stays in its thread's registers for all K transitions and the start
+// point q0 of the current one -- needed for the no-move test and to come back to on rejection -- in a shared-memory
+// tile, so a transition touches global memory only for its accept test's outputs.  At short trajectories (L = 20,
+// the reference's usual setting) that is what a transition costs beside its leapfrog steps: one launch per transition
+// spends more time on the strided load and store of q than on integrating.  The helper warpgroup produces the momenta
+// of (round, transition) pairs one tile ahead, as above.  Every draw is the same function of (seed, global chain id,
+// iteration + k) as in k transitions by single launches, so the results are bit-identical to those.
+template <class Model, typename T, int EPL>
+__global__ void __launch_bounds__(kWsThreads, 1) k_hmc_multi_ws(const Model model, const TransArgs<T> a, const int K,
+                                                                int32_t* __restrict__ n_accept) {
+  static_assert(sizeof(T) == 8, "the warp-specialised kernel is float64 only");
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* sQ = reinterpret_cast<T*>(smem_raw);                                           // [EPL][256] q0 of the running transition
+  float* sP = reinterpret_cast<float*>(sQ + (size_t)EPL * kWsComputeThreads);       // [2][EPL][256] momenta
+  uint64_t* full = reinterpret_cast<uint64_t*>(sP + 2 * EPL * kWsComputeThreads);
+  uint64_t* empty = full + 2;
+  const int tid = threadIdx.x, wg = tid >> 7;
+  if (tid == 0) {
+    for (int s = 0; s < 2; ++s) {
+      lr::mbar_init(full + s, kWsThreads - kWsComputeThreads);
+      lr::mbar_init(empty + s, kWsComputeThreads);
+    }
+    lr::fence_barrier_init();
+  }
+  __syncthreads();
+  const int d = a.d;
+  const int64_t per_round = (int64_t)gridDim.x * kWsComputeThreads;
+  const int rounds = (int)((a.n_chains + per_round - 1) / per_round);
+  if (wg == 2) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+    const int ht = tid - kWsComputeThreads;
+    uint32_t t = 0;
+    for (int r = 0; r < rounds; ++r) {
+      for (int k = 0; k < K; ++k, ++t) {
+        const int s = t & 1;
+        lr::mbar_wait(empty + s, ((t >> 1) & 1) ^ 1);
+        float* dst = sP + (size_t)s * EPL * kWsComputeThreads;
+#pragma unroll 1
+        for (int h = 0; h < 2; ++h) {
+          const int cth = ht + 128 * h;
+          const int64_t chain = ((int64_t)r * gridDim.x + blockIdx.x) * kWsComputeThreads + cth;
+          if (chain < a.n_chains) {
+            const uint64_t gchain = (uint64_t)(a.chain_offset + chain);
+#pragma unroll 1
+            for (int b = 0; b < (EPL + 3) / 4; ++b) {
+              uint32_t w[4];
+              float z[4];
+              Philox::gen(a.seed, gchain, a.iteration + (uint32_t)k, STREAM_MOMENTUM, (uint32_t)b, w);
+              normal4_f32(w, z);
+#pragma unroll
+              for (int e = 0; e < 4; ++e)
+                if (4 * b + e < EPL) dst[(4 * b + e) * kWsComputeThreads + cth] = (4 * b + e < d) ? z[e] : 0.f;
+            }
+          }
+        }
+        lr::mbar_arrive(full + s);
+      }
+    }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 240;");
+    GroupCtx<T> c;
+    c.lane = 0; c.d = d; c.mask = 0xffffffffu; c.smem_q = nullptr;
+    T minv[1] = {T(1)};
+    const int N = a.L[0] > 1 ? a.L[0] : 1;
+    uint32_t t = 0;
+    for (int r = 0; r < rounds; ++r) {
+      const int64_t chain = ((int64_t)r * gridDim.x + blockIdx.x) * kWsComputeThreads + tid;
+      const bool live = chain < a.n_chains;
+      const int64_t qoff = (live ? chain : 0) * a.sc;
+      T q[EPL], p[EPL];
+      load_vec<T, EPL, 1>(q, a.q_in, qoff, a.sd, 0, d, T(1));
+#pragma unroll
+      for (int e = 0; e < EPL; ++e) sQ[e * kWsComputeThreads + tid] = q[e];
+      int nacc = 0;
+      for (int k = 0; k < K; ++k, ++t) {
+        const int s = t & 1;
+        lr::mbar_wait(full + s, (t >> 1) & 1);
+        const float* src = sP + (size_t)s * EPL * kWsComputeThreads + tid;
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) p[e] = (T)src[e * kWsComputeThreads];
+        lr::mbar_arrive(empty + s);
+        if (live) {
+          // one transition, as finish_single<MODE_HMC> (src/pyhmc.py:64-69, src/algorithms.py:192-198)
+          const T K0 = kinetic<T, EPL, 1, true>(p, minv, c.mask);
+          T V0, V1;
+          leapfrog<Model, T, EPL, 1, true>(model, q, p, minv, N, a.eps[0], c, V0, V1);
+          const T H0 = V0 + K0;
+          const T H1 = V1 + kinetic<T, EPL, 1, true>(p, minv, c.mask);
+          const T dq = diff_sum<T, EPL, 1>(q, sQ, tid, kWsComputeThreads, 0, d);   // sum(q0 - q1), src/pyhmc.py:57
+          const T prob = t_exp<T>(H0 - H1);
+          const bool bad = t_bad(prob) || dq == T(0);
+          const double u = draw_uniform<T>(a, chain, 0, (uint32_t)k);
+          const T pm = prob < T(1) ? prob : T(1);
+          const bool accept = !bad && !(u > (double)pm);
+          if (k == K - 1) {
+            if (a.code) a.code[chain] = bad ? (a.rule == HMCB_RULE_PYHMC ? 2 : -1) : (accept ? 1 : 0);
+            if (a.energies) { a.energies[2 * chain] = H0; a.energies[2 * chain + 1] = H1; }
+            if (a.accept_prob) a.accept_prob[chain] = (accept && !t_bad(prob)) ? pm : T(0);
+            if (a.p_out) {
+              if (!accept) fill_normals<T, EPL, 1>(p, a.seed, (uint64_t)(a.chain_offset + chain), a.iteration + (uint32_t)k, 0, d,
+                                                  a.rng_flags);
+              store_vec<T, EPL, 1>(p, a.p_out, qoff, a.sd, 0, d);
+            }
+          }
+          if (accept) {
+            ++nacc;
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) sQ[e * kWsComputeThreads + tid] = q[e];
+          } else {
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) q[e] = sQ[e * kWsComputeThreads + tid];
+          }
+        }
+      }
+      if (live) {
+        store_vec<T, EPL, 1>(q, a.q_out, qoff, a.sd, 0, d);
+        if (n_accept) n_accept[chain] += nacc;
+        if (a.counts) { a.counts[3 * chain] = 2 * K; a.counts[3 * chain + 1] = K * (N + 1); a.counts[3 * chain + 2] = K; }
+      }
+    }
+  }
+}
+
 }  // namespace hmcb

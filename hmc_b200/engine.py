@@ -233,6 +233,34 @@ class Engine:
         out["_keep"] = keep
         return out
 
+    def hmc_sample(self, q, n_leap, step_size, rule, n_transitions, msum=None, msumsq=None, n_accept=None, q_out=None,
+                   want_p=False):
+        """hmcb_hmc_sample on device tensor q [C,d]: n_transitions HMC transitions of every chain in one call (one
+        launch where the shape has the fused kernel).  Returns the state after the last transition, its code and
+        energies, and the work counters of all transitions."""
+        m = self._ensure()
+        C_ = q.shape[0]
+        with torch.cuda.device(self.device):
+            q_out = torch.empty_like(q) if q_out is None else q_out
+            out = {"q": q_out, "p": torch.empty_like(q) if want_p else None,
+                   "code": torch.empty(C_, dtype=torch.int32, device=self.device),
+                   "Hs": torch.empty((C_, 2), dtype=self.dtype, device=self.device),
+                   "counts": torch.empty((C_, 3), dtype=torch.int32, device=self.device)}
+            so = _lib.StepOut()
+            so.p_out, so.code, so.energies, so.counts = (_lib.ptr(out["p"]), _lib.ptr(out["code"]), _lib.ptr(out["Hs"]),
+                                                         _lib.ptr(out["counts"]))
+            io = _lib.SampleIO()
+            io.n_transitions = int(n_transitions)
+            io.moment_sum, io.moment_sumsq, io.n_accept = _lib.ptr(msum), _lib.ptr(msumsq), _lib.ptr(n_accept)
+            ch = self._chains(q, q_out)
+            r, keep = self._rng(None, None, 1, C_)
+            if self.is_logistic:
+                raise _lib.HmcbError("hmc_sample is not available for the logistic-regression model")
+            _lib.check(self.lib.hmcb_hmc_sample(C.byref(m), C.byref(ch), C.byref(r), int(n_leap), float(step_size), int(rule),
+                                                C.byref(io), C.byref(so), self._stream()))
+        self.iteration += int(n_transitions)
+        return out
+
     def drhmc_sample(self, q, n_leap, step_size, nprops, stepfactor, n_transitions, msum=None, msumsq=None,
                      n_accept=None, q_out=None, want_p=False, convention=0, code_out=None, counts_out=None,
                      want_avec=True, p=None, u=None):

@@ -197,6 +197,20 @@ int hmcb_drhmc_sample(const hmcb_model* model, const hmcb_chains* chains, const 
                       const hmcb_sample_io* io, const hmcb_step_out* out, void* workspace, size_t workspace_bytes,
                       void* stream);
 
+/* K vanilla HMC transitions of every chain in ONE call: the loop of HMC.sample (src/algorithms.py:244-250;
+ * scripts_old/funnel/funnelmpi.py:152-162 runs it over PyHMC.hmc_step).  Each transition is
+ * hmcb_hmc_step's, bit for bit (transition k draws with iteration rng->iteration + k).  For float64
+ * thread-per-chain shapes with the unit metric (e.g. the d=50 funnel) and no moments requested the
+ * whole loop is one launch: a chain's position stays in registers, the start point of the running
+ * transition in shared memory (hmc_b200/csrc/transition_ws.cuh, k_hmc_multi_ws) -- at L = 20 a
+ * transition by single launches spends more time loading and storing q than integrating.  Other
+ * shapes, and calls that fold the running moments, run K launches inside this one call.  io and out
+ * as for hmcb_drhmc_sample: out holds the LAST transition's code / energies / p_out / accept_prob,
+ * counts = K x (2, n_leap+1, 1); p0_out is not provided for K > 1. */
+int hmcb_hmc_sample(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng,
+                    int32_t n_leap, double step_size, int32_t rule, const hmcb_sample_io* io,
+                    const hmcb_step_out* out, void* stream);
+
 /* hmcb_drhmc_step without a caller-supplied workspace.  No counterpart in the
  * reference (its Python never manages device memory); added for hosts that cannot
  * give us scratch: a thin C / ctypes caller that only holds the q and output buffers

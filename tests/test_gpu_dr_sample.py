@@ -138,3 +138,54 @@ def test_in_place_and_repeated_launches():
     assert torch.equal(q, ref["q"])
     out = b.drhmc_sample(q, 9, 0.3, 3, 2.0, 3, q_out=q)
     assert torch.equal(q, ref2["q"]) and torch.equal(out["counts"], ref2["counts"])
+
+
+# ------------------------------------------------------------------ K vanilla HMC transitions per call
+@pytest.mark.parametrize("kind,d,C", [("funnel", 50, 4096 + 300), ("funnel", 50, 70000), ("funnel", 20, 5000), ("funnel", 10, 5000),
+                                      ("rosenbrock", 20, 5000), ("gaussian", 20, 3000)])
+@pytest.mark.parametrize("rule", [_lib.RULE_PYHMC, _lib.RULE_ALG])
+def test_k_hmc_transitions_in_one_call_equal_k_single_calls(kind, d, C, rule):
+    """hmcb_hmc_sample: one fused launch for float64 thread-per-chain shapes (d=50, d=20 funnel: k_hmc_multi_ws), K launches
+    inside the call for the others -- either way identical to K hmcb_hmc_step calls."""
+    from hmc_b200 import pyhmc
+    K, L, eps = 7, 9, (0.25 if kind == "funnel" else 0.05)
+    dev = _dev()
+    q0 = torch.as_tensor(_q0(kind, C, d, 17), device=dev)
+    a = pyhmc.HMC(_model(kind, d), device=dev, seed=31, chain_offset=11).engine
+    b = pyhmc.HMC(_model(kind, d), device=dev, seed=31, chain_offset=11).engine
+    a.iteration = b.iteration = 3
+    q = q0
+    nacc = torch.zeros(C, dtype=torch.int32, device=dev)
+    for k in range(K):
+        r = a.hmc_step(q, L, eps, rule)
+        q = r["q"]
+        nacc += (r["code"] == 1).int()
+    macc = torch.zeros(C, dtype=torch.int32, device=dev)
+    rb = b.hmc_sample(q0, L, eps, rule, K, n_accept=macc, want_p=True)
+    assert torch.equal(rb["q"], q), "%d chains differ" % (rb["q"] != q).any(dim=1).sum().item()
+    assert torch.equal(rb["code"], r["code"]) and torch.equal(rb["Hs"], r["Hs"]) and torch.equal(rb["p"], r["p"])
+    assert torch.equal(macc, nacc)
+    assert (rb["counts"] == torch.tensor([2 * K, K * (L + 1), K], dtype=torch.int32, device=dev)).all()
+    assert 0.3 < nacc.double().mean().item() / K < 1.0
+
+
+def test_k_hmc_transitions_with_moments_and_in_place():
+    from hmc_b200 import pyhmc
+    d, C, K, L, eps = 50, 6000, 5, 6, 0.2
+    dev = _dev()
+    q0 = torch.as_tensor(_q0("funnel", C, d, 19), device=dev)
+    a = pyhmc.HMC(models.Funnel(d), device=dev, seed=2).engine
+    b = pyhmc.HMC(models.Funnel(d), device=dev, seed=2).engine
+    q = q0
+    s1, s2 = torch.zeros_like(q0), torch.zeros_like(q0)
+    for k in range(K):
+        q = a.hmc_step(q, L, eps, _lib.RULE_PYHMC)["q"]
+        a.moments_accumulate(q, s1, s2)
+    t1, t2 = torch.zeros_like(q0), torch.zeros_like(q0)
+    qb = q0.clone()
+    b.hmc_sample(qb, L, eps, _lib.RULE_PYHMC, K, msum=t1, msumsq=t2, q_out=qb)
+    assert torch.equal(qb, q) and torch.equal(t1, s1) and torch.equal(t2, s2)
+    qc = q0.clone()
+    c = pyhmc.HMC(models.Funnel(d), device=dev, seed=2).engine
+    c.hmc_sample(qc, L, eps, _lib.RULE_PYHMC, K, q_out=qc)          # fused kernel, in place
+    assert torch.equal(qc, q)
