@@ -526,17 +526,24 @@ int hmcb_hmc_sample(const hmcb_model* model, const hmcb_chains* chains, const hm
   if (!e) return HMCB_E_UNSUPPORTED;
   cudaStream_t st = (cudaStream_t)stream;
   // the whole loop in one launch where the shape has the kernel for it and nothing needs the states in between
-  if (K > 1 && !io->moment_sum && model->dtype == HMCB_F64 && model->kind != HMCB_MODEL_GAUSSIAN) {
-    MultiHmcArgs<double> m;
-    fill_args(m.a, model, chains, rng, out);
-    m.a.rule = rule;
-    m.a.nprops = 1;
-    m.a.L[0] = n_leap;
-    m.a.eps[0] = step_size;
-    m.K = K;
-    m.n_accept = io->n_accept;
-    if ((rc = e->fn(*model, OP_HMC_MULTI, &m, st))) return rc;
-    if (m.applied) return 0;
+  if (K > 1 && !io->moment_sum && model->kind != HMCB_MODEL_GAUSSIAN) {
+    int applied = 0;
+    if (model->dtype == HMCB_F64) {
+      MultiHmcArgs<double> m;
+      fill_args(m.a, model, chains, rng, out);
+      m.a.rule = rule; m.a.nprops = 1; m.a.L[0] = n_leap; m.a.eps[0] = step_size;
+      m.K = K; m.n_accept = io->n_accept;
+      if ((rc = e->fn(*model, OP_HMC_MULTI, &m, st))) return rc;
+      applied = m.applied;
+    } else {
+      MultiHmcArgs<float> m;
+      fill_args(m.a, model, chains, rng, out);
+      m.a.rule = rule; m.a.nprops = 1; m.a.L[0] = n_leap; m.a.eps[0] = (float)step_size;
+      m.K = K; m.n_accept = io->n_accept;
+      if ((rc = e->fn(*model, OP_HMC_MULTI, &m, st))) return rc;
+      applied = m.applied;
+    }
+    if (applied) return 0;
   }
   // otherwise: K launches, later ones in place on the new state; counters are the same for every transition
   for (int k = 0; k < K; ++k) {

@@ -182,8 +182,13 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
       // (nor with the exact f64 normal generator: the helper warpgroup draws with normal4_f32 only, and every
       // other place that re-draws p0 -- the DR stages >= 1, p_out of rejected chains -- would use the f64 one)
       if (!a.p_inject && !a.p_prev && !(a.rng_flags & HMCB_RNG_NORMAL_F64) && a.n_chains >= 4096) {
-        a.tile_io = 0;   // measured: the staging tile does not pay in the warp-specialised kernel (L=150: 2.02 -> 2.18 ms)
-        const size_t ws_smem = 2 * (size_t)EPL * kWsComputeThreads * sizeof(float) + 64;
+        // (the per-warp staging tile of the plain kernel does not pay here: L=150 2.02 -> 2.18 ms.)  tile_io instead
+        // selects a shared-memory copy of q0 for the no-move test and the copy-through of rejected chains
+        // (funnel d=50, 2^20 chains: HMC L=20 0.748 -> 0.614 ms, L=150 2.055 -> 2.002 ms, DR stage 0 1.975 -> 1.948 ms)
+        const size_t q0s_bytes = (size_t)EPL * kWsComputeThreads * sizeof(T);
+        const size_t base_smem = 2 * (size_t)EPL * kWsComputeThreads * sizeof(float) + 64;
+        a.tile_io = (base_smem + q0s_bytes <= (size_t)max_optin_smem() && !(getenv("HMCB_WS_Q0S") && !atoi(getenv("HMCB_WS_Q0S")))) ? 1 : 0;
+        const size_t ws_smem = base_smem + (a.tile_io ? q0s_bytes : 0);
         const int grid = (int)((a.n_chains + kWsComputeThreads - 1) / kWsComputeThreads < sm_count()
                                    ? (a.n_chains + kWsComputeThreads - 1) / kWsComputeThreads
                                    : sm_count());
@@ -216,6 +221,19 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
         k<<<grid, kWsThreads, bytes, st>>>(model, a, m.K, m.n_accept);
         HMCB_CUDA(cudaPeekAtLastError());
         m.applied = 1;
+      }
+    }
+    if constexpr (!GAUSS) {
+      if (!m.applied) {
+        const TransArgs<T>& a = m.a;
+        if (!a.p_inject && !a.u_inject && !a.p_prev && !a.p0_out && !getenv("HMCB_NO_MULTI")) {
+          auto k = k_hmc_multi<Model, T, EPL, LPC, UNITM, THREADS, MINB>;
+          const size_t bytes = (size_t)EPL * THREADS * sizeof(T);
+          if ((rc = prep_smem(k, max_blocks, bytes))) return rc;
+          k<<<grid_for(a.n_chains, max_blocks), THREADS, bytes, st>>>(model, a, m.K, m.n_accept);
+          HMCB_CUDA(cudaPeekAtLastError());
+          m.applied = 1;
+        }
       }
     }
     return 0;

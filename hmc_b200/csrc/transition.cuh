@@ -302,9 +302,12 @@ __device__ __forceinline__ void warp_tile_copy(T* tile, int rs, T* __restrict__ 
 template <class Model, typename T, int EPL, int LPC, bool UNITM, int MODE>
 __device__ __forceinline__ void finish_single(const Model& model, const TransArgs<T>& a, const GroupCtx<T>& c,
                                               const T (&minv)[UNITM ? 1 : EPL], int64_t chain, int64_t qoff,
-                                              T (&q)[EPL], T (&p)[EPL], T* trow = nullptr) {
+                                              T (&q)[EPL], T (&p)[EPL], T* trow = nullptr, const T* q0s = nullptr,
+                                              int q0sd = 0) {
   // trow: this chain's row of the warp tile (holds q0; takes the new q on acceptance), or nullptr when
-  // the state is read from and written to global memory directly
+  // the state is read from and written to global memory directly.  q0s: a read-only copy of q0 in shared memory,
+  // element i at q0s[i*q0sd] (the warp-specialised kernel keeps one: the no-move test and the copy-through of
+  // rejected chains then need no second strided read of q_in)
   using Lay = Layout<EPL, LPC>;
   const int d = a.d;
   int cH, cVg, cLeap;
@@ -317,7 +320,8 @@ __device__ __forceinline__ void finish_single(const Model& model, const TransArg
     const T H1 = V1 + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
     cH = 2; cVg = N + 1; cLeap = 1;
     // sum(q0 - q1) == 0 is the reference's "did not move" test (src/pyhmc.py:57)
-    T dq = trow ? diff_sum<T, EPL, LPC>(q, trow, 0, 1, c.lane, d) : diff_sum<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d);
+    T dq = trow ? diff_sum<T, EPL, LPC>(q, trow, 0, 1, c.lane, d)
+                : (q0s ? diff_sum<T, EPL, LPC>(q, q0s, 0, q0sd, c.lane, d) : diff_sum<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d));
     dq = group_sum_masked<LPC, T>(dq, c.mask);
     T prob = t_exp<T>(H0 - H1);
 
@@ -384,7 +388,7 @@ __device__ __forceinline__ void finish_single(const Model& model, const TransArg
 #pragma unroll
         for (int s = 0; s < EPL; ++s) {
           const int i = Lay::elem(c.lane, s);
-          if (i < d) a.q_out[qoff + i * a.sd] = a.q_in[qoff + i * a.sd];
+          if (i < d) a.q_out[qoff + i * a.sd] = q0s ? q0s[i * q0sd] : a.q_in[qoff + i * a.sd];
         }
       }
       if (a.p_out) {
@@ -657,6 +661,94 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
           }
         }
       }
+    }
+  }
+}
+
+// ------------------------------------------------------------------ K HMC transitions per launch, any shape
+// The loop of HMC.sample (src/algorithms.py:244-250) for one chain per group of lanes: the position stays in registers
+// over the K transitions, the start point of the running transition (no-move test, come-back on rejection) in shared
+// memory, slot s of thread t at sQ[s*THREADS + t].  The warp-specialised form of the same loop for float64
+// thread-per-chain shapes is k_hmc_multi_ws (transition_ws.cuh).  Transition k draws with iteration a.iteration + k:
+// bit-identical to K launches of k_transition<MODE_HMC>.
+template <class Model, typename T, int EPL, int LPC, bool UNITM, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) k_hmc_multi(const Model model, const TransArgs<T> a, const int K,
+                                                             int32_t* __restrict__ n_accept) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  using Lay = Layout<EPL, LPC>;
+  constexpr int GPB = THREADS / LPC;
+  const int d = a.d;
+  T* sQ = reinterpret_cast<T*>(smem_raw) + threadIdx.x;
+  GroupCtx<T> c;
+  c.lane = threadIdx.x & (LPC - 1);
+  c.d = d;
+  const int group_in_warp = (threadIdx.x & 31) / LPC;
+  c.mask = (LPC == 32) ? 0xffffffffu : (((1u << LPC) - 1u) << (group_in_warp * LPC));
+  c.smem_q = nullptr;
+  T minv[UNITM ? 1 : EPL];
+  if (!UNITM) {
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) {
+      const int i = Lay::elem(c.lane, s);
+      minv[UNITM ? 0 : s] = (i < d) ? a.minv[i] : T(1);
+    }
+  } else {
+    minv[0] = T(1);
+  }
+  const int N = a.L[0] > 1 ? a.L[0] : 1;
+  const int64_t total_groups = (int64_t)gridDim.x * GPB;
+  for (int64_t chain = ((int64_t)blockIdx.x * THREADS + threadIdx.x) / LPC; chain < a.n_chains; chain += total_groups) {
+    const int64_t qoff = chain * a.sc;
+    T q[EPL], p[EPL];
+    load_vec<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d, T(1));
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) sQ[s * THREADS] = q[s];
+    int nacc = 0;
+    for (int k = 0; k < K; ++k) {
+      draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d, (uint32_t)k);
+      const T K0 = kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+      T V0, V1;
+      leapfrog<Model, T, EPL, LPC, UNITM>(model, q, p, minv, N, a.eps[0], c, V0, V1);
+      const T H0 = V0 + K0;
+      const T H1 = V1 + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+      // sum(q0 - q1) with diff_sum's partial sums (padded slots hold 0 on both sides)
+      T acc[4] = {T(0), T(0), T(0), T(0)};
+#pragma unroll
+      for (int s0 = 0; s0 < EPL; s0 += 8) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          if (s0 + e < EPL) acc[e & 3] += sQ[(s0 + e) * THREADS] - q[s0 + e];
+      }
+      const T dq = group_sum_masked<LPC, T>((acc[0] + acc[1]) + (acc[2] + acc[3]), c.mask);
+      const T prob = t_exp<T>(H0 - H1);
+      const bool bad = t_bad(prob) || dq == T(0);
+      const double u = draw_uniform<T>(a, chain, 0, (uint32_t)k);
+      const T pm = prob < T(1) ? prob : T(1);
+      const bool accept = !bad && !(u > (double)pm);
+      if (k == K - 1) {
+        if (c.lane == 0) {
+          if (a.code) a.code[chain] = bad ? (a.rule == HMCB_RULE_PYHMC ? 2 : -1) : (accept ? 1 : 0);
+          if (a.energies) { a.energies[2 * chain] = H0; a.energies[2 * chain + 1] = H1; }
+          if (a.accept_prob) a.accept_prob[chain] = (accept && !t_bad(prob)) ? pm : T(0);
+        }
+        if (a.p_out) {
+          if (!accept) draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d, (uint32_t)k);
+          store_vec<T, EPL, LPC>(p, a.p_out, qoff, a.sd, c.lane, d);
+        }
+      }
+      if (accept) {
+        ++nacc;
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) sQ[s * THREADS] = q[s];
+      } else {
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) q[s] = sQ[s * THREADS];
+      }
+    }
+    store_vec<T, EPL, LPC>(q, a.q_out, qoff, a.sd, c.lane, d);
+    if (c.lane == 0) {
+      if (n_accept) n_accept[chain] += nacc;
+      if (a.counts) { a.counts[3 * chain] = 2 * K; a.counts[3 * chain + 1] = K * (N + 1); a.counts[3 * chain + 2] = K; }
     }
   }
 }

@@ -26,7 +26,8 @@ template <class Model, typename T, int EPL, int MODE>
 __global__ void __launch_bounds__(kWsThreads, 1) k_transition_ws(const Model model, const TransArgs<T> a) {
   static_assert(sizeof(T) == 8, "the warp-specialised kernel is float64 only");
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  float* sP = reinterpret_cast<float*>(smem_raw);                              // [2][EPL][256]
+  T* sQ = reinterpret_cast<T*>(smem_raw);                                           // [EPL][256] q0 of the round (optional)
+  float* sP = reinterpret_cast<float*>(sQ + (a.tile_io ? (size_t)EPL * kWsComputeThreads : 0));   // [2][EPL][256]
   uint64_t* full = reinterpret_cast<uint64_t*>(sP + 2 * EPL * kWsComputeThreads);
   uint64_t* empty = full + 2;
   const int tid = threadIdx.x, wg = tid >> 7;
@@ -82,12 +83,18 @@ __global__ void __launch_bounds__(kWsThreads, 1) k_transition_ws(const Model mod
       const int64_t qoff = (live ? chain : 0) * a.sc;
       T q[EPL], p[EPL];
       load_vec<T, EPL, 1>(q, a.q_in, qoff, a.sd, 0, d, T(1));
+      if (a.tile_io) {
+#pragma unroll
+        for (int k = 0; k < EPL; ++k) sQ[k * kWsComputeThreads + tid] = q[k];
+      }
       lr::mbar_wait(full + s, (r >> 1) & 1);
       const float* src = sP + (size_t)s * EPL * kWsComputeThreads + tid;
 #pragma unroll
       for (int k = 0; k < EPL; ++k) p[k] = (T)src[k * kWsComputeThreads];
       lr::mbar_arrive(empty + s);
-      if (live) finish_single<Model, T, EPL, 1, true, MODE>(model, a, c, minv, chain, qoff, q, p);
+      if (live)
+        finish_single<Model, T, EPL, 1, true, MODE>(model, a, c, minv, chain, qoff, q, p, nullptr,
+                                                    a.tile_io ? sQ + tid : nullptr, kWsComputeThreads);
     }
   }
 }

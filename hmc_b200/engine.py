@@ -85,6 +85,7 @@ class Engine:
         self._ws_pool = {}       # drhmc scratch, one per concurrent stream slot
         self._streams = None
         self._host_stage = None  # device staging of drhmc_step_host, kept between calls
+        self._host_out = None    # two alternating sets of pinned result buffers of drhmc_step_host
         self.device = None
 
     # ------------------------------------------------------------------ set-up
@@ -309,16 +310,28 @@ class Engine:
         chunk are half-size: the pipeline fills and drains on small pieces.  Chains are
         independent and draws are keyed by global chain id, so the result is bit-identical to
         the one-shot call.  q_host: CPU tensor [C,d] (pinned for full copy speed); returns
-        pinned CPU tensors.  Device staging for the whole batch is kept between calls."""
+        pinned CPU tensors owned by the engine: two sets, used alternately, so a result stays valid
+        until the call after the next one overwrites it (copy it if you keep it longer).  Device
+        staging for the whole batch is kept between calls."""
         self._ensure()
         C_, d = q_host.shape
         n_chunks = max(1, min(int(n_chunks), (C_ + 4095) // 4096))
-        pin = dict(pin_memory=True)
-        host = {"q": torch.empty((C_, d), dtype=self.dtype, **pin),
-                "p": torch.empty((C_, d), dtype=self.dtype, **pin) if want_p else None,
-                "code": torch.empty(C_, dtype=torch.int32, **pin),
-                "avec": torch.empty((C_, nprops), dtype=self.dtype, **pin),
-                "counts": torch.empty((C_, 3), dtype=torch.int32, **pin)}
+        # results land in one of TWO sets of pinned host buffers the engine keeps (alternating per call, so the previous
+        # call's results stay valid while this one is produced -- e.g. q of call i is the input of call i+1): no pinned
+        # allocation per call
+        hkey = (C_, d, nprops, bool(want_p))
+        if self._host_out is None or self._host_out[0] != hkey:
+            pin = dict(pin_memory=True)
+            self._host_out = (hkey, [{"q": torch.empty((C_, d), dtype=self.dtype, **pin),
+                                      "p": torch.empty((C_, d), dtype=self.dtype, **pin) if want_p else None,
+                                      "code": torch.empty(C_, dtype=torch.int32, **pin),
+                                      "avec": torch.empty((C_, nprops), dtype=self.dtype, **pin),
+                                      "counts": torch.empty((C_, 3), dtype=torch.int32, **pin)} for _ in range(2)], 0)
+        hk, sets, flip = self._host_out
+        if q_host.data_ptr() == sets[flip]["q"].data_ptr():
+            flip ^= 1               # never write the results over the input
+        host = sets[flip]
+        self._host_out = (hk, sets, flip ^ 1)
         cur = torch.cuda.current_stream(self.device)
         with torch.cuda.device(self.device):
             if self._streams is None:
