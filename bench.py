@@ -557,7 +557,11 @@ def secondary_block(a, dev, world, rank, fp64_peak, peaks):
     row("cfg3-light, %d transitions per call (hmcb_drhmc_sample)" % Kf, ms / Kf, total(counts[:, 1].sum(dtype=torch.float64)) / Kf, 7 * d)
     h = pyhmc.HMC(fm, device=dev, seed=1, chain_offset=lo)
     ms, out = timed(lambda: h.engine.hmc_step(q, 20, 0.1, _lib.RULE_PYHMC, want_p=False))
-    row("funnel d=50 HMC L=20 eps=0.1, 2^20 chains", ms, Ct * 21, 7 * d)
+    row("funnel d=50 HMC L=20 eps=0.1, 2^20 chains, one call per transition", ms, Ct * 21, 7 * d)
+    Kh = 16
+    ms, out = timed(lambda: h.engine.hmc_sample(q, 20, 0.1, _lib.RULE_PYHMC, Kh))
+    row("funnel d=50 HMC L=20 eps=0.1, 2^20 chains, %d transitions per launch (hmcb_hmc_sample, k_hmc_multi_ws)" % Kh, ms / Kh,
+        Ct * 21, 7 * d)
     del q, counts
 
     # config 4: Bayesian logistic regression N=100,000 D=128, 16,384 chains, HMC L=10 (tcgen05 gradient GEMMs)
@@ -588,7 +592,9 @@ def secondary_block(a, dev, world, rank, fp64_peak, peaks):
     fpg = 8.5 * d
     hh = algorithms.HMC(rm, device=dev, seed=4, chain_offset=lo)
     ms, out = timed(lambda: hh.engine.hmc_step(q, 20, 0.02, _lib.RULE_ALG, want_p=False))
-    row("cfg5 Rosenbrock d=100 HMC L=20 eps=0.02, 131,072 chains", ms, Ct * 21, fpg)
+    row("cfg5 Rosenbrock d=100 HMC L=20 eps=0.02, 131,072 chains, one call per transition", ms, Ct * 21, fpg)
+    ms, out = timed(lambda: hh.engine.hmc_sample(q, 20, 0.02, _lib.RULE_ALG, 16))
+    row("cfg5 Rosenbrock d=100 HMC L=20, 16 transitions per launch (hmcb_hmc_sample, k_hmc_multi)", ms / 16, Ct * 21, fpg)
     mm = mala.MALA(rm, device=dev, seed=4, chain_offset=lo)
     ms, out = timed(lambda: mm.engine.mala_step(q, 0.02, n_steps=32))
     row("cfg5 Rosenbrock d=100 MALA eps=0.02, 32 steps per launch", ms / 32, Ct * 33 / 32.0, fpg,

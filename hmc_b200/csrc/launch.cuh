@@ -187,7 +187,11 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
         // (funnel d=50, 2^20 chains: HMC L=20 0.748 -> 0.614 ms, L=150 2.055 -> 2.002 ms, DR stage 0 1.975 -> 1.948 ms)
         const size_t q0s_bytes = (size_t)EPL * kWsComputeThreads * sizeof(T);
         const size_t base_smem = 2 * (size_t)EPL * kWsComputeThreads * sizeof(float) + 64;
-        a.tile_io = (base_smem + q0s_bytes <= (size_t)max_optin_smem() && !(getenv("HMCB_WS_Q0S") && !atoi(getenv("HMCB_WS_Q0S")))) ? 1 : 0;
+        // vanilla HMC only: in DR stage 0 the rejected chains are not copied through, and what the no-move test saves
+        // is less than what the smaller L1 (204 KB of shared memory per SM) costs the strided row accesses
+        // (DRHMC nleap=20: 0.787 -> 0.815 ms with the copy)
+        a.tile_io = (op == OP_HMC && base_smem + q0s_bytes <= (size_t)max_optin_smem() &&
+                     !(getenv("HMCB_WS_Q0S") && !atoi(getenv("HMCB_WS_Q0S")))) ? 1 : 0;
         const size_t ws_smem = base_smem + (a.tile_io ? q0s_bytes : 0);
         const int grid = (int)((a.n_chains + kWsComputeThreads - 1) / kWsComputeThreads < sm_count()
                                    ? (a.n_chains + kWsComputeThreads - 1) / kWsComputeThreads
