@@ -597,9 +597,25 @@ def secondary_block(a, dev, world, rank, fp64_peak, peaks):
     row("cfg5 Rosenbrock d=100 HMC L=20, 16 transitions per launch (hmcb_hmc_sample, k_hmc_multi)", ms / 16, Ct * 21, fpg)
     mm = mala.MALA(rm, device=dev, seed=4, chain_offset=lo)
     ms, out = timed(lambda: mm.engine.mala_step(q, 0.02, n_steps=32))
+    # the generator alone (Philox4x32-10 + f32 Box-Muller, 4 blocks in flight per thread, nothing else): MALA's other ceiling
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    sink = torch.empty(sms * 8 * 256, dtype=torch.float64, device=dev)
+    cnt = _lib.C.c_double(0)
+    gen_best = 0.0
+    for it in range(3):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _lib.check(mm.engine.lib.hmcb_probe_normals(0, sms * 8, 256, 400, _lib.ptr(sink), _lib.C.byref(cnt), mm.engine._stream()))
+        e1.record()
+        torch.cuda.synchronize()
+        if it:
+            gen_best = max(gen_best, cnt.value / (e0.elapsed_time(e1) * 1e-3))
+    nps = Ct * 32 * d / (ms * 1e-3)
     row("cfg5 Rosenbrock d=100 MALA eps=0.02, 32 steps per launch", ms / 32, Ct * 33 / 32.0, fpg,
-        extra={"normals_per_s": Ct * 32 * d / (ms * 1e-3), "note": "one gradient per d normals: bound by Philox + Box-Muller issue, "
-               "not by the FP64 pipe (see profiles/ for the generator-only ceiling)"})
+        extra={"normals_per_s": nps, "generator_only_normals_per_s_per_gpu": gen_best,
+               "frac_of_generator_ceiling": nps / (gen_best * world) if gen_best else None,
+               "note": "one gradient per d normals: the step is bound by Philox + Box-Muller issue (integer multiplies, MUFU), not "
+                       "by the FP64 pipe; hmcb_probe_normals measures that generator running alone"})
     ad = adaptivehmc.AdHMC_eps0(rm, device=dev, seed=4, chain_offset=lo)
     steps = ad.get_steps(0.01, 1.0, 10)
     ms, out = timed(lambda: ad.engine.adhmc_eps0_step(q, 20, steps, 1))

@@ -390,6 +390,13 @@ double hmcb_u53(uint32_t a, uint32_t b);
 int hmcb_probe_fma(int32_t dtype, int32_t blocks, int32_t threads, int64_t iters, void* sink,
                    double* fma_count, void* stream);
 
+/* Measurement probe: standard normals per second from the library's generator alone (Philox4x32-10 +
+ * Box-Muller, 4 independent blocks in flight per thread as the kernels run it; f64_generator != 0 selects the
+ * HMCB_RNG_NORMAL_F64 form).  The ceiling MALA (d normals per gradient) and short-trajectory HMC are quoted
+ * against.  sink: >= blocks*threads doubles.  The normals generated are returned through *normal_count. */
+int hmcb_probe_normals(int32_t f64_generator, int32_t blocks, int32_t threads, int64_t iters, void* sink,
+                       double* normal_count, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
