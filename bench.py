@@ -860,6 +860,9 @@ def cpu_config1():
 
 def main():
     a = parse()
+    if os.environ.get("HMCB_BENCH_WATCHDOG"):   # debugging aid: dump every thread's stack and exit after that many seconds
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["HMCB_BENCH_WATCHDOG"]), exit=True)
     # stdout carries exactly ONE line, the JSON: everything else any library prints there (NCCL's version banner ...)
     # goes to stderr.  File descriptor 1 is pointed at stderr for the run; the JSON goes to the saved descriptor.
     sys.stdout.flush()

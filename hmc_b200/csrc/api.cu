@@ -220,9 +220,10 @@ static int dr_uniforms(int nprops, int conv) { return conv >= HMCB_DR_PROB_METRO
 template <typename T>
 static int drhmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r, int n_leap,
                         double eps, int nprops, double stepfactor, int conv, const hmcb_step_out* o, void* ws,
-                        const DrLayout& L, const hmcb_profile* prof, cudaStream_t st) {
+                        const DrLayout& L, const hmcb_profile* prof, cudaStream_t st, bool prefer_plain = false) {
   TransArgs<T> a;
   fill_args(a, m, c, r, o);
+  a.prefer_plain = prefer_plain ? 1 : 0;
   a.nprops = nprops;
   a.dr_conv = conv != HMCB_DR_ALGORITHMS;   // the probabilistic classes keep PyHMC_multistep's conventions
   a.dr_prob = conv == HMCB_DR_PROB_METROP ? 1 : (conv == HMCB_DR_PROB_HASTINGS ? 2 : 0);
@@ -354,7 +355,7 @@ static int adwalk_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains*
 // global chain id).  The helper streams belong to the library (created once per device, outside
 // any stream capture); they fork from and join back into the caller's stream through events, so
 // from the caller's side all work is still ordered on the stream it passed.
-constexpr int kMaxSplit = 8;
+constexpr int kMaxSplit = 16;
 
 static int dr_split_for(int64_t n_chains, const hmcb_profile* prof) {
   if (prof) return 1;                       // per-stage events want the stages one after another
@@ -796,10 +797,13 @@ int hmcb_drhmc_sample(const hmcb_model* model, const hmcb_chains* chains, const 
       if (K > 1 && counts_tot) os.counts = counts_k;
       cudaStream_t on = i == 0 ? st : h->s[i - 1];
       void* ws = (char*)workspace + (offc[i] - L[i].total);
+      const bool plain = S >= 3;   // see launch.cuh: with several ranges in flight the plain stage-0 kernel packs better
       if (model->dtype == HMCB_F64)
-        rc = drhmc_step_t<double>(e, model, &cs, &rs, n_leap, step_size, nprops, stepfactor, convention, &os, ws, L[i], nullptr, on);
+        rc = drhmc_step_t<double>(e, model, &cs, &rs, n_leap, step_size, nprops, stepfactor, convention, &os, ws, L[i], nullptr, on,
+                                  plain);
       else
-        rc = drhmc_step_t<float>(e, model, &cs, &rs, n_leap, step_size, nprops, stepfactor, convention, &os, ws, L[i], nullptr, on);
+        rc = drhmc_step_t<float>(e, model, &cs, &rs, n_leap, step_size, nprops, stepfactor, convention, &os, ws, L[i], nullptr, on,
+                                 plain);
       if (rc) break;
       void* msum = io->moment_sum ? (char*)io->moment_sum + (size_t)lo * model->d * ts : nullptr;
       void* msq = io->moment_sumsq ? (char*)io->moment_sumsq + (size_t)lo * model->d * ts : nullptr;

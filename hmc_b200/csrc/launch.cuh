@@ -181,7 +181,10 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
       // 1.25 ms against 1.40 ms here, the strided p_prev / p_out rows being what costs)
       // (nor with the exact f64 normal generator: the helper warpgroup draws with normal4_f32 only, and every
       // other place that re-draws p0 -- the DR stages >= 1, p_out of rejected chains -- would use the f64 one)
-      if (!a.p_inject && !a.p_prev && !(a.rng_flags & HMCB_RNG_NORMAL_F64) && a.n_chains >= 4096) {
+      // (nor inside hmcb_drhmc_sample, prefer_plain: a warp-specialised block owns a whole SM's registers and cannot share
+      // an SM with the 2-per-SM blocks of another range's later stages -- with 4 ranges pipelined the plain kernel's
+      // packing wins: 5.34 -> 5.12 ms per transition at 2^20 chains although stage 0 alone is 8 % slower)
+      if (!a.p_inject && !a.p_prev && !a.prefer_plain && !(a.rng_flags & HMCB_RNG_NORMAL_F64) && a.n_chains >= 4096) {
         // (the per-warp staging tile of the plain kernel does not pay here: L=150 2.02 -> 2.18 ms.)  tile_io instead
         // selects a shared-memory copy of q0 for the no-move test and the copy-through of rejected chains
         // (funnel d=50, 2^20 chains: HMC L=20 0.748 -> 0.614 ms, L=150 2.055 -> 2.002 ms, DR stage 0 1.975 -> 1.948 ms)

@@ -62,6 +62,7 @@ struct TransArgs {
   T* p0_out;         // starting momentum of every chain (layout of q) or nullptr
   int32_t nprops, stage;
   int32_t tile_io;   // set by the launcher when the per-warp staging tile was allocated (see warp_tile_load)
+  int32_t prefer_plain;  // caller's wish: k_transition rather than the warp-specialised kernel (pipelined sample calls)
   int32_t L[kMaxProps];
   T eps[kMaxProps];
   DrScratch<T> ws;

@@ -184,7 +184,7 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
  * accepted at any stage (needs out->code).  Injected draws and p_prev need n_transitions == 1.
  * Workspace: hmcb_drhmc_sample_workspace_bytes().  Make the first call per device outside stream
  * capture (helper streams are created then); HMCB_SAMPLE_SPLIT=n in the environment sets the
- * number of ranges (1..8). */
+ * number of ranges (1..16). */
 typedef struct hmcb_sample_io {
   int32_t n_transitions;      /* K >= 1 */
   void* moment_sum;           /* [C,d] or NULL (both or neither) */
