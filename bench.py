@@ -776,6 +776,8 @@ def run_hmcb(a):
     if not a.no_cpu_baseline and world == 1:
         cpu = cpu_baseline(a, a.cpu_seconds)
         cfg1 = cpu_config1()
+    split_on = os.environ.get("HMCB_DR_STAGE_SPLIT", "1") != "0" and a.nprops >= 3 and a.nleap >= 48
+    n_stage_kernels = a.nprops + (a.nprops - 2 if split_on else 0)
     line = {"metric": "grad_evals_per_sec", "value": value, "unit": "grad_evals/s", "n_gpus": world, "steps": K,
             "warmup": a.warmup, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": a.scaling,
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -797,9 +799,10 @@ def run_hmcb(a):
             "ess_per_sec": (stationary or {}).get("ess_true_min_per_sec"),
             "gates": gates, "strong": strong, "secondary": secondary,
             "roofline": roofline, "cpu_baseline": cpu, "config1_cpu": cfg1, "e2e": e2e, "clocks": clocks_summary,
-            "gpu_launches": K * H["n_split"] * (a.nprops + 1),
-            "gpu_launches_note": "timed region: %d transitions x %d chain ranges x (%d DR stage kernels + 1 counters/moments "
-                                 "kernel), all libhmcb.so" % (K, H["n_split"], a.nprops)}
+            "gpu_launches": K * H["n_split"] * (n_stage_kernels + 1),
+            "gpu_launches_note": "timed region: %d transitions x %d chain ranges x (%d DR stage kernels%s + 1 counters/moments "
+                                 "kernel), all libhmcb.so" % (K, H["n_split"], n_stage_kernels,
+                                                              ", stages >= 2 in two kernels each" if split_on else "")}
     print(json.dumps(line), flush=True)
 
 

@@ -185,11 +185,22 @@ static int hmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c,
 struct DrLayout {
   size_t off_count, off_list, off_H0, off_avec, off_counts, off_ptries, off_frames, total;
   int64_t frame_threads;
+  // continuation buffers of the split stages (ccap == 0: stages run unsplit)
+  size_t off_ccount, off_clist, off_csti, off_cstf, off_cframes;
+  int64_t ccap;
 };
+
+// Stages >= 2 in two kernels (transition.cuh, dr_phase): the second one takes the chains whose ghost recursion goes on
+// after its first trajectory.  Its list holds a quarter of the batch (all of a small one); chains beyond that finish
+// in the first kernel as before.
+static bool dr_split_stages() {
+  const char* e = getenv("HMCB_DR_STAGE_SPLIT");
+  return !(e && atoi(e) == 0);
+}
 
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-static int dr_layout(const Entry* e, const hmcb_model* m, int64_t n_chains, int nprops, DrLayout& L) {
+static int dr_layout(const Entry* e, const hmcb_model* m, int64_t n_chains, int nprops, DrLayout& L, bool with_cont = true) {
   LaunchInfo li;
   int rc = e->fn(*m, OP_QUERY, &li, nullptr);
   if (rc) return rc;
@@ -209,6 +220,15 @@ static int dr_layout(const Entry* e, const hmcb_model* m, int64_t n_chains, int 
   L.off_frames = off;
   const int nframes = nprops > 1 ? nprops - 1 : 0;
   off = align_up(off + (size_t)nframes * 2 * li.epl * L.frame_threads * ts, 256);
+  L.ccap = 0;
+  if (with_cont && nprops >= 3 && dr_split_stages()) {
+    L.ccap = n_chains <= 65536 ? n_chains : n_chains / 4;
+    L.off_ccount = off;  off = align_up(off + 64, 256);
+    L.off_clist = off;   off = align_up(off + (size_t)L.ccap * sizeof(int32_t), 256);
+    L.off_csti = off;    off = align_up(off + (size_t)3 * L.ccap * sizeof(int32_t), 256);
+    L.off_cstf = off;    off = align_up(off + (size_t)5 * L.ccap * ts, 256);
+    L.off_cframes = off; off = align_up(off + (size_t)2 * li.epl * li.lpc * L.ccap * ts, 256);
+  }
   L.total = off;
   return 0;
 }
@@ -248,9 +268,28 @@ static int drhmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* 
   if (prof && prof->events[0]) HMCB_CUDA(cudaEventRecord((cudaEvent_t)prof->events[0], st));
   int rc = e->fn(*m, OP_DR0, &a, st);
   if (prof && prof->events[1] && rc == 0) HMCB_CUDA(cudaEventRecord((cudaEvent_t)prof->events[1], st));
+  if (L.ccap > 0) {
+    a.ws.ccount = (int32_t*)(w + L.off_ccount);
+    a.ws.clist = (int32_t*)(w + L.off_clist);
+    a.ws.cst_i = (int32_t*)(w + L.off_csti);
+    a.ws.cst_f = (T*)(w + L.off_cstf);
+    a.ws.cframes = (T*)(w + L.off_cframes);
+    a.ws.ccap = (int32_t)L.ccap;
+  }
   for (int j = 1; j < nprops && rc == 0; ++j) {
     a.stage = j;
-    rc = e->fn(*m, OP_DRN, &a, st);
+    // (at short trajectories the second launch and the parking cost more than the idle lanes: DRHMC nleap=20 0.79 -> 0.82 ms)
+    if (j >= 2 && L.ccap > 0 && n_leap >= 48) {
+      // two kernels: up to the point where the chains of a warp part ways, then those whose ghost recursion goes on
+      HMCB_CUDA(cudaMemsetAsync(a.ws.ccount, 0, sizeof(int32_t), st));
+      a.dr_phase = 1;
+      rc = e->fn(*m, OP_DRN, &a, st);
+      a.dr_phase = 2;
+      if (rc == 0) rc = e->fn(*m, OP_DRN, &a, st);
+      a.dr_phase = 0;
+    } else {
+      rc = e->fn(*m, OP_DRN, &a, st);
+    }
     if (prof && prof->events[j + 1] && rc == 0) HMCB_CUDA(cudaEventRecord((cudaEvent_t)prof->events[j + 1], st));
   }
   return rc;
@@ -838,7 +877,7 @@ int hmcb_drhmc_step_static(const hmcb_model* model, const hmcb_chains* chains, c
   const Entry* e = choose_entry(*model);
   if (!e) return HMCB_E_UNSUPPORTED;
   DrLayout L;
-  if ((rc = dr_layout(e, model, chains->n_chains, nprops, L))) return rc;
+  if ((rc = dr_layout(e, model, chains->n_chains, nprops, L, false))) return rc;   // unsplit stages: the scratch it was sized for
   if (L.total > (size_t)HMCB_STATIC_SCRATCH_BYTES) {
     set_error("built-in scratch too small: n_chains=%lld, d=%d, nprops=%d needs %zu bytes, the library holds %u "
               "(HMCB_STATIC_SCRATCH_BYTES); split the batch or call hmcb_drhmc_step with your own workspace",

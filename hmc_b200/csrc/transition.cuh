@@ -31,6 +31,13 @@ struct DrScratch {
   int32_t* counts;   // [n_chains*3] running Hcount, Vgcount, leapcount
   T* frames;         // [(kMaxProps-1)*2*EPL*frame_threads] per-thread proposal frames
   int64_t frame_threads;
+  // continuation of a stage >= 2 (dr_phase): chains whose ghost recursion goes on after its first trajectory
+  int32_t* ccount;   // [1] chains parked by the first part of the running stage
+  int32_t* clist;    // [ccap] their chain ids
+  int32_t* cst_i;    // [3][ccap] Hcount, Vgcount, leapcount so far
+  T* cst_f;          // [5][ccap] lHb[1], lpf[0], lav[1][0], lpt[0][J], lpt[1][0]
+  T* cframes;        // [2*EPL][ccap] the stage's proposal (q, p), element s of slot k at s*ccap + k
+  int32_t ccap;
 };
 
 template <typename T>
@@ -62,6 +69,8 @@ struct TransArgs {
   T* p0_out;         // starting momentum of every chain (layout of q) or nullptr
   int32_t nprops, stage;
   int32_t tile_io;   // set by the launcher when the per-warp staging tile was allocated (see warp_tile_load)
+  int32_t dr_phase;  // MODE_DRN: 0 the whole stage in one kernel; 1 up to the first point where the chains of a warp part
+                     // ways (after the first ghost trajectory), parking those that go on; 2 the parked chains
   int32_t prefer_plain;  // caller's wish: k_transition rather than the warp-specialised kernel (pipelined sample calls)
   int32_t L[kMaxProps];
   T eps[kMaxProps];
@@ -437,8 +446,9 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
 
   const int64_t gthread = (int64_t)blockIdx.x * THREADS + threadIdx.x;
   const int64_t total_groups = (int64_t)gridDim.x * GPB;
-  const int64_t count = (MODE == MODE_DRN) ? (int64_t)a.ws.count[a.stage] : a.n_chains;
-  const int32_t* list = (MODE == MODE_DRN) ? a.ws.list + (int64_t)a.stage * a.n_chains : nullptr;
+  const bool resume = (MODE == MODE_DRN) && a.dr_phase == 2;
+  const int64_t count = (MODE == MODE_DRN) ? (int64_t)(resume ? min(a.ws.ccount[0], a.ws.ccap) : a.ws.count[a.stage]) : a.n_chains;
+  const int32_t* list = (MODE == MODE_DRN) ? (resume ? a.ws.clist : a.ws.list + (int64_t)a.stage * a.n_chains) : nullptr;
   const int J = (MODE == MODE_DRN) ? a.stage : 0;
 
   if constexpr (MODE != MODE_DRN && !Model::kNeedsSmem) {
@@ -497,7 +507,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
         lpt[0][i] = (prob_rule && i < J) ? a.ws.ptries[chain * kMaxProps + i] : T(1);
       }
       cH = a.ws.counts[3 * chain]; cVg = a.ws.counts[3 * chain + 1]; cLeap = a.ws.counts[3 * chain + 2];
-      if (prob_rule) {
+      if (prob_rule && !resume) {
         // one more uniform decides whether stage J is attempted at all (src/algorithms.py:710-711): code -2 if not
         const double u_try = draw_uniform<T>(a, chain, 2 * J - 1);
         if (u_try > (double)lpt[0][J - 1]) {
@@ -526,11 +536,32 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
       const int64_t FT = a.ws.frame_threads;
       T* fr = a.ws.frames + gthread;  // frame f: q at (2f)*EPL*FT, p at (2f+1)*EPL*FT, slot stride FT
       T prob_top = T(0);
+      bool have_qp = false, parked = false;
+      if (resume) {
+        // a chain parked by the first part of this stage: its walk stands in the ghost frame of the stage's proposal
+        // (level 1), first ghost trajectory done, the next one (class 1) due; the proposal goes into this thread's frame 0
+        const int64_t cc = a.ws.ccap, k = item;
+        lvl = 1;
+        lm[1] = J; lj[1] = 1;
+        cH = a.ws.cst_i[k]; cVg = a.ws.cst_i[cc + k]; cLeap = a.ws.cst_i[2 * cc + k];
+        lHb[1] = a.ws.cst_f[k]; lpf[0] = a.ws.cst_f[cc + k];
+#pragma unroll
+        for (int i = 0; i < kMaxProps; ++i) { lav[1][i] = T(0); lpt[1][i] = T(1); }
+        lav[1][0] = a.ws.cst_f[2 * cc + k];
+        if (prob_rule) { lpt[0][J] = a.ws.cst_f[3 * cc + k]; lpt[1][0] = a.ws.cst_f[4 * cc + k]; }
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) { q[s] = a.ws.cframes[(int64_t)s * cc * LPC + k * LPC + c.lane]; p[s] = a.ws.cframes[(int64_t)(EPL + s) * cc * LPC + k * LPC + c.lane]; }
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) { fr[(int64_t)s * FT] = q[s]; fr[(int64_t)(EPL + s) * FT] = p[s]; p[s] = -p[s]; }
+        have_qp = true;
+      }
 
       for (;;) {
         const int j = lj[lvl];
         const int N = a.L[j] > 1 ? a.L[j] : 1;
-        if (lvl == 0) {
+        if (have_qp) {
+          have_qp = false;      // (q, -p) of the proposal are in registers already
+        } else if (lvl == 0) {
           load_vec<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d, T(1));
           draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);
         } else {
@@ -612,7 +643,35 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
           if (lvl == 0) { prob_top = prob; done = true; break; }
         }
         if (done) break;
+        if (a.dr_phase == 1 && lvl == 1 && lj[1] == 1) {
+          // first point where the chains of a warp part ways: some returned to level 0 above (the first ghost stage accepts
+          // for sure, or J == 1), this one's ghost recursion goes on.  Park it for the stage's second kernel, where only such
+          // chains meet, instead of holding the lanes of those that are done (stage 2 of the d=50 funnel ran 26.9 of 32 lanes).
+          int slot = 0;
+          if (c.lane == 0) slot = atomicAdd(a.ws.ccount, 1);
+          slot = __shfl_sync(c.mask, slot, ((threadIdx.x & 31) / LPC) * LPC);
+          if (slot < a.ws.ccap) {
+            const int64_t cc = a.ws.ccap;
+            if (c.lane == 0) {
+              a.ws.clist[slot] = (int32_t)chain;
+              a.ws.cst_i[slot] = cH; a.ws.cst_i[cc + slot] = cVg; a.ws.cst_i[2 * cc + slot] = cLeap;
+              a.ws.cst_f[slot] = lHb[1]; a.ws.cst_f[cc + slot] = lpf[0]; a.ws.cst_f[2 * cc + slot] = lav[1][0];
+              if (prob_rule) { a.ws.cst_f[3 * cc + slot] = lpt[0][J]; a.ws.cst_f[4 * cc + slot] = lpt[1][0]; }
+            }
+#pragma unroll
+            for (int s = 0; s < EPL; ++s) { q[s] = fr[(int64_t)s * FT]; p[s] = fr[(int64_t)(EPL + s) * FT]; }
+#pragma unroll
+            for (int s = 0; s < EPL; ++s) {
+              a.ws.cframes[(int64_t)s * cc * LPC + (int64_t)slot * LPC + c.lane] = q[s];
+              a.ws.cframes[(int64_t)(EPL + s) * cc * LPC + (int64_t)slot * LPC + c.lane] = p[s];
+            }
+            parked = true;
+            break;
+          }
+          // the list is full: this chain finishes its stage here, as without the split
+        }
       }
+      if (parked) continue;
 
       // ---------------- DRHMC.step's accept test for stage J (src/algorithms.py:523-529)
       if (t_bad(prob_top)) prob_top = T(0);
