@@ -143,6 +143,21 @@ class HMC(_PyHMCBase):
         logp, g1 = e.logp_grad(q1)
         return bq.out(q1), bq.out(p1), bq.out(-logp), bq.out(-g1)
 
+    def _sample_fused(self, b, state, run):
+        """store=False form of sample(): burn-in and sampling as one fused call each."""
+        qd = b.q
+        if self.burnin > 0:
+            qd = run(qd, self.burnin)["q"]
+        C_, d = qd.shape
+        msum, msq = torch.zeros_like(qd), torch.zeros_like(qd)
+        nacc = torch.zeros(C_, dtype=torch.int32, device=qd.device)
+        out = run(qd, self.nsamples, msum=msum, msumsq=msq, n_accept=nacc)
+        state.i = self.nsamples + self.burnin
+        state.q, state.n_accept, state.counts = b.out(out["q"]), b.out(nacc), b.out(out["counts"])
+        state.moment_sum, state.moment_sumsq = b.out(msum), b.out(msq)
+        state.samples = state.accepts = state.Hs = None
+        return state
+
     def _parse_kwargs_sample(self, **kwargs):
         self.nsamples = kwargs["nsamples"]
         self.burnin = kwargs["burnin"]
@@ -183,12 +198,18 @@ class HMC(_PyHMCBase):
                 self.step_size = step_size
         return b.out(qd)
 
-    def sample(self, q, p=None, callback=None, skipburn=True, epsadapt=0, draws=None, **kwargs):
+    def sample(self, q, p=None, callback=None, skipburn=True, epsadapt=0, draws=None, store=True, **kwargs):
         """src/algorithms.py:233-254.  ``accepts`` is kept for every iteration, samples /
         Hs / counts only for i > burnin (strict, as the reference): nsamples-1 rows.
         ``p`` is accepted and ignored, as in the reference.  draws=(P, U), P [T, C, d] and
         U [T, C, 1] with T = (epsadapt+1 if epsadapt else 0) + nsamples + burnin, replays the
-        draws in the order the reference would consume them (parity runs)."""
+        draws in the order the reference would consume them (parity runs).
+
+        store=False (not in the reference; for batches whose history does not fit): the same
+        transitions through ONE hmcb_hmc_sample call per phase (burn-in, then sampling) with the
+        chain state on the device; the Sampler then carries, instead of per-iteration lists,
+        ``q`` (final state), ``n_accept`` [C] and ``counts`` [C,3] over the nsamples kept
+        transitions, and the running moments ``moment_sum`` / ``moment_sumsq`` [C,d] of those."""
         self._parse_kwargs_sample(**kwargs)
         state = Sampler()
         P, U = (None, None) if draws is None else draws
@@ -199,6 +220,11 @@ class HMC(_PyHMCBase):
                                     **kwargs)
         b = self._device_q(q)
         qd = b.q
+        if not store:
+            if draws is not None:
+                raise ValueError("replayed draws need store=True (one transition per call)")
+            return self._sample_fused(b, state, lambda qq, n, **kw: self.engine.hmc_sample(
+                qq, self.nleap, self.step_size, self._rule, n, **kw))
         for i in range(self.nsamples + self.burnin):
             out = self.engine.hmc_step(qd, self.nleap, self.step_size, self._rule, want_p=False,
                                        p=None if P is None else P[t0 + i], u=None if U is None else U[t0 + i])
@@ -244,15 +270,22 @@ class DRHMC(HMC):
         self.Hcount, self.Vgcount, self.leapcount = out["counts"][:, 0], out["counts"][:, 1], out["counts"][:, 2]
         return b.out(out["q"]), b.out(out["p"]), b.out(out["code"]), b.out(out["avec"]), b.out(out["counts"])
 
-    def sample(self, q, p=None, callback=None, draws=None, **kwargs):
+    def sample(self, q, p=None, callback=None, draws=None, store=True, **kwargs):
         """src/algorithms.py:534-555: every iteration (burn-in included) is stored.  (The reference draws
         one unused normal vector when ``p`` is None, :538; nothing is drawn for it here.)  draws=(P, U),
-        P [T, C, d] and U [T, C, nprops] with T = nsamples + burnin, replays the draws (parity runs)."""
+        P [T, C, d] and U [T, C, nprops] with T = nsamples + burnin, replays the draws (parity runs).
+        store=False: as HMC.sample(store=False), through hmcb_drhmc_sample (burn-in, then nsamples
+        transitions with running moments); the kept statistics cover the nsamples transitions."""
         self._parse_kwargs_sample(**kwargs)
         state = Sampler()
         state.avecs = []
         b = self._device_q(q)
         qd = b.q
+        if not store:
+            if draws is not None:
+                raise ValueError("replayed draws need store=True (one transition per call)")
+            return self._sample_fused(b, state, lambda qq, n, **kw: self.engine.drhmc_sample(
+                qq, self.nleap, self.step_size, kwargs["nprops"], kwargs["stepfactor"], n, want_avec=False, **kw))
         P, U = (None, None) if draws is None else draws
         for i in range(self.nsamples + self.burnin):
             out = self.engine.drhmc_step(qd, self.nleap, self.step_size, kwargs["nprops"], kwargs["stepfactor"],

@@ -118,3 +118,41 @@ def test_adapt_stepsize_many_chains_uses_the_mean_statistic():
         noisy, avg = da.update(float(np.mean(probs)))
         eps = noisy if i < K else avg
     assert np.isclose(s.step_size, eps, rtol=1e-8)
+
+
+@pytest.mark.parametrize("cls,extra", [(algorithms.HMC, {}), (algorithms.DRHMC, dict(nprops=3, stepfactor=2.0))])
+def test_sample_without_history_equals_the_stored_run(cls, extra):
+    """sample(store=False): one fused call per phase -- the final state, accept counts, work counters and running moments
+    are those of the stored run over its nsamples kept transitions (both start from the same seed)."""
+    d, C, ns, nb = 50, 4500, 6, 3
+    q0 = np.random.default_rng(14).uniform(-1, 1, (C, d))
+    kw = dict(nsamples=ns, burnin=nb, step_size=0.25, nleap=8, **extra)
+    a = cls(models.Funnel(d), device=_dev(), seed=77)
+    b = cls(models.Funnel(d), device=_dev(), seed=77)
+    if cls is algorithms.HMC:
+        # the stored run: burn-in + sampling as single steps, everything kept here for the comparison
+        qs, codes, q = [], [], torch.as_tensor(q0, device=_dev())
+        for t in range(ns + nb):
+            o = a.engine.hmc_step(q, 8, 0.25, a._rule, want_p=False)
+            q = o["q"]
+            qs.append(q)
+            codes.append(o["code"])
+        kept, acc = torch.stack(qs[nb:]), torch.stack(codes[nb:]) == 1
+        counts = torch.tensor([2 * ns, ns * 9, ns], device=_dev(), dtype=torch.int32).expand(C, 3)
+    else:
+        st = a.sample(q0, **kw)
+        kept = torch.as_tensor(st.samples[nb:], device=_dev())
+        acc = torch.as_tensor(st.accepts[nb:], device=_dev()) >= 1
+        counts = torch.as_tensor(st.counts[nb:], device=_dev()).sum(dim=0).int()
+    f = b.sample(q0, store=False, **kw)
+    assert f.samples is None and f.i == ns + nb
+    assert np.array_equal(f.q, kept[-1].cpu().numpy())
+    assert np.array_equal(f.n_accept, acc.sum(dim=0).cpu().numpy())
+    assert np.array_equal(f.counts, counts.cpu().numpy())
+    s1 = torch.zeros((C, d), dtype=torch.float64, device=_dev())
+    s2 = torch.zeros_like(s1)
+    for t in range(ns):
+        s1 += kept[t]
+        s2 = torch.addcmul(s2, kept[t], kept[t])
+    assert np.allclose(f.moment_sum, s1.cpu().numpy(), rtol=1e-13, atol=1e-12)
+    assert np.allclose(f.moment_sumsq, s2.cpu().numpy(), rtol=1e-13, atol=1e-12)
