@@ -334,25 +334,48 @@ def dr_block(a, dev, world, lo, C, q0, seed, K, warmup, burnin, want_stage_times
                        "what": "one hmcb_drhmc_step call (2 chain ranges on 2 streams) + one hmcb_moments_accumulate per transition"}
 
     if want_stage_times:
-        KR = min(K, 6)
+        # Per-stage kernel times (CUDA events recorded inside hmcb_drhmc_step between the stage launches, stages serialised
+        # on one stream), twice: with the plain stage-0 kernel -- the one the timed region launches -- and with the
+        # warp-specialised one that single hmcb_drhmc_step calls use.  Gradient work per stage from the pass's own outputs.
+        KR = min(K, 4)
         evs = [[torch.cuda.Event(enable_timing=True) for _ in range(a.nprops + 1)] for _ in range(KR)]
         for row in evs:
             for ev in row:
                 ev.record()
-        qi, qo = q, nxt
-        for k in range(KR):
-            eng.drhmc_step(qi, a.nleap, a.step_size, a.nprops, a.stepfactor, want_p=False, q_out=qo, stage_events=evs[k],
-                           want_avec=False, code_out=code, counts_out=cl[0])
-            qi, qo = qo, qi
+        codes = torch.zeros((KR, C), dtype=torch.int32, device=dev)
+        passes = {}
+        for name, env in (("plain", "1"), ("ws", None)):
+            if env is None:
+                os.environ.pop("HMCB_NO_WS", None)
+            else:
+                os.environ["HMCB_NO_WS"] = env
+            qi, qo = q.clone(), nxt
+            for k in range(KR):
+                eng.drhmc_step(qi, a.nleap, a.step_size, a.nprops, a.stepfactor, want_p=False, q_out=qo, stage_events=evs[k],
+                               want_avec=False, code_out=codes[k], counts_out=cl[k])
+                qi, qo = qo, qi
+            torch.cuda.synchronize()
+            st = torch.tensor([[evs[k][j].elapsed_time(evs[k][j + 1]) for j in range(a.nprops)] for k in range(KR)],
+                              dtype=torch.float64).mean(dim=0)
+            # chains entering stage j: those not accepted before it (code j' + 1 = accepted at stage j', 0 = never)
+            tot = float(cl[:KR, :, 1].sum(dtype=torch.float64)) / KR
+            g = [C * (max(a.nleap, 1) + 1.0)]
+            if a.nprops >= 2:
+                n1 = float((codes != 1).sum()) / KR
+                L1 = int(a.nleap * a.stepfactor)
+                g1 = n1 * ((max(L1, 1) + 1) + (max(a.nleap, 1) + 1)) if a.nprops >= 2 else 0.0
+                g.append(g1)
+                if a.nprops >= 3:
+                    g.append(tot - g[0] - g1)          # everything deeper (stages >= 2 together when nprops > 3)
+            passes[name] = {"stage_ms": st.tolist(), "stage_grad_evals": g}
+        os.environ.pop("HMCB_NO_WS", None)
         mev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
         mev[0].record()
         for _ in range(4):
             eng.moments_accumulate(q, s1, s2)
         mev[1].record()
         torch.cuda.synchronize()
-        st = torch.tensor([[evs[k][j].elapsed_time(evs[k][j + 1]) for j in range(a.nprops)] for k in range(KR)],
-                          dtype=torch.float64).mean(dim=0)
-        res["stage_ms"] = st.tolist()
+        res["passes"] = passes
         res["moments_ms"] = mev[0].elapsed_time(mev[1]) / 4
         res["stage_passes"] = KR
     return res
@@ -679,25 +702,42 @@ def run_hmcb(a):
     rhat = mom.rhat()
     mean, std = mom.mean_std()
 
-    # roofline of the dominant kernel: DR stage 0 (every chain integrates nleap steps), timed by events between the
-    # stage launches of single hmcb_drhmc_step calls run straight after the timed region
-    L0 = max(a.nleap, 1)
-    st_ms = H["stage_ms"]
-    s0_flops = C * (L0 + 1) * fpg
+    # roofline of the dominant kernel of the timed region: DR stage 0 (every chain integrates nleap steps) as the plain kernel
+    # -- what hmcb_drhmc_sample launches with >= 3 chain ranges -- timed by events between the stage launches of single
+    # hmcb_drhmc_step calls run straight after the timed region (one launch over the whole batch where the timed region
+    # makes four over its quarters)
+    timed_plain = H["n_split"] >= 3          # csrc/api.cu: with fewer ranges the sample call launches the warp-specialised kernel
+    P0, P1 = (H["passes"]["plain"], H["passes"]["ws"]) if timed_plain else (H["passes"]["ws"], H["passes"]["plain"])
+    k_plain = "k_transition<Funnel,f64,EPL=%d,LPC=1,MODE_DR0>" % d
+    k_ws = "k_transition_ws<Funnel,f64,EPL=%d,MODE_DR0> (warp-specialised)" % d
+    st_ms = P0["stage_ms"]
+    s0_flops = P0["stage_grad_evals"][0] * fpg
     achieved = s0_flops / (st_ms[0] * 1e-3) / 1e12
-    roofline = {"bound": "fp64", "kernel": "k_transition_ws<Funnel,f64,EPL=50,MODE_DR0> (DR stage 0, warp-specialised)",
+
+    def fracs(Pp):
+        n = min(len(Pp["stage_ms"]), len(Pp["stage_grad_evals"]))
+        out = [Pp["stage_grad_evals"][j] * fpg / (Pp["stage_ms"][j] * 1e-3) / 1e12 / fp64_peak for j in range(n - 1)]
+        out.append(Pp["stage_grad_evals"][n - 1] * fpg / (sum(Pp["stage_ms"][n - 1:]) * 1e-3) / 1e12 / fp64_peak)
+        return out
+    roofline = {"bound": "fp64", "kernel": "%s: DR stage 0, the kernel the timed region launches" % (k_plain if timed_plain else k_ws),
                 "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak else None,
                 "traffic": None,
-                "traffic_note": "not measured in this run; one ncu --set full capture of this kernel at this shape read "
-                                "794,346,240 B per launch (profiles/r1b_ncu_dr_stages.md) against 2*C*d*8 + outputs = 0.87 GB "
-                                "algorithmic: the kernel is FP64-pipe-bound, HBM at 5 % of its peak",
+                "traffic_note": "not measured in this run; ncu --set full of the stage-0 kernels at this shape: 792 MB per launch "
+                                "(profiles/r2_ncu_kernels.md) against 2*C*d*8 + outputs = 0.87 GB algorithmic: FP64-pipe-bound, "
+                                "HBM at 5 % of its peak",
                 "peak_source": "hmcb_probe_fma: register-resident DFMA loop measured in this run on this GPU "
                                "(MEASURED_PEAKS.json has no FP64 figure)",
                 "algorithmic_flops_per_launch": s0_flops, "avg_launch_ms": st_ms[0], "stage_ms": st_ms, "stage_ms_sum": sum(st_ms),
+                "stage_frac": fracs(P0),
+                "stage_note": "per stage: gradient evaluations of the chains that reach it x 7d flops / its kernels' time / peak; "
+                              "stages >= 2 run as two kernels each (park / resume)",
+                "other_stage0_kernel": {"kernel": (k_ws + ": what a single hmcb_drhmc_step call launches at this size") if timed_plain
+                                        else (k_plain + ": what a sample call of >= 3 chain ranges launches"),
+                                        "stage_ms": P1["stage_ms"], "stage_frac": fracs(P1)},
                 "moments_kernel_ms": H["moments_ms"],
                 "timing_note": "stage kernels timed by CUDA events recorded inside hmcb_drhmc_step (hmcb_profile) over %d single "
-                               "transitions run straight after the timed region, stages serialised on one stream; the timed "
-                               "region itself runs %d chain ranges on %d streams, so its ms_per_step (%.3f) is to be compared "
+                               "transitions per variant run straight after the timed region, stages serialised on one stream; the "
+                               "timed region itself runs %d chain ranges on %d streams, so its ms_per_step (%.3f) is to be compared "
                                "with stage_ms_sum + moments_kernel_ms (%.3f)" %
                                (H["stage_passes"], H["n_split"], H["n_split"], ms_total / K, sum(st_ms) + H["moments_ms"]),
                 "step_frac_all_stages": grads / world * fpg / sec / 1e12 / fp64_peak,

@@ -183,7 +183,10 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
       // other place that re-draws p0 -- the DR stages >= 1, p_out of rejected chains -- would use the f64 one)
       // (nor inside hmcb_drhmc_sample, prefer_plain: a warp-specialised block owns a whole SM's registers and cannot share
       // an SM with the 2-per-SM blocks of another range's later stages -- with 4 ranges pipelined the plain kernel's
-      // packing wins: 5.34 -> 5.12 ms per transition at 2^20 chains although stage 0 alone is 8 % slower)
+      // packing wins: 5.34 -> 5.12 ms per transition at 2^20 chains although stage 0 alone is 8 % slower.  A two-blocks-
+      // per-SM form of the warp-specialised kernel (128 compute threads at 232 registers + 128 helpers at 24: no spills in
+      // the loop) was tried in its place: 4.939 against 4.945 ms -- inside the pipeline the other ranges' blocks on the
+      // same SM already cover a block's momentum prologue, so it is not kept)
       if (!a.p_inject && !a.p_prev && !a.prefer_plain && !(a.rng_flags & HMCB_RNG_NORMAL_F64) && a.n_chains >= 4096) {
         // (the per-warp staging tile of the plain kernel does not pay here: L=150 2.02 -> 2.18 ms.)  tile_io instead
         // selects a shared-memory copy of q0 for the no-move test and the copy-through of rejected chains
@@ -193,8 +196,9 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
         // vanilla HMC only: in DR stage 0 the rejected chains are not copied through, and what the no-move test saves
         // is less than what the smaller L1 (204 KB of shared memory per SM) costs the strided row accesses
         // (DRHMC nleap=20: 0.787 -> 0.815 ms with the copy)
-        a.tile_io = (op == OP_HMC && base_smem + q0s_bytes <= (size_t)max_optin_smem() &&
-                     !(getenv("HMCB_WS_Q0S") && !atoi(getenv("HMCB_WS_Q0S")))) ? 1 : 0;
+        // (measured again with HMCB_WS_Q0S=2: DRHMC nleap=20 0.778 -> 0.801 ms)
+        const int q0s_env = getenv("HMCB_WS_Q0S") ? atoi(getenv("HMCB_WS_Q0S")) : 1;     // 0 off, 1 vanilla HMC only, 2 DR stage 0 too
+        a.tile_io = ((op == OP_HMC || q0s_env == 2) && q0s_env != 0 && base_smem + q0s_bytes <= (size_t)max_optin_smem()) ? 1 : 0;
         const size_t ws_smem = base_smem + (a.tile_io ? q0s_bytes : 0);
         const int grid = (int)((a.n_chains + kWsComputeThreads - 1) / kWsComputeThreads < sm_count()
                                    ? (a.n_chains + kWsComputeThreads - 1) / kWsComputeThreads

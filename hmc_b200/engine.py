@@ -335,7 +335,7 @@ class Engine:
         cur = torch.cuda.current_stream(self.device)
         with torch.cuda.device(self.device):
             if self._streams is None:
-                self._streams = [torch.cuda.Stream(device=self.device) for _ in range(4)]
+                self._streams = [torch.cuda.Stream(device=self.device) for _ in range(6)]
             key = (C_, d, nprops, bool(want_p))
             if self._host_stage is None or self._host_stage[0] != key:
                 dev = dict(device=self.device)
@@ -348,7 +348,7 @@ class Engine:
                     "counts": torch.empty((C_, 3), dtype=torch.int32, **dev)})
         stage = self._host_stage[1]
         s_in, s_out = self._streams[0], self._streams[1]
-        runs = self._streams[2:2 + max(1, min(2, int(run_streams)))]
+        runs = self._streams[2:2 + max(1, min(4, int(run_streams)))]
         # chunk boundaries: halves at both ends, equal pieces between
         if n_chunks >= 3:
             w = [0.5] + [1.0] * (n_chunks - 1) + [0.5]
