@@ -719,15 +719,28 @@ def run_hmcb(a):
         out = [Pp["stage_grad_evals"][j] * fpg / (Pp["stage_ms"][j] * 1e-3) / 1e12 / fp64_peak for j in range(n - 1)]
         out.append(Pp["stage_grad_evals"][n - 1] * fpg / (sum(Pp["stage_ms"][n - 1:]) * 1e-3) / 1e12 / fp64_peak)
         return out
-    roofline = {"bound": "fp64", "kernel": "%s: DR stage 0, the kernel the timed region launches" % (k_plain if timed_plain else k_ws),
-                "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak else None,
+    region_tflops = grads / world * fpg / sec / 1e12
+    roofline = {"bound": "fp64",
+                "kernel": "the stage kernels of the timed hmcb_drhmc_sample call together (k_transition<MODE_DR0> and k_transition<MODE_DRN>, "
+                          "%d launches per transition and chain range, overlapping on %d streams: they have no durations of their own "
+                          "there); per-kernel figures from serialised passes in 'stage0_kernel' / 'stage_frac'" %
+                          (len(st_ms) + max(0, len(st_ms) - 2), H["n_split"]),
+                "achieved": region_tflops, "peak": fp64_peak, "unit": "TFLOP/s", "frac": region_tflops / fp64_peak if fp64_peak else None,
+                "achieved_note": "ALGORITHMIC flops of the timed region (sum of Vgcount x 7d; the exp polynomial, energies and RNG are "
+                                 "executed but not counted) / its duration, per GPU",
+                "stage0_kernel": {"kernel": "%s: DR stage 0 as the timed region launches it (largest single kernel: %.0f %% of the "
+                                            "gradient work)" % (k_plain if timed_plain else k_ws, 100 * P0["stage_grad_evals"][0] * world / grads * K
+                                                                if grads else 0.0),
+                                  "achieved": achieved, "frac": achieved / fp64_peak if fp64_peak else None,
+                                  "algorithmic_flops_per_launch": s0_flops, "avg_launch_ms": st_ms[0]},
                 "traffic": None,
                 "traffic_note": "not measured in this run; ncu --set full of the stage-0 kernels at this shape: 792 MB per launch "
                                 "(profiles/r2_ncu_kernels.md) against 2*C*d*8 + outputs = 0.87 GB algorithmic: FP64-pipe-bound, "
                                 "HBM at 5 % of its peak",
                 "peak_source": "hmcb_probe_fma: register-resident DFMA loop measured in this run on this GPU "
                                "(MEASURED_PEAKS.json has no FP64 figure)",
-                "algorithmic_flops_per_launch": s0_flops, "avg_launch_ms": st_ms[0], "stage_ms": st_ms, "stage_ms_sum": sum(st_ms),
+                "algorithmic_flops_per_step": grads / world * fpg / K, "avg_step_ms": ms_total / K,
+                "stage_ms": st_ms, "stage_ms_sum": sum(st_ms),
                 "stage_frac": fracs(P0),
                 "stage_note": "per stage: gradient evaluations of the chains that reach it x 7d flops / its kernels' time / peak; "
                               "stages >= 2 run as two kernels each (park / resume)",
@@ -740,7 +753,7 @@ def run_hmcb(a):
                                "timed region itself runs %d chain ranges on %d streams, so its ms_per_step (%.3f) is to be compared "
                                "with stage_ms_sum + moments_kernel_ms (%.3f)" %
                                (H["stage_passes"], H["n_split"], H["n_split"], ms_total / K, sum(st_ms) + H["moments_ms"]),
-                "step_frac_all_stages": grads / world * fpg / sec / 1e12 / fp64_peak,
+                "step_frac_all_stages": region_tflops / fp64_peak,
                 "hbm_peak_gbs": peaks["hbm_gbs"], "hbm_peak_source": peaks["source"],
                 "algorithmic_hbm_gbs_of_the_step": (2 * C * d * 8 + 5 * C * d * 8) / (ms_total / K * 1e-3) / 1e9}
 

@@ -817,11 +817,12 @@ int hmcb_drhmc_sample(const hmcb_model* model, const hmcb_chains* chains, const 
   const int min_accept = convention == HMCB_DR_ALGORITHMS ? 1 : 0;
   // transition k of every range is enqueued before transition k+1 of any: all streams have work from the start
   rc = 0;
+  int forked = 1;   // streams that wait on the fork event (the caller's included): exactly these are joined below
   for (int i = 1; i < S && rc == 0; ++i) {
     cudaError_t ce = cudaStreamWaitEvent(h->s[i - 1], h->fork, 0);
     if (ce != cudaSuccess) rc = cuda_fail(ce, "cudaStreamWaitEvent(helper, fork)");
+    else forked = i + 1;
   }
-  int forked = rc == 0 ? S : 1;
   for (int k = 0; k < K && rc == 0; ++k) {
     for (int i = 0; i < S && rc == 0; ++i) {
       const int64_t lo = split_bound(chains->n_chains, S, i), hi = split_bound(chains->n_chains, S, i + 1);

@@ -169,6 +169,23 @@ def test_k_hmc_transitions_in_one_call_equal_k_single_calls(kind, d, C, rule):
     assert 0.3 < nacc.double().mean().item() / K < 1.0
 
 
+def test_k_hmc_transitions_float32_and_diagonal_metric():
+    """The generic fused kernel (k_hmc_multi) on a float32 shape and with a diagonal metric."""
+    from hmc_b200 import pyhmc
+    d, C, K, L, eps = 10, 3000, 5, 8, 0.1
+    dev = _dev()
+    q0 = torch.as_tensor(_q0("funnel", C, d, 23), device=dev)
+    for kw in (dict(dtype=torch.float32), dict(invmetric_diag=np.linspace(0.5, 2.0, d))):
+        a = pyhmc.HMC(models.Funnel(d), device=dev, seed=8, **kw).engine
+        b = pyhmc.HMC(models.Funnel(d), device=dev, seed=8, **kw).engine
+        q = q0.to(a.dtype)
+        for k in range(K):
+            r = a.hmc_step(q, L, eps, _lib.RULE_PYHMC)
+            q = r["q"]
+        rb = b.hmc_sample(q0.to(b.dtype), L, eps, _lib.RULE_PYHMC, K, want_p=True)
+        assert torch.equal(rb["q"], q) and torch.equal(rb["code"], r["code"]) and torch.equal(rb["p"], r["p"])
+
+
 def test_k_hmc_transitions_with_moments_and_in_place():
     from hmc_b200 import pyhmc
     d, C, K, L, eps = 50, 6000, 5, 6, 0.2
