@@ -118,6 +118,8 @@ SIGNATURES = {
                                        C.c_double, C.c_int32, C.POINTER(StepOut), C.c_void_p, C.c_size_t, C.c_void_p]),
     "hmcb_logreg_logp_grad": (C.c_int, [C.POINTER(Model), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                         C.c_void_p, C.c_size_t, C.c_void_p]),
+    "hmcb_logreg_mala_step": (C.c_int, [C.POINTER(Model), C.c_void_p, C.POINTER(Chains), C.POINTER(Rng), C.c_double, C.c_int32,
+                                        C.POINTER(MalaIO), C.c_void_p, C.c_size_t, C.c_void_p]),
     "hmcb_probe_normals": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.POINTER(C.c_double),
                                      C.c_void_p]),
     "hmcb_probe_fma": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.POINTER(C.c_double),

@@ -236,6 +236,150 @@ __global__ void __launch_bounds__(256) k_lr_update(const StepArgs a) {
   }
 }
 
+// ------------------------------------------------------------------ MALA over the tensor-core gradient
+// mala.MALA.step + metropolis (src/mala.py:45-60, 24-42) for the logistic model: per step one gradient sweep at the
+// proposal q1 = q - eps^2/2 grad V(q) + eps z, then the Hastings test; V(q) and grad V(q) are carried from step to step
+// (and between calls, as the reference carries them through its return values).
+struct MalaArgsLR {
+  int64_t n_chains, chain_offset;
+  int32_t d, n_slabs;
+  float* q;            // current state, [C,d] (= q_out)
+  float* q1;           // proposal (ws theta)
+  float* g0;           // grad V(q) (ws)
+  double* V0;          // V(q) (ws)
+  const float* Gpart;
+  const double* Vpart;
+  uint64_t seed;
+  uint32_t iteration;
+  const float* z_inject;
+  const double* u_inject;
+  int32_t u_stride, step;
+  float eps, inv_tau2;
+  int32_t* code;
+  int32_t* n_accept;
+  int32_t* counts;
+  int32_t first;       // first step of the call: n_accept / counts are assigned, not added to
+  int32_t nvg0;        // gradient evaluations already spent on V_gq at the start point (0 or 1)
+};
+
+__global__ void k_lr_mala_propose(const MalaArgsLR a) {
+  const int nblk = (a.d + 3) / 4;
+  const int64_t n = a.n_chains * nblk;
+  const float half_e2 = 0.5f * a.eps * a.eps;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t c = i / nblk;
+    const int b = (int)(i - c * nblk);
+    float z[4];
+    if (a.z_inject) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) z[k] = (4 * b + k < a.d) ? a.z_inject[c * a.d + 4 * b + k] : 0.f;
+    } else {
+      uint32_t w[4];
+      Philox::gen(a.seed, (uint64_t)(a.chain_offset + c), a.iteration + (uint32_t)a.step, STREAM_MOMENTUM, (uint32_t)b, w);
+      normal4_f32(w, z);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int col = 4 * b + k;
+      if (col < a.d) {
+        const int64_t o = c * a.d + col;
+        a.q1[o] = (a.q[o] - half_e2 * a.g0[o]) + a.eps * z[k];      // src/mala.py:54
+      }
+    }
+  }
+}
+
+// one warp per chain.  INIT: V(q), grad V(q) from the sweep at q.  else: the Hastings test of one step.
+template <bool INIT>
+__global__ void __launch_bounds__(256) k_lr_mala_update(const MalaArgsLR a) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+  const float half_e2 = 0.5f * a.eps * a.eps;
+  for (int64_t c = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); c < a.n_chains; c += warps) {
+    const float* x = INIT ? a.q : a.q1;       // the point the sweep was taken at
+    float th[4], g[4];
+    double th2 = 0.0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int col = lane + 32 * k;
+      const bool ok = col < a.d;
+      th[k] = ok ? x[c * a.d + col] : 0.f;
+      float gs = 0.f;
+      for (int s = 0; s < a.n_slabs; ++s) gs += ok ? a.Gpart[((size_t)s * a.n_chains + c) * kD + col] : 0.f;
+      g[k] = gs + th[k] * a.inv_tau2;
+      th2 += (double)th[k] * th[k];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) th2 += __shfl_xor_sync(0xffffffffu, th2, o);
+    double V = 0.0;
+    for (int s = 0; s < a.n_slabs; ++s) V += a.Vpart[(size_t)s * a.n_chains + c];
+    V += 0.5 * th2 * (double)a.inv_tau2;
+    if (INIT) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int col = lane + 32 * k;
+        if (col < a.d) a.g0[c * a.d + col] = g[k];
+      }
+      if (lane == 0) a.V0[c] = V;
+      continue;
+    }
+    // Hastings ratio as the reference forms it (src/mala.py:24-30)
+    double ld = 0.0, ln = 0.0, dq = 0.0;
+    float q0[4], g0[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int col = lane + 32 * k;
+      const bool ok = col < a.d;
+      q0[k] = ok ? a.q[c * a.d + col] : 0.f;
+      g0[k] = ok ? a.g0[c * a.d + col] : 0.f;
+      const float mu0 = q0[k] - half_e2 * g0[k], mu1 = th[k] - half_e2 * g[k];
+      const double a0 = (double)th[k] - (double)mu0, a1 = (double)q0[k] - (double)mu1;
+      ld += a0 * a0;
+      ln += a1 * a1;
+      dq += (double)q0[k] - (double)th[k];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      ld += __shfl_xor_sync(0xffffffffu, ld, o);
+      ln += __shfl_xor_sync(0xffffffffu, ln, o);
+      dq += __shfl_xor_sync(0xffffffffu, dq, o);
+    }
+    const double e2 = (double)a.eps * (double)a.eps;
+    const double V0 = a.V0[c];
+    const double prob = exp(V0 - V) * exp(-0.5 * ln / e2 + 0.5 * ld / e2);
+    const bool bad = isnan(prob) || isinf(prob) || dq == 0.0;
+    bool accept = false;
+    if (!bad) {
+      double u;
+      if (a.u_inject) {
+        u = a.u_inject[c * a.u_stride + a.step];
+      } else {
+        uint32_t w[4];
+        Philox::gen(a.seed, (uint64_t)(a.chain_offset + c), a.iteration + (uint32_t)a.step, STREAM_ACCEPT, 0, w);
+        u = u53(w[0], w[1]);
+      }
+      accept = !(u > (prob < 1.0 ? prob : 1.0));
+    }
+    if (accept) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int col = lane + 32 * k;
+        if (col < a.d) { a.q[c * a.d + col] = th[k]; a.g0[c * a.d + col] = g[k]; }
+      }
+    }
+    if (lane == 0) {
+      if (accept) a.V0[c] = V;
+      if (a.code) a.code[c] = bad ? 2 : (accept ? 1 : 0);
+      if (a.n_accept) a.n_accept[c] = (a.first ? 0 : a.n_accept[c]) + (accept ? 1 : 0);
+      if (a.counts) {
+        a.counts[3 * c] = 0;
+        a.counts[3 * c + 1] = (a.first ? a.nvg0 : a.counts[3 * c + 1]) + 1;
+        a.counts[3 * c + 2] = 0;
+      }
+    }
+  }
+}
+
 static int launch_grad(const hmcb_model& m, const unsigned char* prep, const PrepLayout& P, const WsLayout& W,
                        const float* theta, float* Gpart, double* Vpart, int64_t n_chains, bool want_v, cudaStream_t st) {
   GradArgsV1 g{};
@@ -366,6 +510,68 @@ int hmcb_logreg_hmc_step(const hmcb_model* model, const void* prepared, const hm
     else if (i < N) k_lr_update<PH_MID><<<ublocks, 256, 0, st>>>(a);
     else k_lr_update<PH_LAST><<<ublocks, 256, 0, st>>>(a);
   }
+  HMCB_CUDA(cudaPeekAtLastError());
+  return 0;
+}
+
+int hmcb_logreg_mala_step(const hmcb_model* model, const void* prepared, const hmcb_chains* chains, const hmcb_rng* rng,
+                          double eps, int32_t n_steps, const hmcb_mala_io* io, void* workspace, size_t workspace_bytes,
+                          void* stream) {
+  int rc;
+  if ((rc = check_lr_model(model))) return rc;
+  HMCB_CHECK_ARG(prepared != nullptr, "prepared model buffer is NULL (call hmcb_logreg_prepare first)");
+  HMCB_CHECK_ARG(chains != nullptr && rng != nullptr, "chains/rng is NULL");
+  HMCB_CHECK_ARG(chains->n_chains >= 0 && chains->n_chains < (int64_t)1 << 31, "n_chains out of range");
+  HMCB_CHECK_ARG(n_steps >= 1 && eps > 0, "n_steps must be >= 1 and eps > 0");
+  HMCB_CHECK_ARG(!rng->p_inject || n_steps == 1, "injected normals are only defined for n_steps == 1");
+  HMCB_CHECK_ARG(!rng->u_inject || rng->u_stride >= n_steps, "u_inject needs u_stride >= n_steps");
+  if (chains->n_chains == 0) return 0;
+  HMCB_CHECK_ARG(chains->q_in && chains->q_out, "q_in/q_out must be device pointers");
+  HMCB_CHECK_ARG(chains->stride_dim == 1 && chains->stride_chain == model->d,
+                 "logistic regression needs contiguous row-major [C,d] chain state");
+  const int64_t C = chains->n_chains;
+  const PrepLayout P = prep_layout(model->n_data);
+  const WsLayout W = ws_layout(C, model->d, P.n_blocks);
+  if (!workspace || workspace_bytes < W.total) {
+    set_error("logreg workspace too small: have %zu bytes, need %zu", workspace ? workspace_bytes : (size_t)0, W.total);
+    return HMCB_E_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned char* ws = (unsigned char*)workspace;
+  MalaArgsLR a{};
+  a.n_chains = C; a.chain_offset = chains->chain_offset; a.d = model->d; a.n_slabs = W.n_slabs;
+  a.q = (float*)chains->q_out; a.q1 = (float*)(ws + W.off_theta); a.g0 = (float*)(ws + W.off_p);
+  a.V0 = (double*)(ws + W.off_H0);
+  a.Gpart = (const float*)(ws + W.off_G); a.Vpart = (const double*)(ws + W.off_V);
+  a.seed = rng->seed; a.iteration = (uint32_t)rng->iteration;
+  a.z_inject = (const float*)rng->p_inject; a.u_inject = rng->u_inject; a.u_stride = rng->u_stride;
+  a.eps = (float)eps; a.inv_tau2 = (float)(1.0 / (model->par[0] * model->par[0]));
+  if (io) { a.code = io->code; a.n_accept = io->n_accept; a.counts = io->counts; }
+  const size_t qbytes = (size_t)C * model->d * 4;
+  if (chains->q_out != chains->q_in) HMCB_CUDA(cudaMemcpyAsync(a.q, chains->q_in, qbytes, cudaMemcpyDeviceToDevice, st));
+  const int ublocks = (int)((C + 7) / 8 < 4096 ? (C + 7) / 8 : 4096);
+  const bool have_v = io && io->V_in, have_g = io && io->Vg_in;
+  a.nvg0 = have_g ? 0 : 1;
+  if (!have_v || !have_g) {
+    // V(q), grad V(q) from one sweep at q (src/mala.py:49-52: whichever of the two the caller did not carry over)
+    if ((rc = launch_grad(*model, (const unsigned char*)prepared, P, W, a.q, (float*)(ws + W.off_G), (double*)(ws + W.off_V), C,
+                          true, st)))
+      return rc;
+    k_lr_mala_update<true><<<ublocks, 256, 0, st>>>(a);
+  }
+  if (have_g) HMCB_CUDA(cudaMemcpyAsync(a.g0, io->Vg_in, qbytes, cudaMemcpyDeviceToDevice, st));
+  if (have_v) HMCB_CUDA(cudaMemcpyAsync(a.V0, io->V_in, (size_t)C * 8, cudaMemcpyDeviceToDevice, st));
+  for (int k = 0; k < n_steps; ++k) {
+    a.step = k;
+    a.first = k == 0;
+    k_lr_mala_propose<<<sm_count() * 4, 256, 0, st>>>(a);
+    if ((rc = launch_grad(*model, (const unsigned char*)prepared, P, W, a.q1, (float*)(ws + W.off_G), (double*)(ws + W.off_V), C,
+                          true, st)))
+      return rc;
+    k_lr_mala_update<false><<<ublocks, 256, 0, st>>>(a);
+  }
+  if (io && io->Vg_out) HMCB_CUDA(cudaMemcpyAsync(io->Vg_out, a.g0, qbytes, cudaMemcpyDeviceToDevice, st));
+  if (io && io->V_out) HMCB_CUDA(cudaMemcpyAsync(io->V_out, a.V0, (size_t)C * 8, cudaMemcpyDeviceToDevice, st));
   HMCB_CUDA(cudaPeekAtLastError());
   return 0;
 }

@@ -422,7 +422,10 @@ class Engine:
         C_ = q.shape[0]
         with torch.cuda.device(self.device):
             q_out = torch.empty_like(q) if q_out is None else q_out
-            out = {"q": q_out, "V": torch.empty(C_, dtype=self.dtype, device=self.device), "Vg": torch.empty_like(q),
+            vdt = torch.float64 if self.is_logistic else self.dtype     # the logistic path carries V(q) in float64
+            if V is not None:
+                V = V.to(vdt).contiguous()
+            out = {"q": q_out, "V": torch.empty(C_, dtype=vdt, device=self.device), "Vg": torch.empty_like(q),
                    "code": torch.empty(C_, dtype=torch.int32, device=self.device),
                    "n_accept": torch.empty(C_, dtype=torch.int32, device=self.device),
                    "counts": torch.empty((C_, 3), dtype=torch.int32, device=self.device)}
@@ -432,8 +435,15 @@ class Engine:
             io.n_accept, io.counts = _lib.ptr(out["n_accept"]), _lib.ptr(out["counts"])
             ch = self._chains(q, q_out)
             r, keep = self._rng(z, u, n_steps, C_)
-            _lib.check(self.lib.hmcb_mala_step(C.byref(m), C.byref(ch), C.byref(r), float(eps), int(n_steps),
-                                               C.byref(io), self._stream()))
+            keep.append(V)
+            if self.is_logistic:
+                ws = self._lr_workspace(C_)
+                _lib.check(self.lib.hmcb_logreg_mala_step(C.byref(m), C.c_void_p(self._lr_prepared.data_ptr()), C.byref(ch),
+                                                          C.byref(r), float(eps), int(n_steps), C.byref(io),
+                                                          C.c_void_p(ws.data_ptr()), ws.numel(), self._stream()))
+            else:
+                _lib.check(self.lib.hmcb_mala_step(C.byref(m), C.byref(ch), C.byref(r), float(eps), int(n_steps),
+                                                   C.byref(io), self._stream()))
         self.iteration += int(n_steps)
         out["_keep"] = keep
         return out

@@ -39,7 +39,8 @@ class MALA:
         e = self.engine
         b = Batch(q, e.dev, e.dtype)
         e.check_dim(b)
-        V = None if V_q is None else torch.as_tensor(V_q).reshape(-1).to(device=e.device, dtype=e.dtype).contiguous()
+        vdt = torch.float64 if e.is_logistic else e.dtype      # the logistic path carries V(q) in float64 (hmcb_logreg_mala_step)
+        V = None if V_q is None else torch.as_tensor(V_q).reshape(-1).to(device=e.device, dtype=vdt).contiguous()
         Vg = None if V_gq is None else Batch(V_gq, e.device, e.dtype).q
         out = e.mala_step(b.q, eps, n_steps=n_steps, V=V, Vg=Vg, z=z, u=u)
         self.n_accept = b.out(out["n_accept"])

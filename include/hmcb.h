@@ -366,6 +366,15 @@ int hmcb_logreg_hmc_step(const hmcb_model* model, const void* prepared, const hm
                          const hmcb_step_out* out, void* workspace, size_t workspace_bytes, void* stream);
 int hmcb_logreg_logp_grad(const hmcb_model* model, const void* prepared, const void* theta, int64_t n_chains,
                           void* logp, void* grad, void* workspace, size_t workspace_bytes, void* stream);
+/*  - hmcb_logreg_mala_step: n_steps MALA steps per chain over the same tensor-core gradient
+ *    (mala.MALA.step + metropolis, src/mala.py:45-60,24-42; one gradient sweep per step), semantics
+ *    and outputs as hmcb_mala_step with two differences: the cached potential V_in / V_out is
+ *    FLOAT64 [C] (the reference carries V(q) as a Python float; float32 would lose the Hastings
+ *    ratio's low bits at V ~ 1e5), Vg_in / Vg_out are float32 [C,d].  Workspace:
+ *    hmcb_logreg_workspace_bytes(). */
+int hmcb_logreg_mala_step(const hmcb_model* model, const void* prepared, const hmcb_chains* chains,
+                          const hmcb_rng* rng, double eps, int32_t n_steps, const hmcb_mala_io* io,
+                          void* workspace, size_t workspace_bytes, void* stream);
 
 /* The draw contract, on the host (no GPU needed), so that tests can pin it:
  *  - hmcb_philox4x32_10: the raw Philox4x32-10 block function (Salmon et al. 2011), checked

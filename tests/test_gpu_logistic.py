@@ -129,3 +129,55 @@ def test_production_path_samples_the_posterior():
     sd = np.sqrt(np.diag(cov))
     assert np.abs(q.mean(0).cpu().numpy() - th).max() < 6 * sd.max() / np.sqrt(C) + 0.02 * sd.max()
     assert np.abs(q.std(0).cpu().numpy() / sd - 1).max() < 0.1
+
+
+def test_mala_over_the_tensor_core_gradient_vs_oracle():
+    """mala.MALA.step on the logistic model (hmcb_logreg_mala_step): float32 state against the float64 oracle with the
+    same injected normals and uniforms, cached V / grad V carried from step to step as the reference does."""
+    from hmc_b200 import mala
+    N, d, C, eps = 3000, 24, 61, 0.15
+    X, y = _data(N, d, 31)
+    om = omodels.LogisticRegression(X.astype(np.float64), y.astype(np.float64), 1.2)
+    s = mala.MALA(models.LogisticRegression(X, y, 1.2), device=_dev())
+    q0 = (0.3 * np.random.default_rng(3).standard_normal((C, d))).astype(np.float32)
+    P, U = replay.make_draws(91, 3, C, d, 1)
+    P = P.astype(np.float32)
+    q, V, Vg = q0, None, None
+    rq, rV, rVg = [x.astype(np.float64) for x in q0], [None] * C, [None] * C
+    seen = set()
+    for t in range(3):
+        q, code, V, Vg = s.step(q, eps, V, Vg, z=P[t], u=U[t])
+        ref = [samplers.mala_step(om, rq[c], eps, replay.Draws([P[t, c].astype(np.float64)], U[t, c]), rV[c], rVg[c]) for c in range(C)]
+        rcode = np.array([r[1] for r in ref])
+        seen |= set(rcode.tolist())
+        assert (np.asarray(code) != rcode).sum() <= 1            # a flip needs |u - prob| within fp32 noise
+        same = np.asarray(code) == rcode
+        for c in range(C):
+            rq[c], rV[c], rVg[c] = ref[c][0], ref[c][2], ref[c][3]
+        R = np.array(rq)
+        assert _rel(np.asarray(q)[same], R[same], 1e-2) < 1e-5
+        assert _rel(np.asarray(V)[same], np.array(rV)[same], 1.0) < 2e-6
+        assert _rel(np.asarray(Vg)[same], np.array(rVg)[same], 1.0) < 3e-5
+        # continue from the GPU's own state on both sides (a flipped chain would otherwise diverge)
+        rq = [np.asarray(q, dtype=np.float64)[c] for c in range(C)]
+        rV, rVg = [None] * C, [None] * C
+        V, Vg = (V, Vg) if t % 2 == 0 else (None, None)         # with and without the carried caches
+    print("codes seen:", seen)
+    assert 1.0 in seen
+
+
+def test_mala_logistic_fused_steps_equal_single_steps():
+    from hmc_b200 import mala
+    N, d, C, eps, K = 2000, 16, 300, 0.03, 4
+    X, y = _data(N, d, 33)
+    a = mala.MALA(models.LogisticRegression(X, y, 1.0), device=_dev(), seed=5)
+    b = mala.MALA(models.LogisticRegression(X, y, 1.0), device=_dev(), seed=5)
+    q0 = torch.as_tensor((0.2 * np.random.default_rng(4).standard_normal((C, d))).astype(np.float32), device=_dev())
+    q, V, Vg, nacc = q0, None, None, 0
+    for k in range(K):
+        q, code, V, Vg = a.step(q, eps, V, Vg)
+        nacc = nacc + (code == 1).int()
+    qb, codeb, Vb, Vgb = b.step(q0, eps, n_steps=K)
+    assert torch.equal(qb, q) and torch.equal(codeb, code) and torch.equal(Vb, V) and torch.equal(Vgb, Vg)
+    assert torch.equal(b.n_accept.int(), nacc)
+    assert 0.2 < nacc.double().mean().item() / K <= 1.0
