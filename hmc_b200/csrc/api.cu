@@ -761,6 +761,27 @@ static int sample_layouts(const Entry* e, const hmcb_model* m, int64_t n_chains,
   return 0;
 }
 
+// the multi-pass form for short trajectories (transition_ws.cuh, k_dr0_multi_ws): one chain range, the stage kernels'
+// scratch, then iter_done[C], iter_of[C], two continue lists [C] and their two counters
+struct ShortLayout {
+  DrLayout L;
+  size_t off_done, off_of, off_cl[2], off_cc, total;
+};
+
+static int short_layout(const Entry* e, const hmcb_model* m, int64_t n_chains, int nprops, ShortLayout& S) {
+  int rc = dr_layout(e, m, n_chains, nprops, S.L, false);
+  if (rc) return rc;
+  size_t off = S.L.total;
+  const size_t cb = align_up((size_t)n_chains * sizeof(int32_t), 256);
+  S.off_done = off; off += cb;
+  S.off_of = off;   off += cb;
+  S.off_cl[0] = off; off += cb;
+  S.off_cl[1] = off; off += cb;
+  S.off_cc = off;   off += 256;
+  S.total = off;
+  return 0;
+}
+
 size_t hmcb_drhmc_sample_workspace_bytes(const hmcb_model* model, int64_t n_chains, int32_t nprops) {
   if (check_model(model)) return 0;
   if (n_chains < 1 || nprops < 1 || nprops > kMaxProps) {
@@ -772,7 +793,106 @@ size_t hmcb_drhmc_sample_workspace_bytes(const hmcb_model* model, int64_t n_chai
   DrLayout L[kMaxSplit];
   size_t offc[kMaxSplit], total = 0;
   if (sample_layouts(e, model, n_chains, nprops, sample_split_for(n_chains), L, offc, total)) return 0;
-  return total;
+  ShortLayout SL;
+  if (short_layout(e, model, n_chains, nprops, SL)) return 0;
+  return total > SL.total ? total : SL.total;
+}
+
+// Batches from which the short-trajectory form pays: 2^20 chains of the d=50 funnel at nleap=20, 0.79 -> 0.69 ms per
+// transition; at 2^17 chains it loses (0.18 -> 0.23 ms: its passes over short lists are mostly barrier latency).
+static int64_t short_min_chains() {
+  if (const char* ev = getenv("HMCB_DR_SHORT_MIN")) return atoll(ev);
+  return (int64_t)1 << 19;
+}
+
+// K transitions at short trajectories: chunks of kShortChunk transitions, each a first pass of k_dr0_multi_ws over all
+// chains and then, kShortChunk times, the delayed-rejection stage kernels over the chains that stopped and a pass over
+// those that go on.  Returns 1 if this shape / call has no such kernel (the caller then runs the pipelined form).
+constexpr int kShortChunk = 5;   // measured 2..8 on the d=50 funnel at nleap=20: 0.69-0.71 ms per transition, flat
+
+static int drhmc_sample_short(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r, int n_leap,
+                              double eps, int nprops, double stepfactor, int conv, int K, const hmcb_sample_io* io,
+                              const hmcb_step_out* o, void* ws, size_t ws_bytes, cudaStream_t st) {
+  MultiDrArgs<double> M;
+  memset(&M, 0, sizeof(M));
+  TransArgs<double>& a = M.a;
+  fill_args(a, m, c, r, o);
+  M.query_only = 1;
+  int rc = e->fn(*m, OP_DR0_MULTI, &M, st);
+  if (rc) return rc;
+  if (!M.applied) return 1;
+  ShortLayout SL;
+  if ((rc = short_layout(e, m, c->n_chains, nprops, SL))) return rc;
+  if (!ws || ws_bytes < SL.total) {
+    set_error("drhmc sample workspace too small: have %zu bytes, need %zu", ws ? ws_bytes : (size_t)0, SL.total);
+    return HMCB_E_WORKSPACE;
+  }
+  const int64_t C = c->n_chains;
+  char* w = (char*)ws;
+  a.nprops = nprops;
+  a.dr_conv = conv != HMCB_DR_ALGORITHMS;
+  a.dr_prob = conv == HMCB_DR_PROB_METROP ? 1 : (conv == HMCB_DR_PROB_HASTINGS ? 2 : 0);
+  if (!a.dr_prob) a.ptries_out = nullptr;
+  for (int j = 0; j < nprops; ++j) {
+    const double fac = pow(stepfactor, (double)j);     // src/algorithms.py:510-511
+    a.L[j] = (int32_t)(n_leap * fac);
+    a.eps[j] = eps / fac;
+  }
+  const DrLayout& L = SL.L;
+  a.ws.count = (int32_t*)(w + L.off_count);
+  a.ws.list = (int32_t*)(w + L.off_list);
+  a.ws.H0 = (double*)(w + L.off_H0);
+  a.ws.avec = (double*)(w + L.off_avec);
+  a.ws.counts = (int32_t*)(w + L.off_counts);
+  a.ws.ptries = (double*)(w + L.off_ptries);
+  a.ws.frames = (double*)(w + L.off_frames);
+  a.ws.frame_threads = L.frame_threads;
+  int32_t* iter_done = (int32_t*)(w + SL.off_done);
+  int32_t* iter_of = (int32_t*)(w + SL.off_of);
+  int32_t* CL[2] = {(int32_t*)(w + SL.off_cl[0]), (int32_t*)(w + SL.off_cl[1])};
+  int32_t* CC[2] = {(int32_t*)(w + SL.off_cc), (int32_t*)(w + SL.off_cc) + 32};
+  a.iter_of = iter_of;
+  a.iter_done = iter_done;
+  a.n_accept = io->n_accept;
+  // in place on q_out; counts are summed over the call
+  if (c->q_out != c->q_in) HMCB_CUDA(cudaMemcpyAsync(c->q_out, c->q_in, (size_t)C * m->d * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  a.q_in = a.q_out;
+  if (a.counts) HMCB_CUDA(cudaMemsetAsync(a.counts, 0, (size_t)C * 3 * sizeof(int32_t), st));
+  M.query_only = 0;
+  M.iter_of = iter_of;
+  const size_t count_bytes = (kMaxProps + 2) * sizeof(int32_t);
+  int chunk = kShortChunk;
+  if (const char* ev = getenv("HMCB_DR_SHORT_CHUNK")) {
+    const int v = atoi(ev);
+    if (v >= 1 && v <= 64) chunk = v;
+  }
+  for (int base = 0; base < K; base += chunk) {
+    const int Kc = K - base < chunk ? K - base : chunk;
+    a.iteration = (uint32_t)(r->iteration + (uint64_t)base);
+    a.K_total = Kc;
+    HMCB_CUDA(cudaMemsetAsync(iter_done, 0, (size_t)C * sizeof(int32_t), st));
+    HMCB_CUDA(cudaMemsetAsync(a.ws.count, 0, count_bytes, st));
+    HMCB_CUDA(cudaMemsetAsync(CC[0], 0, 256, st));
+    M.max_steps = Kc; M.list = nullptr; M.list_count = nullptr;
+    if ((rc = e->fn(*m, OP_DR0_MULTI, &M, st))) return rc;
+    if (nprops == 1) continue;      // nothing is ever handed on
+    int cur = 0;
+    for (int p = 1; p <= Kc; ++p) {
+      a.cont_list = CL[cur];
+      a.cont_count = CC[cur];
+      for (int j = 1; j < nprops; ++j) {
+        a.stage = j;
+        if ((rc = e->fn(*m, OP_DRN, &a, st))) return rc;
+      }
+      if (p == Kc) break;
+      HMCB_CUDA(cudaMemsetAsync(a.ws.count, 0, count_bytes, st));
+      M.max_steps = Kc - p; M.list = CL[cur]; M.list_count = CC[cur];
+      if ((rc = e->fn(*m, OP_DR0_MULTI, &M, st))) return rc;
+      cur ^= 1;
+      HMCB_CUDA(cudaMemsetAsync(CC[cur], 0, 128, st));
+    }
+  }
+  return 0;
 }
 
 int hmcb_drhmc_sample(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
@@ -797,6 +917,15 @@ int hmcb_drhmc_sample(const hmcb_model* model, const hmcb_chains* chains, const 
   if (chains->n_chains == 0) return 0;
   const Entry* e = choose_entry(*model);
   if (!e) return HMCB_E_UNSUPPORTED;
+  // short trajectories: chains run their transitions in registers for as long as the first stage accepts
+  // (k_dr0_multi_ws); at nleap=20 a transition by stage launches spends more on loading and storing q than on integrating
+  if (K > 1 && n_leap < 48 && !io->moment_sum && model->dtype == HMCB_F64 && !model->invmetric_diag &&
+      chains->stride_dim == 1 && chains->stride_chain == model->d && chains->n_chains >= short_min_chains() && !rng->p_inject &&
+      !rng->u_inject && !rng->p_prev && !(out && out->p0_out) && !getenv("HMCB_NO_DR_SHORT")) {
+    rc = drhmc_sample_short(e, model, chains, rng, n_leap, step_size, nprops, stepfactor, convention, K, io, out, workspace,
+                            workspace_bytes, (cudaStream_t)stream);
+    if (rc != 1) return rc;
+  }
   const int S = sample_split_for(chains->n_chains);
   DrLayout L[kMaxSplit];
   size_t offc[kMaxSplit], need = 0;

@@ -13,7 +13,7 @@
 namespace hmcb {
 
 enum Op { OP_HMC = 0, OP_DR0 = 1, OP_DRN = 2, OP_LEAPFROG = 3, OP_LOGPGRAD = 4, OP_QUERY = 5, OP_MALA = 6, OP_ADHMC = 7,
-          OP_QUERY_AD = 8, OP_GHMC = 9, OP_ADWALK = 10, OP_QUERY_WALK = 11, OP_HMC_MULTI = 12 };
+          OP_QUERY_AD = 8, OP_GHMC = 9, OP_ADWALK = 10, OP_QUERY_WALK = 11, OP_HMC_MULTI = 12, OP_DR0_MULTI = 13 };
 constexpr int kGhmcMaxEpl = 32;  // GHMC keeps q, p and the gradient: 3*EPL values per lane
 constexpr int kMalaMaxEpl = 28;  // MALA keeps q, grad, q1, grad1 in registers: 4*EPL values per lane
 
@@ -45,6 +45,18 @@ struct MultiHmcArgs {
   TransArgs<T> a;
   int32_t K;
   int32_t* n_accept;
+  int32_t applied;
+};
+
+// one pass of the multi-pass sample mode for short trajectories (k_dr0_multi_ws); query_only asks whether this shape has it
+template <typename T>
+struct MultiDrArgs {
+  TransArgs<T> a;
+  int32_t max_steps;
+  const int32_t* list;
+  const int32_t* list_count;
+  int32_t* iter_of;
+  int32_t query_only;
   int32_t applied;
 };
 
@@ -216,6 +228,27 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
         return 0;
       }
     }
+  }
+  if (op == OP_DR0_MULTI) {
+    MultiDrArgs<T>& m = *(MultiDrArgs<T>*)args;
+    m.applied = 0;
+    if constexpr (LPC == 1 && UNITM && sizeof(T) == 8 && EPL >= 20 && !GAUSS) {
+      const TransArgs<T>& a = m.a;
+      const size_t bytes = (size_t)EPL * kWsComputeThreads * (sizeof(T) + 2 * sizeof(float)) + 64;
+      if (!a.p_inject && !a.u_inject && !a.p_prev && !a.p0_out && !(a.rng_flags & HMCB_RNG_NORMAL_F64) &&
+          bytes <= (size_t)max_optin_smem() && !getenv("HMCB_NO_WS")) {
+        m.applied = 1;
+        if (!m.query_only) {
+          auto k = k_dr0_multi_ws<Model, T, EPL>;
+          HMCB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+          const int64_t need = (a.n_chains + kWsComputeThreads - 1) / kWsComputeThreads;
+          const int grid = (int)(need < sm_count() ? need : sm_count());
+          k<<<grid, kWsThreads, bytes, st>>>(model, a, m.max_steps, m.list, m.list_count, m.iter_of);
+          HMCB_CUDA(cudaPeekAtLastError());
+        }
+      }
+    }
+    return 0;
   }
   if (op == OP_HMC_MULTI) {
     MultiHmcArgs<T>& m = *(MultiHmcArgs<T>*)args;

@@ -71,6 +71,13 @@ struct TransArgs {
   int32_t tile_io;   // set by the launcher when the per-warp staging tile was allocated (see warp_tile_load)
   int32_t dr_phase;  // MODE_DRN: 0 the whole stage in one kernel; 1 up to the first point where the chains of a warp part
                      // ways (after the first ghost trajectory), parking those that go on; 2 the parked chains
+  // multi-pass sample mode for short trajectories (k_dr0_multi_ws + these stage kernels, see hmcb_drhmc_sample):
+  const int32_t* iter_of;   // [n_chains] which transition of the call a chain's running delayed-rejection stages belong to
+  int32_t* iter_done;       // [n_chains] transitions a chain has completed
+  int32_t* cont_list;       // chains that completed a transition here and have more to do: run on by the next pass
+  int32_t* cont_count;      // [1]
+  int32_t* n_accept;        // [n_chains] += 1 per accepted transition
+  int32_t K_total;          // transitions per chain in the call
   int32_t prefer_plain;  // caller's wish: k_transition rather than the warp-specialised kernel (pipelined sample calls)
   int32_t L[kMaxProps];
   T eps[kMaxProps];
@@ -507,9 +514,25 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
         lpt[0][i] = (prob_rule && i < J) ? a.ws.ptries[chain * kMaxProps + i] : T(1);
       }
       cH = a.ws.counts[3 * chain]; cVg = a.ws.counts[3 * chain + 1]; cLeap = a.ws.counts[3 * chain + 2];
+      const uint32_t it_add = a.iter_of ? (uint32_t)a.iter_of[chain] : 0u;   // the draws of this chain's running transition
+      // the end of a chain's transition in the multi-pass sample mode: totals, and on to the next pass if it has more to do
+      auto transition_done = [&](bool accepted) {
+        if (a.iter_of && c.lane == 0) {
+          if (a.n_accept && accepted) a.n_accept[chain] += 1;
+          const int done = (int)it_add + 1;
+          a.iter_done[chain] = done;
+          if (done < a.K_total) a.cont_list[atomicAdd(a.cont_count, 1)] = (int32_t)chain;
+        }
+      };
+      auto put_counts = [&]() {
+        if (a.counts && c.lane == 0) {
+          if (a.iter_of) { a.counts[3 * chain] += cH; a.counts[3 * chain + 1] += cVg; a.counts[3 * chain + 2] += cLeap; }
+          else { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = cLeap; }
+        }
+      };
       if (prob_rule && !resume) {
         // one more uniform decides whether stage J is attempted at all (src/algorithms.py:710-711): code -2 if not
-        const double u_try = draw_uniform<T>(a, chain, 2 * J - 1);
+        const double u_try = draw_uniform<T>(a, chain, 2 * J - 1, it_add);
         if (u_try > (double)lpt[0][J - 1]) {
           if (c.lane == 0) {
             for (int i = 0; i < a.nprops; ++i) {
@@ -517,8 +540,9 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
               if (a.ptries_out) a.ptries_out[chain * a.nprops + i] = lpt[0][i];
             }
             if (a.code) a.code[chain] = -2;
-            if (a.counts) { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = cLeap; }
           }
+          put_counts();
+          transition_done(false);
           if (a.q_out != a.q_in) {
 #pragma unroll
             for (int s = 0; s < EPL; ++s) {
@@ -527,7 +551,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
             }
           }
           if (a.p_out) {
-            draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);
+            draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d, it_add);
             store_vec<T, EPL, LPC>(p, a.p_out, qoff, a.sd, c.lane, d);
           }
           continue;
@@ -563,7 +587,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
           have_qp = false;      // (q, -p) of the proposal are in registers already
         } else if (lvl == 0) {
           load_vec<T, EPL, LPC>(q, a.q_in, qoff, a.sd, c.lane, d, T(1));
-          draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);
+          draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d, it_add);
         } else {
           const T* fq = fr + (int64_t)(2 * (lvl - 1)) * EPL * FT;
 #pragma unroll
@@ -677,7 +701,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
       if (t_bad(prob_top)) prob_top = T(0);
       const T aJ = prob_top < T(1) ? prob_top : T(1);
       if (prob_rule == 2) lpt[0][J] = t_bad(lpf[0]) ? T(1) : T(1) - aJ;                 // src/algorithms.py:808-809
-      const double u = draw_uniform<T>(a, chain, prob_rule ? 2 * J : J);
+      const double u = draw_uniform<T>(a, chain, prob_rule ? 2 * J : J, it_add);
       const bool accept = u < (double)aJ;
       const bool finished = accept || (J == a.nprops - 1);
       if (c.lane == 0) {
@@ -690,7 +714,6 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
             for (int i = 0; i < a.nprops; ++i) a.ptries_out[chain * a.nprops + i] = lpt[0][i];
           }
           if (a.code) a.code[chain] = a.dr_conv ? (accept ? J : -1) : (accept ? J + 1 : 0);
-          if (a.counts) { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = cLeap; }
         } else {
           a.ws.avec[chain * kMaxProps + J] = aJ;
           if (prob_rule) a.ws.ptries[chain * kMaxProps + J] = lpt[0][J];
@@ -700,6 +723,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
         }
       }
       if (finished) {
+        put_counts();
+        transition_done(accept);
         if (accept) {
           // the stage-J proposal was parked in frame 0
           const T* fq = fr;
@@ -716,7 +741,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_transition(const Model model,
             }
           }
           if (a.p_out) {
-            draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d);
+            draw_momentum<T, EPL, LPC, UNITM>(p, a, minv, chain, c.lane, d, it_add);
             store_vec<T, EPL, LPC>(p, a.p_out, qoff, a.sd, c.lane, d);
           }
         }

@@ -206,3 +206,36 @@ def test_k_hmc_transitions_with_moments_and_in_place():
     c = pyhmc.HMC(models.Funnel(d), device=dev, seed=2).engine
     c.hmc_sample(qc, L, eps, _lib.RULE_PYHMC, K, q_out=qc)          # fused kernel, in place
     assert torch.equal(qc, q)
+
+
+@pytest.mark.parametrize("conv", [_lib.DR_ALGORITHMS, _lib.DR_MULTISTEP, _lib.DR_PROB_METROP, _lib.DR_PROB_HASTINGS])
+@pytest.mark.parametrize("nprops,eps,K", [(3, 0.25, 19), (3, 0.6, 9), (2, 0.45, 8), (1, 0.3, 5), (4, 0.5, 11)])
+def test_short_trajectory_sample_mode_equals_single_calls(conv, nprops, eps, K, monkeypatch):
+    """hmcb_drhmc_sample at short trajectories (nleap < 48, no moments, d=50 funnel: k_dr0_multi_ws -- chains run in
+    registers while the first stage accepts, the stage kernels finish the transitions that do not, pass after pass):
+    every output equals K single hmcb_drhmc_step calls, at high and at low acceptance, several chunks of 8."""
+    d, C, nleap, f = 50, 6000, 6, 2.0
+    monkeypatch.setenv("HMCB_DR_SHORT_MIN", "4096")      # the library uses this form from 2^19 chains on
+    dev = _dev()
+    q0 = torch.as_tensor(_q0("funnel", C, d, 29), device=dev)
+    a = algorithms.DRHMC(models.Funnel(d), device=dev, seed=41, chain_offset=3).engine
+    b = algorithms.DRHMC(models.Funnel(d), device=dev, seed=41, chain_offset=3).engine
+    a.iteration = b.iteration = 100
+    q = q0
+    counts = torch.zeros((C, 3), dtype=torch.int32, device=dev)
+    nacc = torch.zeros(C, dtype=torch.int32, device=dev)
+    stage0 = 0.0
+    for k in range(K):
+        r = a.drhmc_step(q, nleap, eps, nprops, f, convention=conv)
+        q = r["q"]
+        counts += r["counts"]
+        nacc += (r["code"] >= (0 if conv else 1)).int()
+        stage0 += (r["code"] == (0 if conv else 1)).double().mean().item() / K
+    macc = torch.zeros(C, dtype=torch.int32, device=dev)
+    rb = b.drhmc_sample(q0, nleap, eps, nprops, f, K, n_accept=macc, convention=conv, want_p=True)
+    assert torch.equal(rb["q"], q), "%d chains differ" % (rb["q"] != q).any(dim=1).sum().item()
+    assert torch.equal(rb["code"], r["code"]) and torch.equal(rb["avec"], r["avec"]) and torch.equal(rb["p"], r["p"])
+    if "ptries" in r:
+        assert torch.equal(rb["ptries"], r["ptries"])
+    assert torch.equal(rb["counts"], counts) and torch.equal(macc, nacc)
+    print("first-stage acceptance %.2f" % stage0)
