@@ -4,14 +4,19 @@ Neal's funnel d=50, delayed-rejection HMC (nleap=150, step 0.2 -> lpath 30 as
 scripts_old/jobscripts/run_funnel2.sh:21-22; nprops=3, stepfactor=2), 2^20 chains.
 Chains are independent, so N GPUs shard them by global chain id with no data-path
 collective.  Default: weak scaling -- every GPU runs the N=1 workload (2^20 chains per
-GPU, N*2^20 in total); `--scaling strong` keeps 2^20 chains in total, as the BASELINE
-config words it.
+GPU, N*2^20 in total); at N > 1 the line also carries a `strong` block: 2^20 chains in
+total, as the BASELINE config words it (`--scaling strong` makes that the headline).
 
-A "step" is one DRHMC transition of every chain.  Prints ONE JSON line.
-  value  : gradient evaluations/s (the reference's Vgcount counter, src/pyhmc.py:21-23),
-           chain state resident in HBM
-  e2e    : same metric through the public API with HOST (pinned) buffers, copies timed
-  roofline / cpu_baseline / clocks: see DESIGN.md "Measurement"
+A "step" is one DRHMC transition of every chain with its running moments; the timed
+region is ONE hmcb_drhmc_sample call of K steps.  Prints ONE JSON line on stdout.
+  value      : gradient evaluations/s (the reference's Vgcount counter, src/pyhmc.py:21-23),
+               chain state resident in HBM; per_call: the same by single hmcb_drhmc_step calls
+  e2e        : same metric through the public API with HOST (pinned) buffers, copies timed,
+               and link_floor_ms (the copies alone)
+  roofline   : algorithmic rate of the timed call over the FP64 peak measured in the run,
+               per-stage kernel figures beside it
+  strong, secondary, stationary, autocorr, gates, cpu_baseline, config1_cpu, clocks:
+               see DESIGN.md "Measurement"
 `--impl reference` times the CPU path (the numpy oracle port of the reference's
 DRHMC.step; the reference itself cannot travel to the GPU box) on all host cores.
 """
