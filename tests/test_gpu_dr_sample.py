@@ -239,3 +239,30 @@ def test_short_trajectory_sample_mode_equals_single_calls(conv, nprops, eps, K, 
         assert torch.equal(rb["ptries"], r["ptries"])
     assert torch.equal(rb["counts"], counts) and torch.equal(macc, nacc)
     print("first-stage acceptance %.2f" % stage0)
+
+
+@pytest.mark.parametrize("nleap,conv", [(7, _lib.DR_ALGORITHMS), (60, _lib.DR_PROB_HASTINGS)])
+def test_running_moments_of_a_four_range_sample_call(nleap, conv):
+    """>= 131,072 chains: four chain ranges on four streams, plain stage-0 kernel, one moments / counters pass per range and
+    transition -- the sums must be hmcb_moments_accumulate's, bit for bit (nleap=60 also takes stage 2 through its two
+    kernels)."""
+    d, C, K = 50, 140003, 3
+    dev = _dev()
+    q0 = torch.as_tensor(_q0("funnel", C, d, 37), device=dev)
+    a = algorithms.DRHMC(models.Funnel(d), device=dev, seed=6).engine
+    b = algorithms.DRHMC(models.Funnel(d), device=dev, seed=6).engine
+    q = q0
+    s1, s2 = torch.zeros_like(q0), torch.zeros_like(q0)
+    counts = torch.zeros((C, 3), dtype=torch.int32, device=dev)
+    for k in range(K):
+        r = a.drhmc_step(q, nleap, 0.3, 3, 2.0, convention=conv)
+        q = r["q"]
+        a.moments_accumulate(q, s1, s2)
+        counts += r["counts"]
+    t1, t2 = torch.zeros_like(q0), torch.zeros_like(q0)
+    rb = b.drhmc_sample(q0, nleap, 0.3, 3, 2.0, K, msum=t1, msumsq=t2, convention=conv)
+    assert torch.equal(rb["q"], q) and torch.equal(rb["counts"], counts) and torch.equal(rb["code"], r["code"])
+    assert torch.equal(t1, s1), "%d rows of the running sum differ" % (t1 != s1).any(dim=1).sum().item()
+    assert torch.equal(t2, s2)
+    codes = set(r["code"].tolist())
+    assert len(codes) >= 3
