@@ -306,8 +306,8 @@ class Engine:
         chunks of chains that flow through a copy-in stream, two compute streams and a copy-out
         stream -- host-to-device copies, the stage kernels, device-to-host copies -- chained by
         events, so both copy engines and the SMs
-        work at the same time and the inbound copies run back to back.  The first and last
-        chunk are half-size: the pipeline fills and drains on small pieces.  Chains are
+        work at the same time and the inbound copies run back to back.  The first chunks grow from a
+        quarter to full size and the last is half-size: the pipeline fills and drains on small pieces.  Chains are
         independent and draws are keyed by global chain id, so the result is bit-identical to
         the one-shot call.  q_host: CPU tensor [C,d] (pinned for full copy speed); returns
         pinned CPU tensors owned by the engine: two sets, used alternately, so a result stays valid
@@ -349,9 +349,13 @@ class Engine:
         stage = self._host_stage[1]
         s_in, s_out = self._streams[0], self._streams[1]
         runs = self._streams[2:2 + max(1, min(4, int(run_streams)))]
-        # chunk boundaries: halves at both ends, equal pieces between
-        if n_chunks >= 3:
-            w = [0.5] + [1.0] * (n_chunks - 1) + [0.5]
+        # chunk boundaries
+        if n_chunks >= 4:
+            # a rising head (the copy-out engine, the slower direction and the one that bounds the call, starts ~0.6 ms
+            # sooner than behind one half-size chunk) and a half-size tail
+            w = [0.25, 0.5, 0.75] + [1.0] * (n_chunks - 2) + [0.5]
+        elif n_chunks == 3:
+            w = [0.5, 1.0, 1.0, 0.5]
         else:
             w = [1.0] * n_chunks
         acc, bounds = 0.0, [0]
@@ -361,29 +365,43 @@ class Engine:
         bounds[-1] = C_
         for st in self._streams:
             st.wait_stream(cur)
+        # host_timeline (debug): set engine.host_timeline = [] before the call and every chunk appends
+        # [index, chains, copy-in done, run start, run done, copy-out done] as timing events
+        tl = getattr(self, "host_timeline", None)
+
+        def _tev(stream):
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(stream)
+            return ev
+        if tl is not None:
+            tl.append(_tev(cur))
         for i in range(len(bounds) - 1):
             lo, hi = bounds[i], bounds[i + 1]
             if hi == lo:
                 continue
             with torch.cuda.stream(s_in):
                 stage["q_in"][lo:hi].copy_(q_host[lo:hi], non_blocking=True)
-                ev_in = s_in.record_event()
+                ev_in = _tev(s_in) if tl is not None else s_in.record_event()
             # consecutive chunks alternate between two compute streams (each with its own scratch), so the
             # thin last DR stages of one chunk share the GPU with the first stage of the next
             s_run = runs[i % len(runs)]
             with torch.cuda.stream(s_run):
                 s_run.wait_event(ev_in)
+                if tl is not None:
+                    tl.append([i, hi - lo, ev_in, _tev(s_run)])
                 self.drhmc_step(stage["q_in"][lo:hi], n_leap, step_size, nprops, stepfactor, want_p=want_p,
                                 q_out=stage["q"][lo:hi], p_out=None if not want_p else stage["p"][lo:hi],
                                 code_out=stage["code"][lo:hi], avec_out=stage["avec"][lo:hi],
                                 counts_out=stage["counts"][lo:hi], extra_offset=lo, ws_slot=i % len(runs),
                                 advance=False)
-                ev_run = s_run.record_event()
+                ev_run = _tev(s_run) if tl is not None else s_run.record_event()
             with torch.cuda.stream(s_out):
                 s_out.wait_event(ev_run)
                 for k in ("q", "p", "code", "avec", "counts"):
                     if host[k] is not None:
                         host[k][lo:hi].copy_(stage[k][lo:hi], non_blocking=True)
+                if tl is not None:
+                    tl[-1] += [ev_run, _tev(s_out)]
         s_out.synchronize()
         for s_run in runs:
             cur.wait_stream(s_run)
