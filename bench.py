@@ -590,7 +590,19 @@ def secondary_block(a, dev, world, rank, fp64_peak, peaks):
     ms, out = timed(lambda: h.engine.hmc_sample(q, 20, 0.1, _lib.RULE_PYHMC, Kh))
     row("funnel d=50 HMC L=20 eps=0.1, 2^20 chains, %d transitions per launch (hmcb_hmc_sample, k_hmc_multi_ws)" % Kh, ms / Kh,
         Ct * 21, 7 * d)
-    del q, counts
+    # GHMC (partial momentum refresh, cached V and grad V): one launch per transition moves six state arrays,
+    # K per launch keeps them in registers
+    gh = algorithms.GHMC(fm, device=dev, seed=1, chain_offset=lo)
+    pg = torch.randn(C, d, generator=g, dtype=torch.float64).to(dev)
+    for nl in (20, 1):
+        o0 = gh.engine.ghmc_sample(q, pg, nl, 0.1, 0.5, 4)
+        ms, out = timed(lambda: gh.engine.ghmc_step(o0["q"], o0["p"], nl, 0.1, 0.5, V=o0["V"], Vg=o0["Vg"]))
+        row("funnel d=50 GHMC nleap=%d eps=0.1 alpha=0.5, 2^20 chains, one call per transition" % nl, ms, Ct * nl, 7 * d,
+            extra={"state_bytes_per_s": 6.0 * Ct * d * 8 / (ms * 1e-3), "frac_of_hbm_peak": 6.0 * Ct * d * 8 / (ms * 1e-3) / 1e9 / (peaks["hbm_gbs"] * world)})
+        Kg = 16
+        ms, out = timed(lambda: gh.engine.ghmc_sample(o0["q"], o0["p"], nl, 0.1, 0.5, Kg, V=o0["V"], Vg=o0["Vg"]))
+        row("funnel d=50 GHMC nleap=%d, %d transitions per launch (hmcb_ghmc_sample, k_ghmc_multi)" % (nl, Kg), ms / Kg, Ct * nl, 7 * d)
+    del q, counts, pg, o0
 
     # config 4: Bayesian logistic regression N=100,000 D=128, 16,384 chains, HMC L=10 (tcgen05 gradient GEMMs)
     N, D, Ct, L = 100000, 128, 16384, 10

@@ -104,6 +104,8 @@ SIGNATURES = {
                                  C.POINTER(MalaIO), C.c_void_p]),
     "hmcb_ghmc_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
                                  C.POINTER(GhmcIO), C.c_void_p]),
+    "hmcb_ghmc_sample": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
+                                   C.POINTER(GhmcIO), C.c_int32, C.c_void_p, C.c_void_p]),
     "hmcb_adhmc_eps0_workspace_bytes": (C.c_size_t, [C.POINTER(Model), C.c_int64]),
     "hmcb_adhmc_eps0_step": (C.c_int, [C.POINTER(Model), C.POINTER(Chains), C.POINTER(Rng), C.c_int32, C.c_double,
                                        C.POINTER(C.c_double), C.c_int32, C.c_int32, C.POINTER(AdhmcOut), C.c_void_p,

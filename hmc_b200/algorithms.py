@@ -331,13 +331,35 @@ class GHMC(HMC):
         return (b.out(out["q"]), b.out(out["p"]), b.out(out["V"]), b.out(out["Vg"]), b.out(code), b.out(out["Hs"]),
                 b.out(out["counts"]))
 
-    def sample(self, q, p=None, callback=None, **kwargs):
-        """src/algorithms.py:284-303: every iteration is stored; p starts as a fresh normal draw."""
+    def _sample_fused_ghmc(self, b, state, pd, alpha, pu=None, delta=0.0):
+        """store=False form of sample(): burn-in and sampling as one hmcb_ghmc_sample call each; the state keeps the
+        final q, p (and u), the accept counts and summed work counters of the nsamples kept transitions."""
+        e = self.engine
+        qd, V, Vg = b.q, None, None
+        for K, keep in ((self.burnin, False), (self.nsamples, True)):
+            if K < 1:
+                continue
+            out = e.ghmc_sample(qd, pd, self.nleap, self.step_size, alpha, K, V=V, Vg=Vg, pu=pu, delta=delta)
+            qd, pd, V, Vg, pu = out["q"], out["p"], out["V"], out["Vg"], out["u"]
+            if keep:
+                state.n_accept, state.counts = b.out(out["n_accept"]), b.out(out["counts"])
+        state.i = self.nsamples + self.burnin
+        state.q, state.p = b.out(qd), b.out(pd)
+        if pu is not None:
+            state.u = b.out(pu)
+        state.samples = state.accepts = state.Hs = None
+        return state
+
+    def sample(self, q, p=None, callback=None, store=True, **kwargs):
+        """src/algorithms.py:284-303: every iteration is stored; p starts as a fresh normal draw.  store=False keeps no
+        history and runs each phase as one fused call (see _sample_fused_ghmc)."""
         self._parse_kwargs_sample(**kwargs)
         state = Sampler()
         b = self._device_q(q)
         qd = b.q
         pd = torch.randn(qd.shape, dtype=qd.dtype, device=qd.device) if p is None else self._as_dev(p, b)
+        if not store:
+            return self._sample_fused_ghmc(b, state, pd, kwargs["alpha"])
         V, Vg = None, None
         for i in range(self.nsamples + self.burnin):
             out = self.engine.ghmc_step(qd, pd, self.nleap, self.step_size, kwargs["alpha"], V=V, Vg=Vg)
@@ -380,15 +402,22 @@ class Persistent_GHMC(GHMC):
         return (b.out(out["q"]), b.out(out["p"]), b.out(out["u"]), b.out(out["V"]), b.out(out["Vg"]), b.out(code),
                 b.out(out["Hs"]), b.out(out["counts"]))
 
-    def sample(self, q, p=None, callback=None, **kwargs):
-        """src/algorithms.py:336-357."""
+    def sample(self, q, p=None, callback=None, store=True, u=None, **kwargs):
+        """src/algorithms.py:336-357.  store=False: no history, each phase one fused call; u [C] sets the initial
+        persistent variable (default: a normal draw per chain, as the reference draws one)."""
         self._parse_kwargs_sample(**kwargs)
         state = Sampler()
         state.u = []
         b = self._device_q(q)
         qd = b.q
         pd = torch.randn(qd.shape, dtype=qd.dtype, device=qd.device) if p is None else self._as_dev(p, b)
-        ud = torch.randn(qd.shape[0], dtype=torch.float64, device=qd.device)
+        if u is None:
+            ud = torch.randn(qd.shape[0], dtype=torch.float64, device=qd.device)
+        else:
+            ud = torch.as_tensor(np.asarray(u, dtype=np.float64) if not torch.is_tensor(u) else u, dtype=torch.float64)
+            ud = ud.reshape(-1).to(qd.device).contiguous()
+        if not store:
+            return self._sample_fused_ghmc(b, state, pd, kwargs["alpha"], pu=ud, delta=kwargs["delta"])
         V, Vg = None, None
         for i in range(self.nsamples + self.burnin):
             out = self.engine.ghmc_step(qd, pd, self.nleap, self.step_size, kwargs["alpha"], V=V, Vg=Vg, pu=ud,

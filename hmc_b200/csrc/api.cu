@@ -314,7 +314,8 @@ static int mala_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c
 
 template <typename T>
 static int ghmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c, const hmcb_rng* r, int n_leap,
-                       double eps, const hmcb_ghmc_io* io, cudaStream_t st) {
+                       double eps, const hmcb_ghmc_io* io, cudaStream_t st, int K = 1, int accumulate = 0,
+                       int32_t* n_accept = nullptr, int* applied = nullptr) {
   GhmcArgs<T> g;
   memset(&g, 0, sizeof(g));
   fill_args(g.t, m, c, r, nullptr);
@@ -324,7 +325,11 @@ static int ghmc_step_t(const Entry* e, const hmcb_model* m, const hmcb_chains* c
   g.t.p_out = (T*)io->p_out; g.t.code = io->code; g.t.energies = (T*)io->energies; g.t.counts = io->counts;
   g.V_in = (const T*)io->V_in; g.Vg_in = (const T*)io->Vg_in; g.V_out = (T*)io->V_out; g.Vg_out = (T*)io->Vg_out;
   g.pu_in = io->u_in; g.pu_out = io->u_out; g.delta = io->delta;
-  return e->fn(*m, OP_GHMC, &g, st);
+  g.K = K; g.accumulate = accumulate; g.n_accept = n_accept;
+  if (!applied) return e->fn(*m, OP_GHMC, &g, st);
+  const int rc = e->fn(*m, OP_GHMC_MULTI, &g, st);        // the whole loop in one launch, where the shape has the kernel
+  *applied = g.applied;
+  return rc;
 }
 
 static int ad_frame_threads(const Entry* e, const hmcb_model* m, int64_t n_chains, int64_t& ft, int& epl,
@@ -1065,6 +1070,55 @@ int hmcb_ghmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmc
   cudaStream_t st = (cudaStream_t)stream;
   if (model->dtype == HMCB_F64) return ghmc_step_t<double>(e, model, chains, rng, n_leap, step_size, io, st);
   return ghmc_step_t<float>(e, model, chains, rng, n_leap, step_size, io, st);
+}
+
+int hmcb_ghmc_sample(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
+                     double step_size, const hmcb_ghmc_io* io, int32_t n_transitions, int32_t* n_accept, void* stream) {
+  int rc;
+  if ((rc = check_model(model))) return rc;
+  if ((rc = check_chains(chains))) return rc;
+  HMCB_CHECK_ARG(rng != nullptr && io != nullptr, "rng/io is NULL");
+  HMCB_CHECK_ARG(n_leap >= 0, "n_leap must be >= 0");
+  const int K = n_transitions;
+  HMCB_CHECK_ARG(K >= 1, "n_transitions must be >= 1");
+  HMCB_CHECK_ARG(rng->p_prev != nullptr, "rng->p_prev (the momentum the first transition refreshes) is NULL");
+  HMCB_CHECK_ARG(rng->alpha >= -1.0 && rng->alpha <= 1.0, "alpha must be in [-1, 1]");
+  HMCB_CHECK_ARG(K == 1 || (!rng->p_inject && !rng->u_inject), "injected draws are defined for n_transitions == 1 only");
+  HMCB_CHECK_ARG(io->p_out && io->V_out && io->Vg_out, "p_out, V_out and Vg_out carry the state between transitions: all required");
+  HMCB_CHECK_ARG(!io->u_in || io->u_out, "u_in needs u_out");
+  if (chains->n_chains == 0) return 0;
+  // One launch per transition is bound by its six state arrays and wants hmcb_ghmc_step's 4 lanes per chain; K transitions
+  // in one launch are bound by arithmetic and want the fewest lanes that hold d (d=50 funnel, 2^20 chains, nleap=20, per
+  // transition: 1.58 ms single; fused 0.71 ms with 4 lanes, 0.58 ms with 2).  HMCB_LPC pins one shape for both.
+  const bool fuse = K > 1 && model->kind != HMCB_MODEL_GAUSSIAN && !getenv("HMCB_NO_MULTI");
+  const Entry* e = choose_entry_lanes(*model, kGhmcMaxEpl, (model->d >= 32 && !fuse) ? 4 : 1);
+  if (!e) return HMCB_E_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool f64 = model->dtype == HMCB_F64;
+  if (fuse) {
+    int applied = 0;
+    rc = f64 ? ghmc_step_t<double>(e, model, chains, rng, n_leap, step_size, io, st, K, 0, n_accept, &applied)
+             : ghmc_step_t<float>(e, model, chains, rng, n_leap, step_size, io, st, K, 0, n_accept, &applied);
+    if (rc || applied) return rc;
+  }
+  // otherwise launch by launch, the later ones in place on the outputs of the one before; counters summed by the kernel
+  for (int k = 0; k < K; ++k) {
+    hmcb_chains cs = *chains;
+    hmcb_rng rs = *rng;
+    hmcb_ghmc_io is = *io;
+    if (k > 0) {
+      cs.q_in = cs.q_out;
+      rs.p_prev = io->p_out;
+      is.V_in = io->V_out;
+      is.Vg_in = io->Vg_out;
+      if (io->u_in) is.u_in = io->u_out;
+    }
+    rs.iteration = rng->iteration + (uint64_t)k;
+    rc = f64 ? ghmc_step_t<double>(e, model, &cs, &rs, n_leap, step_size, &is, st, 1, k > 0, n_accept)
+             : ghmc_step_t<float>(e, model, &cs, &rs, n_leap, step_size, &is, st, 1, k > 0, n_accept);
+    if (rc) return rc;
+  }
+  return 0;
 }
 
 // The step-size kernels keep the base state of their trial sweeps in registers when a lane holds at most

@@ -233,4 +233,8 @@ template <> __device__ __forceinline__ float t_rsqrt<float>(float x) { return 1.
 
 template <typename T> __device__ __forceinline__ bool t_bad(T x) { return isnan(x) || isinf(x); }
 
+// a product the compiler may not fuse into a following sum
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+
 }  // namespace hmcb

@@ -153,6 +153,11 @@ struct GhmcArgs {
   const double* pu_in;     // [C] persistent uniform, or nullptr (plain GHMC)
   double* pu_out;
   double delta;
+  // hmcb_ghmc_sample: K transitions (k_ghmc_multi), or launch by launch with counts summed (accumulate) -- n_accept[C] += accepted
+  int32_t K;
+  int32_t accumulate;
+  int32_t* n_accept;
+  int32_t applied;         // set by the launcher: this shape has k_ghmc_multi
 };
 
 template <class Model, typename T, int EPL, int LPC, bool UNITM, int THREADS, int MINB>
@@ -249,7 +254,11 @@ __global__ void __launch_bounds__(THREADS, MINB) k_ghmc(const Model model, const
     if (c.lane == 0) {
       if (a.code) a.code[chain] = bad ? -1 : (accept ? 1 : 0);
       if (a.energies) { a.energies[2 * chain] = H0; a.energies[2 * chain + 1] = H1; }
-      if (a.counts) { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = 1; }
+      if (a.counts) {
+        if (ga.accumulate) { a.counts[3 * chain] += cH; a.counts[3 * chain + 1] += cVg; a.counts[3 * chain + 2] += 1; }
+        else { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = 1; }
+      }
+      if (ga.n_accept) ga.n_accept[chain] += accept ? 1 : 0;
       if (ga.V_out) ga.V_out[chain] = accept ? V1 : (had_cache ? V0 : (T)NAN);
       if (ga.pu_out) ga.pu_out[chain] = accept ? u / (double)prob : u;
     }
@@ -280,6 +289,186 @@ __global__ void __launch_bounds__(THREADS, MINB) k_ghmc(const Model model, const
           store_vec<T, EPL, LPC>(g, ga.Vg_out, off, a.sd, c.lane, d);
         }
       }
+    }
+  }
+}
+
+// ------------------------------------------------------------------ K GHMC transitions per launch
+// The loop of GHMC.sample / Persistent_GHMC.sample (src/algorithms.py:284-303, :336-357) for one chain per group of
+// lanes: q, the momentum and the cached gradient stay in registers over the K transitions (with nleap = 1 a single
+// launch moves six state arrays per gradient -- HBM-bound like MALA); what a rejection comes back to -- the
+// start point, the refreshed momentum (returned flipped) and the cached gradient -- sits in shared memory, slot s of
+// thread t at s*THREADS + t.  Transition k draws with iteration a.iteration + k and follows k_ghmc's per-chain cache
+// rules (V = grad V = None until the first acceptance: recomputed and counted every time), so the results -- state,
+// caches, persistent uniform, the last transition's code and energies, the summed counters -- are bit-identical to K
+// launches of k_ghmc.
+template <class Model, typename T, int EPL, int LPC, bool UNITM, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) k_ghmc_multi(const Model model, const GhmcArgs<T> ga) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  using Lay = Layout<EPL, LPC>;
+  constexpr int GPB = THREADS / LPC;
+  const TransArgs<T>& a = ga.t;
+  const int d = a.d;
+  T* sQ = reinterpret_cast<T*>(smem_raw) + threadIdx.x;
+  T* sP = sQ + EPL * THREADS;
+  T* sG = sP + EPL * THREADS;
+  GroupCtx<T> c;
+  c.lane = threadIdx.x & (LPC - 1);
+  c.d = d;
+  const int group_in_warp = (threadIdx.x & 31) / LPC;
+  c.mask = (LPC == 32) ? 0xffffffffu : (((1u << LPC) - 1u) << (group_in_warp * LPC));
+  c.smem_q = nullptr;
+  T minv[UNITM ? 1 : EPL];
+  if (!UNITM) {
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) {
+      const int i = Lay::elem(c.lane, s);
+      minv[UNITM ? 0 : s] = (i < d) ? a.minv[i] : T(1);
+    }
+  } else {
+    minv[0] = T(1);
+  }
+  const int64_t total_groups = (int64_t)gridDim.x * GPB;
+  const int N = a.L[0] > 1 ? a.L[0] : 1;
+  const int K = ga.K;
+  const T eps = a.eps[0], heps = T(0.5) * a.eps[0];
+  for (int64_t chain = ((int64_t)blockIdx.x * THREADS + threadIdx.x) / LPC; chain < a.n_chains; chain += total_groups) {
+    const int64_t off = chain * a.sc;
+    T q[EPL], p[EPL], g[EPL];
+    load_vec<T, EPL, LPC>(q, a.q_in, off, a.sd, c.lane, d, T(1));
+#pragma unroll
+    for (int s = 0; s < EPL; ++s) sQ[s * THREADS] = q[s];
+    {
+      T pv[EPL];
+      load_vec<T, EPL, LPC>(pv, a.p_prev, off, a.sd, c.lane, d, T(1));
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) sP[s * THREADS] = pv[s];      // the carried momentum lives in sP between transitions
+    }
+    int cH = 0, cVg = 0, nacc = 0;
+    T V0 = T(0);
+    bool has = ga.Vg_in != nullptr;
+    if (has && ga.V_in) {
+      V0 = ga.V_in[chain];
+      if (isnan(V0)) has = false;
+    }
+    if (has) {
+      load_vec<T, EPL, LPC>(g, ga.Vg_in, off, a.sd, c.lane, d, T(1));
+      if (!ga.V_in) {                       // a cached gradient without its potential: one H evaluation, once
+        T tmp[EPL];
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) tmp[s] = T(0);
+        V0 = model.template kick<EPL, LPC, true>(q, tmp, T(-1), c);
+        cH += 1;
+      }
+    }
+    double pu = ga.pu_in ? ga.pu_in[chain] : 0.0;
+#pragma unroll 1
+    for (int k = 0; k < K; ++k) {
+      // p = alpha * p_carried + beta * pn (draw_momentum's arithmetic, the carried momentum read from sP)
+      fill_normals<T, EPL, LPC>(p, a.seed, (uint64_t)(a.chain_offset + chain), a.iteration + (uint32_t)k, c.lane, d, a.rng_flags);
+      if (!UNITM) {
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) p[s] *= t_rsqrt<T>(minv[UNITM ? 0 : s]);
+      }
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) {
+        p[s] = mix_momentum(a.alpha, sP[s * THREADS], a.beta, p[s]);
+        sP[s * THREADS] = p[s];             // now the refreshed momentum: what a rejection returns, flipped
+      }
+      const T K0 = kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+      const bool had_cache = has;
+      if (!has) {
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) g[s] = T(0);
+        V0 = model.template kick<EPL, LPC, true>(q, g, T(-1), c);
+        cVg += 1;
+        cH += 1;
+      } else {
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) sG[s * THREADS] = g[s];
+      }
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) p[s] = fma(-heps, g[s], p[s]);
+#pragma unroll 1
+      for (int i = 1; i < N; ++i) {
+        drift<T, EPL, UNITM>(q, p, minv, eps);
+        model.template kick<EPL, LPC, false>(q, p, eps, c);
+      }
+      cVg += N - 1;
+      drift<T, EPL, UNITM>(q, p, minv, eps);
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) g[s] = T(0);
+      const T V1 = model.template kick<EPL, LPC, true>(q, g, T(-1), c);
+      cVg += 1;
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) p[s] = fma(-heps, g[s], p[s]);
+      const T H0 = V0 + K0, H1 = V1 + kinetic<T, EPL, LPC, UNITM>(p, minv, c.mask);
+      // sum(q0 - q1) with diff_sum's partial sums (padded slots hold 0 on both sides)
+      T acc[4] = {T(0), T(0), T(0), T(0)};
+#pragma unroll
+      for (int s0 = 0; s0 < EPL; s0 += 8) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          if (s0 + e < EPL) acc[e & 3] += sQ[(s0 + e) * THREADS] - q[s0 + e];
+      }
+      const T dq = group_sum_masked<LPC, T>((acc[0] + acc[1]) + (acc[2] + acc[3]), c.mask);
+      const T prob = t_exp<T>(H0 - H1);
+      const bool bad = t_bad(prob) || dq == T(0);
+      double u;
+      if (ga.pu_in) {
+        const double w = pu + 1.0 + ga.delta;
+        double r = fmod(w, 2.0);
+        if (r < 0.0) r += 2.0;
+        u = r - 1.0;
+      } else {
+        u = draw_uniform<T>(a, chain, 0, (uint32_t)k);
+      }
+      const T pm = prob < T(1) ? prob : T(1);
+      const bool accept = !bad && !(u > (double)pm);
+      pu = accept ? u / (double)prob : u;
+      if (k == K - 1 && c.lane == 0) {
+        if (a.code) a.code[chain] = bad ? -1 : (accept ? 1 : 0);
+        if (a.energies) { a.energies[2 * chain] = H0; a.energies[2 * chain + 1] = H1; }
+      }
+      if (accept) {
+        ++nacc;
+        has = true;
+        V0 = V1;
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) {
+          sQ[s * THREADS] = q[s];
+          sP[s * THREADS] = p[s];
+        }
+      } else {
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) {
+          q[s] = sQ[s * THREADS];
+          sP[s * THREADS] = -sP[s * THREADS];
+        }
+        if (had_cache) {
+#pragma unroll
+          for (int s = 0; s < EPL; ++s) g[s] = sG[s * THREADS];
+        }
+      }
+    }
+    store_vec<T, EPL, LPC>(q, a.q_out, off, a.sd, c.lane, d);
+    if (a.p_out) {
+#pragma unroll
+      for (int s = 0; s < EPL; ++s) p[s] = sP[s * THREADS];
+      store_vec<T, EPL, LPC>(p, a.p_out, off, a.sd, c.lane, d);
+    }
+    if (ga.Vg_out) {
+      if (!has) {
+#pragma unroll
+        for (int s = 0; s < EPL; ++s) g[s] = (T)NAN;        // still "None" for this chain
+      }
+      store_vec<T, EPL, LPC>(g, ga.Vg_out, off, a.sd, c.lane, d);
+    }
+    if (c.lane == 0) {
+      if (ga.V_out) ga.V_out[chain] = has ? V0 : (T)NAN;
+      if (ga.pu_out) ga.pu_out[chain] = pu;
+      if (ga.n_accept) ga.n_accept[chain] += nacc;
+      if (a.counts) { a.counts[3 * chain] = cH; a.counts[3 * chain + 1] = cVg; a.counts[3 * chain + 2] = K; }
     }
   }
 }

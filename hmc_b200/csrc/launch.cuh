@@ -13,7 +13,7 @@
 namespace hmcb {
 
 enum Op { OP_HMC = 0, OP_DR0 = 1, OP_DRN = 2, OP_LEAPFROG = 3, OP_LOGPGRAD = 4, OP_QUERY = 5, OP_MALA = 6, OP_ADHMC = 7,
-          OP_QUERY_AD = 8, OP_GHMC = 9, OP_ADWALK = 10, OP_QUERY_WALK = 11, OP_HMC_MULTI = 12, OP_DR0_MULTI = 13 };
+          OP_QUERY_AD = 8, OP_GHMC = 9, OP_ADWALK = 10, OP_QUERY_WALK = 11, OP_HMC_MULTI = 12, OP_DR0_MULTI = 13, OP_GHMC_MULTI = 14 };
 constexpr int kGhmcMaxEpl = 32;  // GHMC keeps q, p and the gradient: 3*EPL values per lane
 constexpr int kMalaMaxEpl = 28;  // MALA keeps q, grad, q1, grad1 in registers: 4*EPL values per lane
 
@@ -343,6 +343,22 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
         set_error("internal: GHMC is not compiled for EPL=%d", EPL);
         return HMCB_E_UNSUPPORTED;
       }
+    }
+    case OP_GHMC_MULTI: {
+      GhmcArgs<T>& a = *(GhmcArgs<T>*)args;
+      a.applied = 0;
+      if constexpr (EPL <= kGhmcMaxEpl && !GAUSS) {
+        // q0, the refreshed momentum and the cached gradient of the running transition: 3*EPL values per thread
+        const size_t bytes = 3 * (size_t)EPL * THREADS * sizeof(T);
+        if (bytes <= (size_t)max_optin_smem() && !getenv("HMCB_NO_MULTI")) {
+          constexpr int MB = min_blocks_for<T, (3 * EPL + 1) / 2, UNITM, GAUSS>();
+          auto k = k_ghmc_multi<Model, T, EPL, LPC, UNITM, THREADS, MB>;
+          if ((rc = prep_smem(k, max_blocks, bytes))) return rc;
+          k<<<grid_for(a.t.n_chains, max_blocks), THREADS, bytes, st>>>(model, a);
+          a.applied = 1;
+        }
+      }
+      break;
     }
     case OP_ADHMC: {
       auto k = k_adhmc_eps0<Model, T, EPL, LPC, UNITM, THREADS, MINB>;

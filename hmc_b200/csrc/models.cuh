@@ -62,11 +62,15 @@ struct FunnelModel {
     T S = acc[0];
 #pragma unroll
     for (int o = LPC >> 1; o > 0; o >>= 1) S += __shfl_xor_sync(c.mask, S, o);
-    const T gv = fma(v, inv_s2, half_n) - T(0.5) * e * S;
-    p[0] = own_v ? (p[0] - h * gv) : fma(-he, q[0], p[0]);
+    // every multiply-add below is written as the fma it is meant to be: left to the compiler, whether a product is fused
+    // into the sum that follows depends on what the call site makes constant (h = -1 into a zeroed p in the GHMC kernels),
+    // and two kernels that must agree bit for bit then differ in the last place for a few chains per step
+    const T hE = T(0.5) * e;
+    const T gv = fma(-hE, S, fma(v, inv_s2, half_n));
+    p[0] = own_v ? fma(-h, gv, p[0]) : fma(-he, q[0], p[0]);
 #pragma unroll
     for (int s = 1; s < EPL; ++s) p[s] = fma(-he, q[s], p[s]);
-    if (WANT_V) return T(0.5) * v * v * inv_s2 + half_n * v + T(0.5) * e * S;
+    if (WANT_V) return fma(hE, S, fma(half_n, v, mul_rn(T(0.5) * v * v, inv_s2)));
     return T(0);
   }
 };
@@ -99,7 +103,9 @@ struct RosenbrockModel {
       const T am = a - u;
       const T r = fma(-u, u, w);
       const T br = b * r;
-      const T gu = T(-2) * am - T(4) * u * br;  // dV/du * T
+      // dV/du * T = -2 (a-u) - 4 u b r with the fma explicit (see FunnelModel), in the form the compiler chose on its own:
+      // fma(-4u, br, -2(a-u)) costs the d=100 kernels 8 % (same arithmetic, a third more spills)
+      const T gu = fma(T(-2), am, -(T(4) * u * br));
       const T gw = T(2) * br;                   // dV/dw * T
       p[s] = valid ? fma(-hs, gu, p[s]) : p[s];
       p[s + 1] = valid ? fma(-hs, gw, p[s + 1]) : p[s + 1];

@@ -433,6 +433,36 @@ class Engine:
         out["_keep"] = keep
         return out
 
+    def ghmc_sample(self, q, p_prev, n_leap, step_size, alpha, n_transitions, V=None, Vg=None, pu=None, delta=0.0,
+                    n_accept=None):
+        """hmcb_ghmc_sample: n_transitions GHMC (pu=None) or Persistent_GHMC transitions in one call; the returned
+        q, p, V, Vg, u are the final ones, code / Hs the last transition's, counts the sums; n_accept [C] int32 (or a
+        new zeroed one) is incremented by the number of accepted transitions."""
+        m = self._ensure()
+        C_ = q.shape[0]
+        K = int(n_transitions)
+        with torch.cuda.device(self.device):
+            if n_accept is None:
+                n_accept = torch.zeros(C_, dtype=torch.int32, device=self.device)
+            out = {"q": torch.empty_like(q), "p": torch.empty_like(q),
+                   "V": torch.empty(C_, dtype=self.dtype, device=self.device), "Vg": torch.empty_like(q),
+                   "u": torch.empty(C_, dtype=torch.float64, device=self.device) if pu is not None else None,
+                   "code": torch.empty(C_, dtype=torch.int32, device=self.device),
+                   "Hs": torch.empty((C_, 2), dtype=self.dtype, device=self.device),
+                   "counts": torch.empty((C_, 3), dtype=torch.int32, device=self.device), "n_accept": n_accept}
+            io = _lib.GhmcIO()
+            io.p_out, io.V_in, io.Vg_in = _lib.ptr(out["p"]), _lib.ptr(V), _lib.ptr(Vg)
+            io.V_out, io.Vg_out = _lib.ptr(out["V"]), _lib.ptr(out["Vg"])
+            io.u_in, io.u_out, io.delta = _lib.ptr(pu), _lib.ptr(out["u"]), float(delta)
+            io.code, io.energies, io.counts = _lib.ptr(out["code"]), _lib.ptr(out["Hs"]), _lib.ptr(out["counts"])
+            ch = self._chains(q, out["q"])
+            r, keep = self._rng(None, None, 1, C_, p_prev, alpha)
+            _lib.check(self.lib.hmcb_ghmc_sample(C.byref(m), C.byref(ch), C.byref(r), int(n_leap), float(step_size),
+                                                 C.byref(io), K, C.c_void_p(n_accept.data_ptr()), self._stream()))
+        self.iteration += K
+        out["_keep"] = keep
+        return out
+
     def mala_step(self, q, eps, n_steps=1, V=None, Vg=None, z=None, u=None, q_out=None):
         """hmcb_mala_step on device tensor q [C,d]; V [C] / Vg [C,d] are the cached
         potential and its gradient (None on the first call)."""

@@ -295,6 +295,22 @@ typedef struct hmcb_ghmc_io {
 int hmcb_ghmc_step(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
                    double step_size, const hmcb_ghmc_io* io, void* stream);
 
+/* n_transitions consecutive GHMC / Persistent_GHMC transitions, the loop of GHMC.sample and Persistent_GHMC.sample
+ * (src/algorithms.py:284-303, :336-357) without the stored history: transition k draws with iteration
+ * rng->iteration + k and starts from the state, momentum, cached V / grad V and persistent uniform the one before
+ * left.  rng->p_prev is the momentum the first transition refreshes (required); io->V_in / Vg_in / u_in as for
+ * hmcb_ghmc_step; io->p_out, V_out, Vg_out (and u_out with u_in) are required and hold the final values; code and
+ * energies are those of the LAST transition, counts the sums over all of them, n_accept[C] (or NULL) is INCREMENTED by
+ * the number of accepted transitions.  Shapes that have the kernel run all transitions in ONE launch with q, p and the
+ * gradient in registers (with a short trajectory a single launch moves six state arrays per gradient); the others
+ * (dense Gaussian) launch once per transition, in place.  Either way the result is that of n_transitions calls of
+ * hmcb_ghmc_step chained through their outputs: bit-identical when both run the same lanes-per-chain shape (always
+ * for d < 32; from d = 32 the step takes 4 lanes per chain for its memory traffic and the fused launch the fewest that
+ * hold d, so in-chain sums round differently in the last place -- the environment variable HMCB_LPC pins one shape
+ * for both).  Injected draws: n_transitions == 1 only. */
+int hmcb_ghmc_sample(const hmcb_model* model, const hmcb_chains* chains, const hmcb_rng* rng, int32_t n_leap,
+                     double step_size, const hmcb_ghmc_io* io, int32_t n_transitions, int32_t* n_accept, void* stream);
+
 /* AdHMC_eps0.hmc_step (src/adaptivehmc.py:138-192) and its step-size draw get_stepsize
  * (:111-134).  Give either n_leap >= 1 (and tint = 0) or tint = Tint > 0 (and n_leap = 0): with
  * Tint the trajectory takes int(Tint/eps) + 1 steps of the drawn step size (:178-179).  `steps` is a HOST array of the ntry trial step sizes
