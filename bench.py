@@ -806,13 +806,18 @@ def run_hmcb(a):
         dist.barrier()
         torch.cuda.synchronize()
         t0 = time.time()
-        g_e2e = 0
+        # the gradient evaluations of a step (this bench's numerator) are summed from the DEVICE copy of the step's counters,
+        # asynchronously behind the step -- every result, counters included, still lands in host memory inside the step;
+        # summing the host copy here instead is 0.5 ms of single-core work per step that is the bench's, not the call's
+        g_dev = torch.zeros((), dtype=torch.int64, device=dev)
         for _ in range(Ke):
             r = dr_e.step(qh, a.nleap, a.step_size, a.nprops, a.stepfactor, want_p=False)
             qh = r[0]
-            g_e2e += int(r[4][:, 1].sum())
+            g_dev += dr_e.engine._host_stage[1]["counts"][:, 1].sum(dtype=torch.int64)
         torch.cuda.synchronize()
         dt = torch.tensor([time.time() - t0], dtype=torch.float64, device=dev)
+        g_e2e = int(g_dev)
+        assert int(r[4][:, 1].sum()) > 0 and r[4].device.type == "cpu"
         r = (qh,)
         for _ in range(2):                                                       # warm the pinned p buffers
             r = dr_e.step(r[0], a.nleap, a.step_size, a.nprops, a.stepfactor)
