@@ -350,9 +350,10 @@ class GHMC(HMC):
         state.samples = state.accepts = state.Hs = None
         return state
 
-    def sample(self, q, p=None, callback=None, store=True, **kwargs):
+    def sample(self, q, p=None, callback=None, store=True, draws=None, **kwargs):
         """src/algorithms.py:284-303: every iteration is stored; p starts as a fresh normal draw.  store=False keeps no
-        history and runs each phase as one fused call (see _sample_fused_ghmc)."""
+        history and runs each phase as one fused call (see _sample_fused_ghmc).  draws = (pn [T,C,d], u [T,C,1]) replays
+        the refresh normals and Metropolis uniforms of the T = nsamples + burnin iterations (parity runs)."""
         self._parse_kwargs_sample(**kwargs)
         state = Sampler()
         b = self._device_q(q)
@@ -362,7 +363,8 @@ class GHMC(HMC):
             return self._sample_fused_ghmc(b, state, pd, kwargs["alpha"])
         V, Vg = None, None
         for i in range(self.nsamples + self.burnin):
-            out = self.engine.ghmc_step(qd, pd, self.nleap, self.step_size, kwargs["alpha"], V=V, Vg=Vg)
+            out = self.engine.ghmc_step(qd, pd, self.nleap, self.step_size, kwargs["alpha"], V=V, Vg=Vg,
+                                        pn=None if draws is None else draws[0][i], u=None if draws is None else draws[1][i])
             qd, pd, V, Vg = out["q"], out["p"], out["V"], out["Vg"]
             state.i += 1
             state.samples.append(b.out(qd))
@@ -402,9 +404,10 @@ class Persistent_GHMC(GHMC):
         return (b.out(out["q"]), b.out(out["p"]), b.out(out["u"]), b.out(out["V"]), b.out(out["Vg"]), b.out(code),
                 b.out(out["Hs"]), b.out(out["counts"]))
 
-    def sample(self, q, p=None, callback=None, store=True, u=None, **kwargs):
+    def sample(self, q, p=None, callback=None, store=True, u=None, draws=None, **kwargs):
         """src/algorithms.py:336-357.  store=False: no history, each phase one fused call; u [C] sets the initial
-        persistent variable (default: a normal draw per chain, as the reference draws one)."""
+        persistent variable (default: a normal draw per chain, as the reference draws one); draws = pn [T,C,d] replays
+        the refresh normals (parity runs)."""
         self._parse_kwargs_sample(**kwargs)
         state = Sampler()
         state.u = []
@@ -421,7 +424,7 @@ class Persistent_GHMC(GHMC):
         V, Vg = None, None
         for i in range(self.nsamples + self.burnin):
             out = self.engine.ghmc_step(qd, pd, self.nleap, self.step_size, kwargs["alpha"], V=V, Vg=Vg, pu=ud,
-                                        delta=kwargs["delta"])
+                                        delta=kwargs["delta"], pn=None if draws is None else draws[i])
             qd, pd, ud, V, Vg = out["q"], out["p"], out["u"], out["V"], out["Vg"]
             state.i += 1
             state.samples.append(b.out(qd))

@@ -748,6 +748,43 @@ def pghmc_step(model, q, p, u, nleap, step_size, alpha, delta, rng, V_q=None, V_
     return q, p, u, V_q, V_gq, accepted, Hs, cnt.as_list()
 
 
+def ghmc_sample(model, q, nsamples, burnin, step_size, nleap, alpha, rng, p=None, invmetric_diag=None):
+    """algorithms.GHMC.sample, src/algorithms.py:284-303: p starts as one normal vector when not given (:290), V and grad V
+    start as None, every iteration (burn-in included) is stored."""
+    if p is None:
+        p = rng.normal(0, 1, q.size).reshape(q.shape)
+    V_q, V_gq = None, None
+    samples, accepts, Hs, counts = [], [], [], []
+    for i in range(nsamples + burnin):
+        q, p, V_q, V_gq, acc, H, count = ghmc_step(model, q, p, nleap, step_size, alpha, rng, V_q, V_gq, invmetric_diag)
+        samples.append(q)
+        accepts.append(acc)
+        Hs.append(H)
+        counts.append(count)
+    return dict(samples=np.array(samples), accepts=np.array(accepts), Hs=np.array(Hs), counts=np.array(counts),
+                i=nsamples + burnin, p=p, V_q=V_q, V_gq=V_gq)
+
+
+def pghmc_sample(model, q, nsamples, burnin, step_size, nleap, alpha, delta, rng, p=None, invmetric_diag=None):
+    """algorithms.Persistent_GHMC.sample, src/algorithms.py:336-357: as GHMC.sample, plus the persistent variable u, which
+    starts as ONE scalar normal draw (:343, after the momentum draw) and is stored every iteration."""
+    if p is None:
+        p = rng.normal(0, 1, q.size).reshape(q.shape)
+    u = rng.normal(0, 1)
+    V_q, V_gq = None, None
+    samples, accepts, Hs, counts, us = [], [], [], [], []
+    for i in range(nsamples + burnin):
+        q, p, u, V_q, V_gq, acc, H, count = pghmc_step(model, q, p, u, nleap, step_size, alpha, delta, rng, V_q, V_gq,
+                                                       invmetric_diag)
+        samples.append(q)
+        accepts.append(acc)
+        Hs.append(H)
+        counts.append(count)
+        us.append(u)
+    return dict(samples=np.array(samples), accepts=np.array(accepts), Hs=np.array(Hs), counts=np.array(counts),
+                u=np.array(us), i=nsamples + burnin, p=p)
+
+
 def drghmc_step(model, q, p, nleap, step_size, alpha, nprops, stepfactor, rng, invmetric_diag=None):
     """algorithms.DRGHMC.step, src/algorithms.py:596-625: DRHMC.step started from the partially
     refreshed momentum p0 = alpha p + sqrt(1-alpha^2) pn; p0 is returned (not flipped) on rejection."""

@@ -185,3 +185,34 @@ def test_gaussian_partial_refresh_reaches_the_generic_kernel(monkeypatch):
         assert torch.equal(p0, alpha * pv + np.sqrt(1 - alpha ** 2) * z)
         res.append((qo, p0))
     assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
+
+
+@pytest.mark.parametrize("persistent", [False, True])
+def test_sample_loop_vs_oracle(persistent):
+    """GHMC.sample / Persistent_GHMC.sample (src/algorithms.py:284-303, :336-357) with replayed draws against
+    oracle.samplers.ghmc_sample / pghmc_sample (pinned to the reference loops in tests/test_oracle_vs_reference.py):
+    every iteration stored, caches starting as None, u carried."""
+    d, C, ns, nb, N, alpha = 10, 6, 7, 3, 5, 0.6
+    eps = 0.4 if persistent else 0.25      # (u in (-1, 1) accepts easily: a longer step for some rejections)
+    pm, om = _models("funnel", d)
+    T = ns + nb
+    P, U = replay.make_draws(410, T, C, d, 1)
+    rng = np.random.default_rng(2)
+    q0, p0, u0 = rng.uniform(-1, 1, (C, d)), rng.standard_normal((C, d)), rng.standard_normal(C)
+    kw = dict(nsamples=ns, burnin=nb, step_size=eps, nleap=N, alpha=alpha)
+    if persistent:
+        st = algorithms.Persistent_GHMC(pm, device=_dev()).sample(q0, p=p0, u=u0, draws=P, delta=0.37, **kw)
+    else:
+        st = algorithms.GHMC(pm, device=_dev()).sample(q0, p=p0, draws=(P, U), **kw)
+    assert st.i == T and st.samples.shape == (T, C, d) and st.accepts.shape == (T, C) and st.counts.shape == (T, C, 3)
+    for c in range(C):
+        if persistent:
+            o = samplers.pghmc_sample(om, q0[c], ns, nb, eps, N, alpha, 0.37,
+                                      replay.Draws([np.array([u0[c]])] + list(P[:, c]), []), p=p0[c])
+            _close(st.u[:, c], o["u"], rtol=1e-8, atol=1e-11)
+        else:
+            o = samplers.ghmc_sample(om, q0[c], ns, nb, eps, N, alpha, replay.Draws(list(P[:, c]), U[:, c, 0]), p=p0[c])
+        assert np.array_equal(st.accepts[:, c], o["accepts"]) and np.array_equal(st.counts[:, c], o["counts"])
+        _close(st.samples[:, c], o["samples"])
+        _close(st.Hs[:, c], o["Hs"], rtol=1e-9, atol=1e-10)
+    assert len(set(st.accepts.ravel().tolist())) >= 2

@@ -344,6 +344,35 @@ def test_ghmc_and_pghmc_bit_exact(mi, alpha):
         sr, so = out_r[:5], out_o[:5]
 
 
+@pytest.mark.parametrize("persistent", [False, True])
+def test_ghmc_sample_bookkeeping_bit_exact(persistent, capsys):
+    """algorithms.GHMC.sample / Persistent_GHMC.sample (src/algorithms.py:284-303, :336-357): the leading momentum draw
+    (and the scalar normal that starts u), caches starting as None, every iteration stored."""
+    alg = ref_loader.load("algorithms")
+    model = models.Funnel(10)
+    ns, nb, N, eps, alpha = 8, 3, 5, (0.9 if persistent else 0.25), 0.6
+    P, U = replay.make_draws(91, ns + nb + 1, 1, model.d, 1)
+    q0 = _q0(model, 9)
+    normals = [P[0, 0]] + ([np.array([0.4321])] if persistent else []) + list(P[1:, 0])
+    mk = lambda: replay.Draws(normals, [] if persistent else U[1:, 0, 0])
+    if persistent:
+        ref = alg.Persistent_GHMC(model.log_prob, model.grad_log_prob, model.log_prob_and_grad)
+        with replay.patched_numpy_random(mk()):
+            st = ref.sample(q0, nsamples=ns, burnin=nb, step_size=eps, nleap=N, alpha=alpha, delta=0.37)
+        o = samplers.pghmc_sample(model, q0, ns, nb, eps, N, alpha, 0.37, mk())
+        assert _same(st.u, o["u"])
+    else:
+        ref = alg.GHMC(model.log_prob, model.grad_log_prob, model.log_prob_and_grad)
+        with replay.patched_numpy_random(mk()):
+            st = ref.sample(q0, nsamples=ns, burnin=nb, step_size=eps, nleap=N, alpha=alpha)
+        o = samplers.ghmc_sample(model, q0, ns, nb, eps, N, alpha, mk())
+    capsys.readouterr()
+    assert st.i == o["i"] == ns + nb and st.samples.shape == (ns + nb, model.d)
+    assert _same(st.samples, o["samples"]) and _same(st.accepts, o["accepts"])
+    assert _same(st.Hs, o["Hs"]) and _same(st.counts, o["counts"])
+    assert len(set(np.asarray(st.accepts).tolist())) >= 2
+
+
 @pytest.mark.parametrize("mi", [0, 3])
 def test_drghmc_bit_exact(mi, capsys):
     alg = ref_loader.load("algorithms")
