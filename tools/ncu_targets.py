@@ -50,6 +50,9 @@ if "ghmc" in which:
     pp = torch.randn(C, d, generator=g, dtype=torch.float64).to(dev)
     o0 = gh.ghmc_step(q, pp, 20, 0.1, 0.5)
     twice(lambda: gh.ghmc_step(o0["q"], o0["p"], 20, 0.1, 0.5, V=o0["V"], Vg=o0["Vg"]))
+    twice(lambda: gh.ghmc_sample(o0["q"], o0["p"], 20, 0.1, 0.5, 8, V=o0["V"], Vg=o0["Vg"]))     # k_ghmc_multi, 8 transitions
+    twice(lambda: gh.ghmc_step(o0["q"], o0["p"], 1, 0.1, 0.5, V=o0["V"], Vg=o0["Vg"]))
+    twice(lambda: gh.ghmc_sample(o0["q"], o0["p"], 1, 0.1, 0.5, 16, V=o0["V"], Vg=o0["Vg"]))
 if "gauss" in which:
     gm = models.CorrGaussian.ar1(100)
     s = pyhmc.HMC(gm, device=dev, seed=1).engine
