@@ -72,7 +72,12 @@ static const Entry* choose_entry_lanes(const hmcb_model& hm, int max_epl, int mi
       if (slots_needed(hm.d, e.lpc) > e.epl || e.epl > max_epl) continue;
       if (hm.kind == HMCB_MODEL_ROSENBROCK && (e.epl & 1)) continue;
       // least padded slots first, then fewest lanes per chain
-      const long cost = (long)e.epl * e.lpc * 64 + e.lpc;
+      long cost = (long)e.epl * e.lpc * 64 + e.lpc;
+      // The pairwise Rosenbrock gradient needs no sum across the lanes of a chain inside the trajectory, so more lanes cost
+      // nothing there, and past 50 slots per lane q and p no longer fit the register file beside the gradient's temporaries:
+      // d=100, 131,072 chains, HMC L=20: 2 lanes x 52 slots 0.273 ms per launch / 0.192 at 16 transitions per launch,
+      // 4 lanes x 28 slots 0.226 / 0.172 (tools/rosen_lanes_probe.py)
+      if (hm.kind == HMCB_MODEL_ROSENBROCK && e.epl > 50) cost += cost / 4;
       if (!best || cost < best_cost) {
         best = &e;
         best_cost = cost;
