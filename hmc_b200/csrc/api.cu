@@ -749,7 +749,11 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
 // ranges of a sample call: enough that the stage kernels of different ranges and transitions always have
 // something to fill each other's tails with, few enough that a range's first stage still covers the GPU
 static int sample_split_for(int64_t n_chains) {
-  int s = n_chains >= (1 << 17) ? 4 : (n_chains >= (1 << 14) ? 2 : 1);
+  // d=50 funnel, nleap=150, ms per transition by ranges (tools/dr_sample_bench.py, HMCB_SAMPLE_SPLIT):
+  //   2^19 chains: 4: 2.533  6: 2.549  8: 2.574      2^18: 4: 1.400  8: 1.357      2^17: 4: 0.892  6: 0.875  8: 0.864  12: 1.36
+  //   2^16: 2: 0.734  4: 0.693  8: 0.685             2^15: 2: 0.638  4: 0.624  8: 0.623             2^14: 2: 0.624  4: 0.607  8: 0.624
+  // (below ~2^16 chains the transition is its critical path: one trajectory per stage, 0.6 ms)
+  int s = n_chains >= (1 << 19) ? 4 : (n_chains >= (1 << 16) ? 8 : (n_chains >= (1 << 14) ? 4 : 1));
   if (const char* e = getenv("HMCB_SAMPLE_SPLIT")) {
     const int v = atoi(e);
     if (v >= 1 && v <= kMaxSplit) s = v;

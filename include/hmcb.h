@@ -172,7 +172,7 @@ int hmcb_drhmc_step(const hmcb_model* model, const hmcb_chains* chains, const hm
  * (src/algorithms.py:542-552; scripts_old/funnel/funnelmpi_multistep.py runs the same loop over
  * PyHMC_multistep.multi_step) with the chain state kept on the device.  Each transition is
  * hmcb_drhmc_step's, bit for bit (transition k of a chain draws with iteration rng->iteration + k).
- * Chains are independent, so the batch is cut into up to 4 contiguous chain ranges, each running
+ * Chains are independent, so the batch is cut into up to 8 contiguous chain ranges, each running
  * its K transitions back to back on a stream of its own (the caller's and helper streams the
  * library owns, forked from and joined into `stream`): the thin last round of one range's stage
  * kernel is filled by another range's kernels -- of the same or of a later transition -- so the

@@ -243,7 +243,7 @@ def test_short_trajectory_sample_mode_equals_single_calls(conv, nprops, eps, K, 
 
 @pytest.mark.parametrize("nleap,conv", [(7, _lib.DR_ALGORITHMS), (60, _lib.DR_PROB_HASTINGS)])
 def test_running_moments_of_a_four_range_sample_call(nleap, conv):
-    """>= 131,072 chains: four chain ranges on four streams, plain stage-0 kernel, one moments / counters pass per range and
+    """>= 65,536 chains: several chain ranges (8 here) on as many streams, plain stage-0 kernel, one moments / counters pass per range and
     transition -- the sums must be hmcb_moments_accumulate's, bit for bit (nleap=60 also takes stage 2 through its two
     kernels)."""
     d, C, K = 50, 140003, 3
