@@ -95,21 +95,26 @@ struct RosenbrockModel {
   __device__ __forceinline__ T kick(const T (&q)[EPL], T (&p)[EPL], T h, const GroupCtx<T>& c) const {
     static_assert(EPL % 2 == 0, "Rosenbrock pairs need an even slot count");
     T Vl = T(0);
+    // p -= h grad V with the constants of the pair gradient folded into four per-call factors: with r = w - u^2,
+    //   -h dV/du = (2 hs a) + u (4 b hs r - 2 hs),   -h dV/dw = -2 b hs r,   hs = h / T
+    // -- five FP64 instructions per pair (r, s, p_u + k3, two fmas) where the gradient written out term by term
+    // (a-u, b r, 4u, 4u b r, -2(a-u) - .., 2 b r, two fmas) takes nine: the trajectory loop of the d=100 kernels is bound by
+    // the FP64 pipe's issue rate (57 % active at 0.37 of the algorithmic peak).  Every multiply-add is an explicit fma (see
+    // FunnelModel).
     const T hs = h * inv_T;
+    const T k1 = T(4) * b * hs, k2 = T(-2) * hs, k3 = T(2) * hs * a, kw = T(-2) * b * hs;
 #pragma unroll
     for (int s = 0; s < EPL; s += 2) {
       const bool valid = Layout<EPL, LPC>::elem(c.lane, s) < c.d;  // padding pairs contribute nothing
       const T u = q[s], w = q[s + 1];
-      const T am = a - u;
       const T r = fma(-u, u, w);
-      const T br = b * r;
-      // dV/du * T = -2 (a-u) - 4 u b r with the fma explicit (see FunnelModel), in the form the compiler chose on its own:
-      // fma(-4u, br, -2(a-u)) costs the d=100 kernels 8 % (same arithmetic, a third more spills)
-      const T gu = fma(T(-2), am, -(T(4) * u * br));
-      const T gw = T(2) * br;                   // dV/dw * T
-      p[s] = valid ? fma(-hs, gu, p[s]) : p[s];
-      p[s + 1] = valid ? fma(-hs, gw, p[s + 1]) : p[s + 1];
-      if (WANT_V) Vl += valid ? fma(am, am, br * r) : T(0);
+      const T sl = fma(k1, r, k2);
+      p[s] = valid ? fma(u, sl, p[s] + k3) : p[s];
+      p[s + 1] = valid ? fma(kw, r, p[s + 1]) : p[s + 1];
+      if (WANT_V) {
+        const T am = a - u;
+        Vl += valid ? fma(am, am, mul_rn(b * r, r)) : T(0);
+      }
     }
     if (WANT_V) {
 #pragma unroll
