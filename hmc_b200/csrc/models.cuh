@@ -80,12 +80,16 @@ struct FunnelModel {
 template <typename T>
 struct RosenbrockModel {
   T a, b, inv_T;
+  T b4, a2, bm2;     // 4b, 2a, -2b: operands of the pair gradient, read from the kernel's parameter bank
   static constexpr bool kNeedsSmem = false;
   __host__ static RosenbrockModel make(const hmcb_model& m) {
     RosenbrockModel r;
     r.a = (T)m.par[0];
     r.b = (T)m.par[1];
     r.inv_T = (T)(1.0 / m.par[2]);
+    r.b4 = (T)(4.0 * m.par[1]);
+    r.a2 = (T)(2.0 * m.par[0]);
+    r.bm2 = (T)(-2.0 * m.par[1]);
     return r;
   }
   __host__ __device__ size_t p_smem_elems() const { return 0; }
@@ -95,22 +99,25 @@ struct RosenbrockModel {
   __device__ __forceinline__ T kick(const T (&q)[EPL], T (&p)[EPL], T h, const GroupCtx<T>& c) const {
     static_assert(EPL % 2 == 0, "Rosenbrock pairs need an even slot count");
     T Vl = T(0);
-    // p -= h grad V with the constants of the pair gradient folded into four per-call factors: with r = w - u^2,
-    //   -h dV/du = (2 hs a) + u (4 b hs r - 2 hs),   -h dV/dw = -2 b hs r,   hs = h / T
-    // -- five FP64 instructions per pair (r, s, p_u + k3, two fmas) where the gradient written out term by term
-    // (a-u, b r, 4u, 4u b r, -2(a-u) - .., 2 b r, two fmas) takes nine: the trajectory loop of the d=100 kernels is bound by
-    // the FP64 pipe's issue rate (57 % active at 0.37 of the algorithmic peak).  Every multiply-add is an explicit fma (see
-    // FunnelModel).
+    // p -= h grad V with the pair gradient in nested form: with r = w - u^2 and hs = h / T,
+    //   -h dV/du = hs (u (4b r - 2) + 2a),   -h dV/dw = (-2b hs) r
+    // -- five FP64 instructions per pair (r, 4b r - 2, u (..) + 2a, two fmas into p) where the gradient written out term
+    // by term (a-u, b r, 4u, 4u b r, -2(a-u) - .., 2 b r, two fmas) takes nine: the trajectory loop of the d=100 kernels is
+    // bound by the FP64 pipe's issue rate (57 % active at 0.37 of the algorithmic peak).  4b, 2a, -2b come from the
+    // parameter bank, so the only values live across a kick are hs and -2b hs (four folded per-call factors cost the
+    // step-size kernels, which run at their register limit, a quarter of their speed).  Every multiply-add is an explicit
+    // fma (see FunnelModel).
     const T hs = h * inv_T;
-    const T k1 = T(4) * b * hs, k2 = T(-2) * hs, k3 = T(2) * hs * a, kw = T(-2) * b * hs;
+    const T hsw = hs * bm2;
 #pragma unroll
     for (int s = 0; s < EPL; s += 2) {
       const bool valid = Layout<EPL, LPC>::elem(c.lane, s) < c.d;  // padding pairs contribute nothing
       const T u = q[s], w = q[s + 1];
       const T r = fma(-u, u, w);
-      const T sl = fma(k1, r, k2);
-      p[s] = valid ? fma(u, sl, p[s] + k3) : p[s];
-      p[s + 1] = valid ? fma(kw, r, p[s + 1]) : p[s + 1];
+      const T t = fma(b4, r, T(-2));
+      const T gi = fma(u, t, a2);
+      p[s] = valid ? fma(hs, gi, p[s]) : p[s];
+      p[s + 1] = valid ? fma(hsw, r, p[s + 1]) : p[s + 1];
       if (WANT_V) {
         const T am = a - u;
         Vl += valid ? fma(am, am, mul_rn(b * r, r)) : T(0);
