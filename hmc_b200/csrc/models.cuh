@@ -115,9 +115,12 @@ struct RosenbrockModel {
       const T u = q[s], w = q[s + 1];
       const T r = fma(-u, u, w);
       const T t = fma(b4, r, T(-2));
-      const T gi = fma(u, t, a2);
-      p[s] = valid ? fma(hs, gi, p[s]) : p[s];
-      p[s + 1] = valid ? fma(hsw, r, p[s + 1]) : p[s + 1];
+      // padding pairs hold q = p = 0: r = 0 leaves p_w alone, and with the constant term masked so does u (4b r - 2) + 2a
+      // -- one select on a loop-invariant value instead of one per updated momentum (`valid ? fma(..) : p` put four FSEL
+      // per pair into the trajectory loop: as many instructions beside the 98 DFMA of a d=100 lane as the DFMA themselves)
+      const T gi = fma(u, t, valid ? a2 : T(0));
+      p[s] = fma(hs, gi, p[s]);
+      p[s + 1] = fma(hsw, r, p[s + 1]);
       if (WANT_V) {
         const T am = a - u;
         Vl += valid ? fma(am, am, mul_rn(b * r, r)) : T(0);
