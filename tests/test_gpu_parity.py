@@ -44,7 +44,7 @@ def _oracle_model(spec):
     if k == "funnel":
         return omodels.Funnel(spec["d"], spec.get("sigma", 3.0))
     if k == "rosenbrock":
-        return omodels.Rosenbrock(spec["d"])
+        return omodels.Rosenbrock(spec["d"], spec.get("a", 1.0), spec.get("b", 100.0), spec.get("T", 20.0))
     if k == "gaussian":
         return omodels.CorrGaussian.ar1(spec["d"], spec.get("rho", 0.9))
     raise ValueError(k)
@@ -128,6 +128,36 @@ def test_hmc_step_vs_oracle_all_shapes(kind, d, lpc, monkeypatch):
         _close(q, rq)
         _close(p, rp)
         _close(Hs, rHs, rtol=1e-9, atol=1e-10)
+
+
+@pytest.mark.parametrize("d,lpc", [(2, 0), (10, 8), (18, 4), (50, 2), (100, 0), (100, 32)])
+def test_rosenbrock_other_parameters_on_padded_shapes(d, lpc, monkeypatch):
+    """a != 1, b, T away from the defaults on lane shapes with padding slots: the pair gradient keeps padding pairs out
+    through one masked constant (models.cuh) -- they must stay at q = p = 0 whatever a is.  HMC and DRHMC against the oracle."""
+    if lpc:
+        monkeypatch.setenv("HMCB_LPC", str(lpc))
+    else:
+        monkeypatch.delenv("HMCB_LPC", raising=False)
+    spec = dict(kind="rosenbrock", d=d, a=1.7, b=40.0, T=7.0)
+    om, pmodel = _oracle_model(spec), _product_model(spec)
+    C, N, eps = 29, 7, 0.03
+    rng = np.random.default_rng(d + lpc)
+    q0 = 1.5 + 0.2 * rng.uniform(-1, 1, (C, d))
+    P, U = replay.make_draws(500 + d, 1, C, d, 3)
+    s = algorithms.HMC(pmodel, device=_dev())
+    q, p, code, Hs, counts = s.step(q0, N, eps, p=P[0], u=U[0][:, :1])
+    rq, rp, rcode, rHs, rcounts = _run_oracle_hmc(om, q0, P[0], U[0][:, :1], N, eps, "alg")
+    assert np.array_equal(code, rcode) and np.array_equal(counts, rcounts)
+    _close(q, rq)
+    _close(p, rp)
+    _close(Hs, rHs, rtol=1e-9, atol=1e-10)
+    dr = algorithms.DRHMC(pmodel, device=_dev())
+    q, p, code, avec, counts = dr.step(q0, N, 4 * eps, 3, 2.0, p=P[0], u=U[0])
+    for c in range(C):
+        o = samplers.drhmc_step(om, q0[c], N, 4 * eps, 3, 2.0, replay.Draws([P[0, c]], U[0, c]))
+        assert code[c] == o[2] and list(counts[c]) == o[4]
+        _close(q[c], o[0])
+        _close(avec[c], o[3], rtol=1e-9, atol=1e-11)
 
 
 @pytest.mark.parametrize("kind,d", [("funnel", 10), ("funnel", 50), ("rosenbrock", 20), ("gaussian", 20)])
