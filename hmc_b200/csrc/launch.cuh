@@ -147,6 +147,10 @@ template <class Model, typename T, int EPL, int LPC, bool UNITM, bool GAUSS>
 int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
   constexpr int THREADS = 128;
   constexpr int MINB = min_blocks_for<T, EPL, UNITM, GAUSS>();
+  // the step-size kernels hold a base state beside the running one: at 26+ slots per lane three blocks per SM (168
+  // registers) spill that state in their trial sweeps; two blocks at 255 registers -- Rosenbrock d=100, 131,072 chains:
+  // AdHMC_eps0 1.20 -> 0.98 ms, AdHMC walk 2.40 -> 2.08 ms
+  constexpr int ADMINB = (MINB == 3 && EPL >= 26) ? 2 : MINB;
   constexpr int GPB = THREADS / LPC;
   Model model = Model::make(hm);
   size_t smem = 0;
@@ -361,14 +365,14 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
       break;
     }
     case OP_ADHMC: {
-      auto k = k_adhmc_eps0<Model, T, EPL, LPC, UNITM, THREADS, MINB>;
+      auto k = k_adhmc_eps0<Model, T, EPL, LPC, UNITM, THREADS, ADMINB>;
       if ((rc = prep(k, max_blocks))) return rc;
       AdArgs<T>& a = *(AdArgs<T>*)args;
       k<<<(int)(a.frame_threads / THREADS), THREADS, smem, st>>>(model, a);
       break;
     }
     case OP_QUERY_AD: {
-      auto k = k_adhmc_eps0<Model, T, EPL, LPC, UNITM, THREADS, MINB>;
+      auto k = k_adhmc_eps0<Model, T, EPL, LPC, UNITM, THREADS, ADMINB>;
       if ((rc = prep(k, max_blocks))) return rc;
       LaunchInfo* li = (LaunchInfo*)args;
       li->threads = THREADS;
@@ -378,14 +382,14 @@ int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
       return 0;
     }
     case OP_ADWALK: {
-      auto k = k_adhmc_walk<Model, T, EPL, LPC, UNITM, THREADS, MINB>;
+      auto k = k_adhmc_walk<Model, T, EPL, LPC, UNITM, THREADS, ADMINB>;
       if ((rc = prep(k, max_blocks))) return rc;
       WalkArgs<T>& a = *(WalkArgs<T>*)args;
       k<<<(int)(a.frame_threads / THREADS), THREADS, smem, st>>>(model, a);
       break;
     }
     case OP_QUERY_WALK: {
-      auto k = k_adhmc_walk<Model, T, EPL, LPC, UNITM, THREADS, MINB>;
+      auto k = k_adhmc_walk<Model, T, EPL, LPC, UNITM, THREADS, ADMINB>;
       if ((rc = prep(k, max_blocks))) return rc;
       LaunchInfo* li = (LaunchInfo*)args;
       li->threads = THREADS;
