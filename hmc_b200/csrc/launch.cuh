@@ -147,10 +147,11 @@ template <class Model, typename T, int EPL, int LPC, bool UNITM, bool GAUSS>
 int launch_any(const hmcb_model& hm, int op, void* args, cudaStream_t st) {
   constexpr int THREADS = 128;
   constexpr int MINB = min_blocks_for<T, EPL, UNITM, GAUSS>();
-  // the step-size kernels hold a base state beside the running one: at 26+ slots per lane three blocks per SM (168
-  // registers) spill that state in their trial sweeps; two blocks at 255 registers -- Rosenbrock d=100, 131,072 chains:
-  // AdHMC_eps0 1.20 -> 0.98 ms, AdHMC walk 2.40 -> 2.08 ms
-  constexpr int ADMINB = (MINB == 3 && EPL >= 26) ? 2 : MINB;
+  // the step-size kernels hold a base state beside the running one and spill it in their trial sweeps at the register budget
+  // of the plain transition: one block per SM fewer (measured, 131,072-262,144 chains, AdHMC_eps0 / AdHMC walk in ms --
+  // Rosenbrock d=100: 1.20 -> 0.98 / 2.40 -> 2.08, d=20: 0.163 -> 0.143 / 0.344 -> 0.307; funnel d=10: 0.168 -> 0.155 /
+  // 0.383 -> 0.330, d=50: 0.859 -> 0.853 / 1.776 -> 1.741, d=100: 0.913 -> 0.937 / 1.821 -> 1.808)
+  constexpr int ADMINB = (MINB >= 3) ? MINB - 1 : MINB;
   constexpr int GPB = THREADS / LPC;
   Model model = Model::make(hm);
   size_t smem = 0;
