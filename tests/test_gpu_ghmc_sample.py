@@ -160,3 +160,46 @@ def test_argument_errors():
         e.ghmc_sample(q, p, 3, 0.1, 0.5, 0)
     with pytest.raises(Exception):
         e.ghmc_sample(q, p, 3, 0.1, 1.5, 2)
+
+
+@pytest.mark.parametrize("d,K", [(50, 5), (10, 4), (100, 3)])
+def test_outputs_stay_inside_their_buffers(d, K):
+    """hmcb_ghmc_sample through the C ABI with every output placed inside a larger, sentinel-filled allocation and a
+    ragged chain count (the last warp is partial, and at d=50 / 100 the lanes carry padding slots): nothing outside the
+    [C, ...] windows may change, and the windows must hold what the engine call returns."""
+    import ctypes as C_
+    from hmc_b200 import _lib
+    Cn, G = 1237, 97
+    q, p, u = _start("funnel", Cn, d, torch.float64, 60 + d)
+    a = algorithms.GHMC(models.Funnel(d), device=_dev(), seed=31)
+    b = algorithms.GHMC(models.Funnel(d), device=_dev(), seed=31)
+    ref = a.engine.ghmc_sample(q, p, 3, 0.2, 0.5, K, pu=u, delta=0.2)
+    e = b.engine
+    m = e._ensure()
+    S = -12345.0
+
+    def padded(shape, dtype):
+        n = int(np.prod(shape))
+        buf = torch.full((n + 2 * G,), S if dtype.is_floating_point else -12345, dtype=dtype, device=_dev())
+        return buf, buf[G:G + n].view(shape)
+    bufs = {k: padded(s, t) for k, (s, t) in dict(q=((Cn, d), torch.float64), p=((Cn, d), torch.float64), V=((Cn,), torch.float64),
+                                                  Vg=((Cn, d), torch.float64), u=((Cn,), torch.float64), code=((Cn,), torch.int32),
+                                                  Hs=((Cn, 2), torch.float64), counts=((Cn, 3), torch.int32),
+                                                  n_accept=((Cn,), torch.int32)).items()}
+    bufs["n_accept"][1].zero_()
+    io = _lib.GhmcIO()
+    io.p_out, io.V_in, io.Vg_in = _lib.ptr(bufs["p"][1]), None, None
+    io.V_out, io.Vg_out = _lib.ptr(bufs["V"][1]), _lib.ptr(bufs["Vg"][1])
+    io.u_in, io.u_out, io.delta = _lib.ptr(u), _lib.ptr(bufs["u"][1]), 0.2
+    io.code, io.energies, io.counts = _lib.ptr(bufs["code"][1]), _lib.ptr(bufs["Hs"][1]), _lib.ptr(bufs["counts"][1])
+    ch = e._chains(q, bufs["q"][1])
+    r, keep = e._rng(None, None, 1, Cn, p, 0.5)
+    with torch.cuda.device(_dev()):
+        _lib.check(e.lib.hmcb_ghmc_sample(C_.byref(m), C_.byref(ch), C_.byref(r), 3, 0.2, C_.byref(io), K,
+                                          C_.c_void_p(bufs["n_accept"][1].data_ptr()), e._stream()))
+    torch.cuda.synchronize()
+    for k, (buf, win) in bufs.items():
+        sent = S if buf.dtype.is_floating_point else -12345
+        assert bool((buf[:G] == sent).all()) and bool((buf[-G:] == sent).all()), "wrote outside " + k
+    got = {k: w for k, (_, w) in bufs.items()}
+    _same(got, ref, KEYS + ("u",))
