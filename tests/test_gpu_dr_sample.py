@@ -266,3 +266,51 @@ def test_running_moments_of_a_four_range_sample_call(nleap, conv):
     assert torch.equal(t2, s2)
     codes = set(r["code"].tolist())
     assert len(codes) >= 3
+
+
+@pytest.mark.parametrize("C,which", [(5003, "hmc"), (1237, "hmc"), (5003, "hmcm"), (5003, "dr"), (140003, "dr")])
+def test_sample_calls_stay_inside_caller_buffers(C, which):
+    """The caller-supplied outputs of the sample calls (state, running moments, accept counts, and for DR the code and
+    counters) placed inside larger sentinel-filled allocations, ragged chain counts (a partial last warp; 5003 takes the
+    warp-specialised fused HMC kernel, 1237 the generic one, "hmcm" the per-transition path with moments, 140003 the
+    range-pipelined DR path): nothing outside the
+    windows may change, and the windows equal an unpadded call."""
+    d, K, G = 50, 3, 211
+    dev = _dev()
+    q0 = torch.as_tensor(_q0("funnel", C, d, 5), device=dev)
+    S = -777.0
+
+    def padded(shape, dtype, fill=None):
+        n = int(np.prod(shape))
+        sent = S if dtype.is_floating_point else -777
+        buf = torch.full((n + 2 * G,), sent, dtype=dtype, device=dev)
+        win = buf[G:G + n].view(shape)
+        if fill is not None:
+            win.fill_(fill)
+        return buf, win, sent
+    P = {"q": padded((C, d), torch.float64), "s1": padded((C, d), torch.float64, 0.0), "s2": padded((C, d), torch.float64, 0.0),
+         "na": padded((C,), torch.int32, 0)}
+    if which == "hmc":
+        a = algorithms.HMC(models.Funnel(d), device=dev, seed=3).engine
+        b = algorithms.HMC(models.Funnel(d), device=dev, seed=3).engine
+        ref = a.hmc_sample(q0, 6, 0.2, _lib.RULE_ALG, K)
+        out = b.hmc_sample(q0, 6, 0.2, _lib.RULE_ALG, K, n_accept=P["na"][1], q_out=P["q"][1])
+    elif which == "hmcm":       # with running moments: one launch per transition plus the moments / counters pass
+        a = algorithms.HMC(models.Funnel(d), device=dev, seed=3).engine
+        b = algorithms.HMC(models.Funnel(d), device=dev, seed=3).engine
+        ref = a.hmc_sample(q0, 6, 0.2, _lib.RULE_ALG, K, msum=torch.zeros_like(q0), msumsq=torch.zeros_like(q0))
+        out = b.hmc_sample(q0, 6, 0.2, _lib.RULE_ALG, K, msum=P["s1"][1], msumsq=P["s2"][1], n_accept=P["na"][1], q_out=P["q"][1])
+    else:
+        P["code"] = padded((C,), torch.int32)
+        P["counts"] = padded((C, 3), torch.int32)
+        a = algorithms.DRHMC(models.Funnel(d), device=dev, seed=3).engine
+        b = algorithms.DRHMC(models.Funnel(d), device=dev, seed=3).engine
+        ref = a.drhmc_sample(q0, 7, 0.3, 3, 2.0, K)
+        out = b.drhmc_sample(q0, 7, 0.3, 3, 2.0, K, msum=P["s1"][1], msumsq=P["s2"][1], n_accept=P["na"][1], q_out=P["q"][1],
+                             code_out=P["code"][1], counts_out=P["counts"][1])
+        assert torch.equal(out["code"], ref["code"]) and torch.equal(out["counts"], ref["counts"])
+    torch.cuda.synchronize()
+    assert torch.equal(out["q"], ref["q"]) and torch.equal(P["q"][1], ref["q"])
+    for k, (buf, win, sent) in P.items():
+        assert bool((buf[:G] == sent).all()) and bool((buf[-G:] == sent).all()), "wrote outside " + k
+    assert int(P["na"][1].sum()) > 0 and bool((P["s2"][1] >= 0).all())
